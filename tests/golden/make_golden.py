@@ -1,0 +1,460 @@
+#!/usr/bin/env python3
+"""Generate the golden vectors under tests/golden/ by RUNNING THE REFERENCE ITSELF.
+
+This script is the only thing in the repository that touches /root/reference, and it
+only runs in the build container (the GPU box has no /root/reference).  It imports the
+unmodified reference ``scheduler.py`` with two shims:
+
+  * ``HUGGINGFACE_TOKEN`` set to a dummy value (the module exits at import otherwise,
+    scheduler.py:62-66);
+  * stub ``kubernetes`` modules registered in ``sys.modules`` (scheduler.py:17-18).
+
+and records, as JSON, what the reference computes for the fallback placement path:
+
+  kat_scores.json      best_score bits of ``_fallback_decision`` (scheduler.py:521-559)
+                       on single-node tables, captured with ``sys.settrace`` from the
+                       function's own local ``best_score`` - no restatement involved.
+  decisions.json       chosen index + best_score bits on seeded random clusters (ties,
+                       not-Ready nodes, max_pods == 0, over-full nodes), 3 strategies
+                       plus an unknown strategy string.
+  greedy.json          bind sequences of the reference's own loop: real
+                       ``ContextManager.get_node_metrics`` (scheduler.py:121-170) over a
+                       fake CoreV1Api, real ``_fallback_decision``, fake bind.
+  parsers.json         ``_parse_cpu`` / ``_parse_memory`` (scheduler.py:172-187) and
+                       ``_convert_pod_to_spec`` (scheduler.py:731-764) outputs.
+  config1_trace.json   BASELINE config 1: 3-node cluster x ai-test-pods.yaml through
+                       ``CustomScheduler._schedule_pod`` with the LLM call failing.
+
+Run:  python tests/golden/make_golden.py           (rewrites the JSON files in place)
+"""
+from __future__ import annotations
+
+import asyncio
+import json
+import os
+import struct
+import sys
+import types
+from pathlib import Path
+
+import numpy as np
+
+REF_DIR = Path(os.environ.get("KP_REFERENCE_DIR", "/root/reference"))
+OUT_DIR = Path(__file__).resolve().parent
+
+
+# --------------------------------------------------------------------------------------
+# reference import (unmodified file, two shims)
+# --------------------------------------------------------------------------------------
+def import_reference():
+    os.environ.setdefault("HUGGINGFACE_TOKEN", "dummy-token-for-offline-import")
+    os.environ.setdefault("LOG_LEVEL", "CRITICAL")
+
+    class ApiException(Exception):
+        def __init__(self, status=0, reason=""):
+            super().__init__(f"({status}) {reason}")
+            self.status, self.reason = status, reason
+
+    class _Obj:
+        def __init__(self, **kw):
+            self.__dict__.update(kw)
+
+    k = types.ModuleType("kubernetes")
+    kc = types.ModuleType("kubernetes.client")
+    kcfg = types.ModuleType("kubernetes.config")
+    kw = types.ModuleType("kubernetes.watch")
+    kr = types.ModuleType("kubernetes.client.rest")
+    kr.ApiException = ApiException
+    kcfg.load_kube_config = lambda *a, **kw_: None
+    kc.CoreV1Api = lambda *a, **kw_: None
+    kc.V1Binding = _Obj
+    kc.V1ObjectMeta = _Obj
+    kc.V1ObjectReference = _Obj
+    kc.rest = kr
+    kw.Watch = _Obj
+    k.client, k.config, k.watch = kc, kcfg, kw
+    sys.modules.update({
+        "kubernetes": k, "kubernetes.client": kc, "kubernetes.config": kcfg,
+        "kubernetes.watch": kw, "kubernetes.client.rest": kr,
+    })
+    sys.path.insert(0, str(REF_DIR))
+    import scheduler  # noqa: E402  (the reference)
+    return scheduler
+
+
+def f64_bits(x):
+    if x is None:          # empty node list: the function returns before best_score exists
+        return None
+    return struct.pack(">d", float(x)).hex()
+
+
+# --------------------------------------------------------------------------------------
+# helpers that call the reference function and capture its local best_score
+# --------------------------------------------------------------------------------------
+class ScoreTap:
+    """sys.settrace hook: grabs best_node / best_score locals at _fallback_decision return."""
+
+    def __init__(self, sched):
+        self.code = sched.HuggingFaceClient._fallback_decision.__code__
+        self.best_score = None
+        self.best_node = None
+
+    def _local(self, frame, event, arg):
+        if event == "return":
+            self.best_score = frame.f_locals.get("best_score")
+            self.best_node = frame.f_locals.get("best_node")
+        return self._local
+
+    def _global(self, frame, event, arg):
+        if frame.f_code is self.code:
+            return self._local
+        return None
+
+    def decide(self, sched, nodes, strategy, reason="golden"):
+        sched.CONFIG.setdefault("fallback", {})["strategy"] = strategy
+        self.best_score, self.best_node = None, None
+        sys.settrace(self._global)
+        try:
+            dec = sched.HuggingFaceClient._fallback_decision(None, nodes, reason)
+        finally:
+            sys.settrace(None)
+        return dec
+
+
+READY = [{"type": "Ready", "status": "True", "reason": "KubeletReady"}]
+COND_VARIANTS = {
+    "ready": READY,
+    "false": [{"type": "Ready", "status": "False", "reason": "x"}],
+    "unknown": [{"type": "Ready", "status": "Unknown", "reason": "x"}],
+    "none": [],
+    "other_only": [{"type": "MemoryPressure", "status": "True", "reason": "x"}],
+    "ready_second": [{"type": "DiskPressure", "status": "False", "reason": "x"},
+                     {"type": "Ready", "status": "True", "reason": "x"}],
+}
+
+
+def usage_a3(pc: int, mp: int):
+    # the reference's own expression (scheduler.py:150-151), evaluated by CPython
+    return (pc / mp) * 50 if mp > 0 else 0
+
+
+def mk_node(sched, i, pc, mp, cu=None, mu=None, cond="ready", cpu=8.0, mem=15.616012573242188):
+    u = usage_a3(pc, mp)
+    return sched.NodeMetrics(
+        name=f"node-{i}", cpu_usage_percent=u if cu is None else cu,
+        memory_usage_percent=u if mu is None else mu, available_cpu=cpu,
+        available_memory=mem, pod_count=pc, max_pods=mp, labels={}, taints=[],
+        conditions=COND_VARIANTS[cond])
+
+
+STRATS = ["resource_balanced", "least_loaded", "round_robin", "no_such_strategy"]
+
+
+def gen_kat_scores(sched, tap):
+    rows = []
+    pairs = [(2, 110), (3, 110), (8, 110), (55, 110), (1, 3), (0, 0), (109, 110), (110, 110),
+             (0, 110), (1, 110), (1, 2), (2, 6), (341, 110), (223, 110), (222, 110), (340, 110),
+             (7, 30), (29, 58), (250, 250), (125, 250), (17, 58), (0, 1), (1, 1), (5, 0)]
+    rng = np.random.Generator(np.random.PCG64(11))
+    for _ in range(200):
+        mp = int(rng.choice([30, 58, 110, 250, 1, 7, 1000]))
+        pairs.append((int(rng.integers(0, mp + 1)), mp))
+    for pc, mp in pairs:
+        node = mk_node(sched, 0, pc, mp)
+        row = {"pc": pc, "mp": mp, "usage_bits": f64_bits(node.cpu_usage_percent)}
+        for s in STRATS[:3]:
+            dec = tap.decide(sched, [node], s)
+            row[s] = {"selected": dec.selected_node != "",
+                      "score_bits": f64_bits(tap.best_score),
+                      "score_is_int": isinstance(tap.best_score, int)}
+        rows.append(row)
+    # custom usage values that do not follow A3 (direct NodeMetrics input)
+    custom = []
+    for cu, mu, pc, mp in [(0.0, 0.0, 0, 110), (100.0, 100.0, 0, 110), (150.0, 20.0, 4, 110),
+                           (201.0, 0.5, 4, 110), (33.3, 66.6, 10, 30), (99.999, 1e-9, 1, 58),
+                           (250.0, 250.0, 500, 110), (12.5, 87.5, 0, 0), (400.0, 0.0, 0, 10)]:
+        node = mk_node(sched, 0, pc, mp, cu=cu, mu=mu)
+        row = {"pc": pc, "mp": mp, "cu": cu, "mu": mu}
+        for s in STRATS[:3]:
+            dec = tap.decide(sched, [node], s)
+            row[s] = {"selected": dec.selected_node != "",
+                      "score_bits": f64_bits(tap.best_score)}
+        custom.append(row)
+    return {"a3_usage": rows, "custom_usage": custom}
+
+
+def gen_decisions(sched, tap):
+    cases = []
+    rng = np.random.Generator(np.random.PCG64(7))
+    shapes = [30, 58, 110, 250]
+
+    def record(tag, spec):
+        nodes = [mk_node(sched, i, *sp) for i, sp in enumerate(spec)]
+        out = {}
+        for s in STRATS:
+            dec = tap.decide(sched, nodes, s, reason=f"r-{tag}")
+            idx = -1 if tap.best_node is None else nodes.index(tap.best_node)
+            assert (dec.selected_node == "") == (idx == -1)
+            if idx >= 0:
+                assert dec.selected_node == nodes[idx].name
+            out[s] = {"idx": idx, "score_bits": f64_bits(tap.best_score),
+                      "confidence": dec.confidence, "reasoning": dec.reasoning,
+                      "fallback_needed": dec.fallback_needed}
+        cases.append({"tag": tag,
+                      "nodes": [{"pc": sp[0], "mp": sp[1],
+                                 "cu_bits": f64_bits(n.cpu_usage_percent),
+                                 "mu_bits": f64_bits(n.memory_usage_percent),
+                                 "cond": sp[4] if len(sp) > 4 else "ready"}
+                                for sp, n in zip(spec, nodes)],
+                      "expect": out})
+
+    # behavioural known answers from SURVEY.md §8(c)
+    record("kat-10-5-5", [(10, 110), (5, 110), (5, 110)])
+    record("kat-half-zero", [(55, 110), (0, 0)])
+    record("kat-r04-zero", [(44, 110), (0, 0)])
+    record("kat-341", [(341, 110)])
+    record("kat-223", [(223, 110)])
+    record("kat-all-notready", [(1, 110, None, None, "false"), (2, 110, None, None, "unknown"),
+                                (3, 110, None, None, "none"), (0, 110, None, None, "other_only")])
+    record("kat-ready-second", [(9, 110, None, None, "false"), (9, 110, None, None, "ready_second"),
+                                (9, 110)])
+    record("kat-exact-ties", [(1, 2), (55, 110), (2, 4), (1, 3), (2, 6)])
+    record("kat-empty", [])
+    # seeded random clusters
+    for c in range(60):
+        n = int(rng.integers(1, 48))
+        spec = []
+        homogeneous = c % 3 == 0
+        for _ in range(n):
+            mp = 110 if homogeneous else int(rng.choice(shapes))
+            r = rng.random()
+            if r < 0.04:
+                mp = 0
+            pc = int(rng.integers(0, (mp if mp > 0 else 5) + 1))
+            if rng.random() < 0.03:
+                pc = int(mp * rng.uniform(2.0, 3.5)) if mp > 0 else 3
+            cond = "ready"
+            r = rng.random()
+            if r < 0.08:
+                cond = ["false", "unknown", "none", "other_only"][int(rng.integers(0, 4))]
+            elif r < 0.12:
+                cond = "ready_second"
+            cu = mu = None
+            if c % 5 == 4 and rng.random() < 0.5:       # usage that does not follow A3
+                cu = float(np.round(rng.uniform(0, 120), 3))
+                mu = float(np.round(rng.uniform(0, 120), 3))
+            spec.append((pc, mp, cu, mu, cond))
+        record(f"rand-{c}", spec)
+    return cases
+
+
+# --------------------------------------------------------------------------------------
+# fake K8s API server: the complete surface scheduler.py touches
+# --------------------------------------------------------------------------------------
+class _NS:
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+
+class FakeCoreV1:
+    def __init__(self, node_specs):
+        # node_specs: list of dict(name, cpu, memory, pods, n_running, cond)
+        self.node_specs = node_specs
+        self.pods_on = {ns["name"]: ns["n_running"] for ns in node_specs}
+        self.binds = []
+
+    def list_node(self):
+        items = []
+        for ns in self.node_specs:
+            conds = [_NS(type=c["type"], status=c["status"], reason=c.get("reason"))
+                     for c in COND_VARIANTS[ns.get("cond", "ready")]]
+            alloc = {"cpu": ns["cpu"], "memory": ns["memory"], "pods": ns["pods"]}
+            items.append(_NS(metadata=_NS(name=ns["name"], labels=None),
+                             spec=_NS(taints=None),
+                             status=_NS(conditions=conds, capacity=dict(alloc), allocatable=alloc)))
+        return _NS(items=items)
+
+    def list_pod_for_all_namespaces(self, field_selector=None, **kw):
+        name = field_selector.split("=", 1)[1]
+        return _NS(items=[None] * self.pods_on[name])
+
+    def create_namespaced_binding(self, namespace, body, _preload_content=False):
+        target = body.target.name
+        self.pods_on[target] += 1
+        self.binds.append(target)
+
+
+def gen_greedy(sched, tap):
+    cases = []
+    rng = np.random.Generator(np.random.PCG64(13))
+
+    def run(tag, node_specs, n_pods, strategy):
+        api = FakeCoreV1([dict(ns) for ns in node_specs])
+        cm = sched.ContextManager.__new__(sched.ContextManager)
+        cm.v1 = api
+        seq, scores = [], []
+        first_table = None
+        for _ in range(n_pods):
+            table = cm.get_node_metrics()              # real reference code, A3 usage formula
+            if first_table is None:
+                first_table = table
+            dec = tap.decide(sched, table, strategy)
+            names = [t.name for t in table]
+            idx = names.index(dec.selected_node) if dec.selected_node else -1
+            seq.append(idx)
+            scores.append(f64_bits(tap.best_score))
+            if idx >= 0:                               # scheduler.py:716-721 -> bind
+                api.pods_on[names[idx]] += 1
+        final = [api.pods_on[ns["name"]] for ns in node_specs]
+        cases.append({
+            "tag": tag, "strategy": strategy, "n_pods": n_pods,
+            "nodes": node_specs,
+            "parsed": [{"available_cpu_bits": f64_bits(t.available_cpu),
+                        "available_memory_bits": f64_bits(t.available_memory),
+                        "max_pods": t.max_pods, "pod_count": t.pod_count,
+                        "cu_bits": f64_bits(t.cpu_usage_percent)} for t in first_table],
+            "idx_seq": seq, "score_bits_seq": scores, "final_pod_count": final})
+
+    cfg1 = [dict(name="minikube", cpu="8", memory="16374576Ki", pods="110", n_running=8),
+            dict(name="minikube-m02", cpu="8", memory="16374576Ki", pods="110", n_running=2),
+            dict(name="minikube-m03", cpu="8", memory="16374576Ki", pods="110", n_running=2)]
+    for s in STRATS[:3]:
+        run(f"config1-{s}", cfg1, 12, s)
+    shapes = [("4", "16Gi", "30"), ("16", "64Gi", "58"), ("32", "128Gi", "110"),
+              ("96", "768Gi", "250"), ("7910m", "32780300Ki", "110"), ("2", "4096Mi", "8")]
+    for c in range(12):
+        n = int(rng.integers(2, 24))
+        specs = []
+        for i in range(n):
+            cpu, mem, pods = shapes[int(rng.integers(0, len(shapes)))] if c % 2 else shapes[2]
+            if rng.random() < 0.05:
+                pods = "0"
+            cond = "ready" if rng.random() > 0.1 else "false"
+            mp = int(pods)
+            specs.append(dict(name=f"n{i}", cpu=cpu, memory=mem, pods=pods,
+                              n_running=int(rng.integers(0, max(mp, 1) + 1)), cond=cond))
+        for s in STRATS[:3]:
+            run(f"rand-{c}-{s}", specs, int(rng.integers(20, 120)), s)
+    # a tiny cluster driven past max_pods: the reference never stops at pc == mp, and a
+    # node stops winning only once its score falls to <= -1 (scheduler.py:529,547)
+    tiny = [dict(name="a", cpu="2", memory="4Gi", pods="3", n_running=0),
+            dict(name="b", cpu="2", memory="4Gi", pods="2", n_running=1)]
+    for s in STRATS[:3]:
+        run(f"overfill-{s}", tiny, 24, s)
+    return cases
+
+
+def gen_parsers(sched):
+    cm = sched.ContextManager.__new__(sched.ContextManager)
+    cpu_in = ["8", "250m", "500m", "100m", "7910m", "0", "0.5", "1.5", "32", "96", "4000m",
+              "1m", "123456m", "2.25", "16"]
+    mem_in = ["16374576Ki", "256Mi", "512Mi", "128Mi", "16Gi", "768Gi", "0", "1073741824",
+              "32780300Ki", "1.5Gi", "100Mi", "4096Mi", "17179869184", "1Ki", "0.5Mi"]
+    bad_mem = ["1G", "1M", "1K", "1Ti", "1e3Mi"[:0] or "12x"]
+    out = {"parse_cpu": [{"in": s, "bits": f64_bits(cm._parse_cpu(s))} for s in cpu_in],
+           "parse_memory": [{"in": s, "bits": f64_bits(cm._parse_memory(s))} for s in mem_in],
+           "parse_memory_errors": []}
+    for s in bad_mem:
+        try:
+            cm._parse_memory(s)
+            out["parse_memory_errors"].append({"in": s, "error": None})
+        except Exception as e:  # noqa: BLE001
+            out["parse_memory_errors"].append({"in": s, "error": type(e).__name__})
+
+    cs = sched.CustomScheduler.__new__(sched.CustomScheduler)
+    pods = [
+        [("250m", "256Mi")], [("500m", "512Mi")], [("100m", "128Mi")],
+        [("100m", "64Mi"), ("200m", "64Mi")],                       # 0.1 + 0.2 in fp64
+        [("1", "1Gi"), ("0.5", "512Mi"), ("250m", "1048576Ki")],
+        [("100m", "1073741824")],                                   # plain bytes -> ignored (A4 quirk)
+        [(None, None)], [("", "")], [],
+        [("300m", "100Mi"), ("300m", "100Mi"), ("300m", "100Mi")],
+        [(2, 1024)],                                                # non-string values
+    ]
+    conv = []
+    for i, containers in enumerate(pods):
+        cl = []
+        for cpu, mem in containers:
+            req = {}
+            if cpu is not None:
+                req["cpu"] = cpu
+            if mem is not None:
+                req["memory"] = mem
+            cl.append(_NS(resources=_NS(requests=req) if req or cpu is None else None))
+        pod = _NS(metadata=_NS(name=f"p{i}", namespace="default"),
+                  spec=_NS(containers=cl, node_selector=None, tolerations=None, priority=None))
+        ps = cs._convert_pod_to_spec(pod)
+        conv.append({"containers": [[c, m] for c, m in containers],
+                     "cpu_bits": f64_bits(ps.cpu_request), "mem_bits": f64_bits(ps.memory_request),
+                     "priority": ps.priority})
+    out["convert_pod_to_spec"] = conv
+    return out
+
+
+def gen_config1_trace(sched):
+    """BASELINE config 1 through the reference's own _schedule_pod."""
+    import yaml
+    docs = list(yaml.safe_load_all((REF_DIR / "ai-test-pods.yaml").read_text()))
+    api = FakeCoreV1([
+        dict(name="minikube", cpu="8", memory="16374576Ki", pods="110", n_running=8),
+        dict(name="minikube-m02", cpu="8", memory="16374576Ki", pods="110", n_running=2),
+        dict(name="minikube-m03", cpu="8", memory="16374576Ki", pods="110", n_running=2)])
+    sleeps = []
+    real_sleep = sched.time.sleep
+    sched.time.sleep = lambda s: sleeps.append(s)
+    sched.CONFIG.setdefault("fallback", {})["strategy"] = "resource_balanced"
+    try:
+        cm = sched.ContextManager.__new__(sched.ContextManager)
+        cm.v1 = api
+        llm = sched.HuggingFaceClient(sched.LLM_MODEL, "dummy", sched.LLM_ENDPOINT)
+
+        def boom(*a, **kw):
+            raise RuntimeError("offline: no HuggingFace endpoint")
+        llm.client.chat_completion = boom
+        il = sched.IntegrationLayer.__new__(sched.IntegrationLayer)
+        il.v1 = api
+        cs = sched.CustomScheduler.__new__(sched.CustomScheduler)
+        cs.context_manager, cs.prompt_engine = cm, sched.PromptEngine()
+        cs.llm_client, cs.integration_layer = llm, il
+        cs.running = True
+        cs.stats = {"total_scheduled": 0, "llm_decisions": 0, "fallback_decisions": 0,
+                    "failed_bindings": 0}
+        specs = []
+        for d in docs:
+            c = d["spec"]["containers"][0]
+            pod = _NS(metadata=_NS(name=d["metadata"]["name"], namespace=d["metadata"]["namespace"]),
+                      spec=_NS(containers=[_NS(resources=_NS(requests=dict(c["resources"]["requests"])))],
+                               node_selector=None, tolerations=None, priority=None))
+            ps = cs._convert_pod_to_spec(pod)
+            specs.append({"name": ps.name, "cpu_bits": f64_bits(ps.cpu_request),
+                          "mem_bits": f64_bits(ps.memory_request),
+                          "requests": dict(c["resources"]["requests"])})
+            asyncio.run(cs._schedule_pod(pod))
+    finally:
+        sched.time.sleep = real_sleep
+    table = cm.get_node_metrics()
+    return {"pods": specs, "binds": api.binds, "sleeps": sleeps, "stats": cs.stats,
+            "llm_stats": llm.get_stats(),
+            "final_table": [{"name": t.name, "pod_count": t.pod_count,
+                             "available_cpu_bits": f64_bits(t.available_cpu),
+                             "available_memory_bits": f64_bits(t.available_memory),
+                             "cu_bits": f64_bits(t.cpu_usage_percent)} for t in table]}
+
+
+def main():
+    sched = import_reference()
+    tap = ScoreTap(sched)
+    outputs = {
+        "kat_scores.json": gen_kat_scores(sched, tap),
+        "decisions.json": gen_decisions(sched, tap),
+        "greedy.json": gen_greedy(sched, tap),
+        "parsers.json": gen_parsers(sched),
+        "config1_trace.json": gen_config1_trace(sched),
+    }
+    for name, obj in outputs.items():
+        (OUT_DIR / name).write_text(json.dumps(obj, indent=1, sort_keys=True) + "\n")
+        print(f"wrote {name}: {(OUT_DIR / name).stat().st_size} bytes")
+
+
+if __name__ == "__main__":
+    main()
