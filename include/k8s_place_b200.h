@@ -1,0 +1,168 @@
+/*
+ * k8s_place_b200 -- C ABI of the B200-native fallback placement path.
+ *
+ * This is the drop-in boundary for ONE path of AshishGautamX/K8s-LLM-Scheduler: the
+ * non-LLM placement decision, reference `HuggingFaceClient._fallback_decision`
+ * (scheduler.py:521-559), fed by the node table of `ContextManager.get_node_metrics`
+ * (scheduler.py:121-170) and the pod rows of `CustomScheduler._convert_pod_to_spec`
+ * (scheduler.py:731-764).  The reference is pure Python and has no FFI; the binding a
+ * maintainer would add is a ctypes stub -- see INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no C++ or torch types; every call returns a kp_status
+ *     and never throws.  kp_last_error() gives a thread-local message for the last
+ *     non-OK status.
+ *   - "device" entry points take DEVICE pointers, are ordered on the given CUDA stream
+ *     (a cudaStream_t passed as void*, NULL = default stream), allocate nothing and
+ *     never synchronise: the caller owns every buffer including the workspace.
+ *   - "session" entry points take HOST pointers and own their device buffers (allocated
+ *     once in kp_session_create); they copy in, run the same kernels, copy out and
+ *     synchronise.  This is the form the reference-facing Python adapter binds.
+ *   - wire tables: int64 milli-CPU, int64 bytes, int64 pod counts,
+ *     fp64 usage percent, uint8 ready flag.  cores = milli/1000.0 and
+ *     GiB = bytes/1024/1024/1024 reproduce the floats of scheduler.py:172-187.
+ *   - results: int64 node index per pod (-1 = no node, the reference's
+ *     selected_node == ""), fp64 score of the chosen node (-1.0 = none, the reference's
+ *     best_score sentinel, scheduler.py:529).
+ *   - values must satisfy |x| < 2^53 (exact in fp64); n_nodes < 2^31 - 4096.
+ */
+#ifndef K8S_PLACE_B200_H
+#define K8S_PLACE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KP_ABI_VERSION 1
+
+/* status codes */
+#define KP_OK 0
+#define KP_ERR_INVALID_ARG 1   /* NULL pointer, negative size, bad enum */
+#define KP_ERR_WORKSPACE 2     /* workspace missing, misaligned or too small */
+#define KP_ERR_CUDA 3          /* a CUDA runtime call failed (see kp_last_error) */
+#define KP_ERR_NO_DEVICE 4     /* no usable sm_100 device */
+#define KP_ERR_CAPACITY 5      /* session created for fewer nodes / pods */
+
+/* Strategy ids: the values of config key fallback.strategy (scheduler.py:526,
+ * config.yaml:34-36).  Any id other than 0 or 1 takes the round_robin branch, exactly
+ * as any unknown string does in the reference (scheduler.py:544). */
+#define KP_STRATEGY_RESOURCE_BALANCED 0   /* scheduler.py:537-541 */
+#define KP_STRATEGY_LEAST_LOADED 1        /* scheduler.py:542-543 */
+#define KP_STRATEGY_ROUND_ROBIN 2         /* scheduler.py:544-545 (picks the MOST loaded node) */
+
+/* Filter modes.
+ * KP_FILTER_READY    -- what the reference does: node Ready==True only
+ *                       (scheduler.py:531-535); pod requests are not looked at.
+ * KP_FILTER_CAPACITY -- north-star extension: additionally pod_count < max_pods,
+ *                       cpu_req <= free_cpu and mem_req <= free_mem with
+ *                       free = available * (100 - usage%) / 100.0, the only capacity
+ *                       formula in the reference (scheduler.py:232-233). */
+#define KP_FILTER_READY 0
+#define KP_FILTER_CAPACITY 1
+
+/* Node table, structure of arrays, one entry per node in LIST ORDER (= tie-break order,
+ * scheduler.py:547).  Mirrors reference type NodeMetrics (scheduler.py:72-84). */
+typedef struct kp_node_table {
+    int64_t n_nodes;
+    const int64_t *alloc_cpu_milli;  /* allocatable cpu, milli-cores   (available_cpu, :139)    */
+    const int64_t *alloc_mem_bytes;  /* allocatable memory, bytes      (available_memory, :140) */
+    const int64_t *pod_count;        /* pods running on the node       (:147)                   */
+    const int64_t *max_pods;         /* allocatable pods               (:141)                   */
+    const uint8_t *ready;            /* 1 iff a condition Ready=="True" exists (:532-533)       */
+    const double *cpu_usage_pct;     /* cpu_usage_percent              (:150)                   */
+    const double *mem_usage_pct;     /* memory_usage_percent           (:151)                   */
+} kp_node_table;
+
+/* Pod table, one entry per pending pod in ARRIVAL ORDER.  Mirrors reference type PodSpec
+ * (scheduler.py:86-96); only the two request fields matter to this path. */
+typedef struct kp_pod_table {
+    int64_t n_pods;
+    const int64_t *req_cpu_milli;    /* cpu_request, milli-cores (:742-745)           */
+    const int64_t *req_mem_bytes;    /* memory_request, bytes    (:747-753)           */
+    const int64_t *strategy_ids;     /* optional per-pod strategy id, NULL = uniform  */
+} kp_pod_table;
+
+/* ---- library ------------------------------------------------------------------- */
+int kp_abi_version(void);
+const char *kp_status_string(int status);
+const char *kp_last_error(void);
+/* Number of SMs etc. of `device`; KP_ERR_NO_DEVICE unless compute capability is 10.x. */
+int kp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor);
+/* Number of kernels this library has launched in this process (for bench accounting). */
+int64_t kp_launch_count(void);
+/* Diagnostics for bench.py's roofline: when enabled, kp_snapshot_place records CUDA events
+ * on its stream around the node-plan kernels and around the placement kernel.
+ * kp_profile_last_ms waits for the last recorded call and returns both durations in ms.
+ * Process-global and not thread-safe; off by default (no events are recorded). */
+int kp_profile_enable(int enable);
+int kp_profile_last_ms(float *plan_ms, float *place_ms);
+
+/* ---- snapshot placement, device pointers ------------------------------------------
+ * Replaces: one `_fallback_decision` call per pod (scheduler.py:521-559) over the SAME
+ * node table -- P independent decisions.  Fused filter + score + first-best argmax; the
+ * P x N matrix is never materialised.
+ *
+ * `strategy` applies to every pod unless pods->strategy_ids is set.
+ * Workspace: kp_snapshot_workspace_bytes(n_nodes, n_pods, per_pod_strategy != 0) bytes,
+ * 256-byte aligned device memory; contents are scratch.
+ */
+size_t kp_snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, int per_pod_strategy);
+int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                      int filter_mode, int64_t *out_node_idx, double *out_score,
+                      void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---- greedy placement with commit, device pointers ---------------------------------
+ * Replaces: the sequential loop `_schedule_pod` -> `_fallback_decision` -> bind ->
+ * next `get_node_metrics()` (scheduler.py:690-729, :598, :144-151).  Pods are placed in
+ * arrival order; each placement does pod_count[chosen] += 1 and re-derives BOTH usage
+ * percents of that node as (pod_count / max_pods) * 50 (0 if max_pods == 0); allocatable
+ * never changes.  The input node table is not modified: the final state is
+ * written to out_pod_count / out_cpu_usage_pct / out_mem_usage_pct (each n_nodes long,
+ * may be NULL when not wanted).
+ */
+size_t kp_greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods);
+int kp_greedy_place(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                    int filter_mode, int64_t *out_node_idx, double *out_score,
+                    int64_t *out_pod_count, double *out_cpu_usage_pct,
+                    double *out_mem_usage_pct, void *workspace, size_t workspace_bytes,
+                    void *stream);
+
+/* ---- per-node derived values, device pointers --------------------------------------
+ * The hoisted per-node part of the path: score under `strategy` (scheduler.py:537-545),
+ * free cpu cores / free memory GiB (scheduler.py:232-233) and eligibility under
+ * `filter_mode` ignoring pod requests (1 = the node can win for some pod).  Any output
+ * may be NULL.  No workspace.
+ */
+int kp_node_scores(const kp_node_table *nodes, int strategy, int filter_mode,
+                   double *out_score, double *out_free_cpu, double *out_free_mem,
+                   uint8_t *out_eligible, void *stream);
+
+/* ---- session: host pointers, owns device memory ------------------------------------
+ * The reference-facing form: `nodes`, `pods` and the outputs are HOST memory (pinned
+ * host memory makes the copies asynchronous and faster, pageable memory works).  Each
+ * call copies the tables in, runs the device path above on the session's stream, copies
+ * the results out and waits for them.
+ */
+typedef struct kp_session kp_session;
+int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_session **out);
+void kp_session_destroy(kp_session *s);
+/* Copy + keep a node table on the device; later kp_session_snapshot/greedy calls with
+ * nodes == NULL reuse it (the per-pod loop of the reference re-reads the same cluster). */
+int kp_session_set_nodes(kp_session *s, const kp_node_table *nodes);
+int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_table *pods,
+                        int strategy, int filter_mode, int64_t *out_node_idx,
+                        double *out_score);
+int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_table *pods,
+                      int strategy, int filter_mode, int64_t *out_node_idx, double *out_score,
+                      int64_t *out_pod_count, double *out_cpu_usage_pct,
+                      double *out_mem_usage_pct);
+/* Bytes moved host->device and device->host by the last session call. */
+int kp_session_last_copy_bytes(const kp_session *s, int64_t *h2d, int64_t *d2h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* K8S_PLACE_B200_H */

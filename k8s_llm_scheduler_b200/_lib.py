@@ -1,0 +1,92 @@
+"""ctypes binding of include/k8s_place_b200.h.  There is NO fallback: if the CUDA library
+is missing, or a call fails, this raises -- the product never routes through a CPU path."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import POINTER, c_char_p, c_double, c_int, c_int64, c_size_t, c_uint8, c_void_p
+from pathlib import Path
+
+from .build import LIB_PATH
+
+KP_OK = 0
+STRATEGY_RESOURCE_BALANCED, STRATEGY_LEAST_LOADED, STRATEGY_ROUND_ROBIN = 0, 1, 2
+FILTER_READY, FILTER_CAPACITY = 0, 1
+
+_I64P, _F64P, _U8P = POINTER(c_int64), POINTER(c_double), POINTER(c_uint8)
+
+
+class KpNodeTable(ctypes.Structure):
+    _fields_ = [("n_nodes", c_int64), ("alloc_cpu_milli", c_void_p), ("alloc_mem_bytes", c_void_p),
+                ("pod_count", c_void_p), ("max_pods", c_void_p), ("ready", c_void_p),
+                ("cpu_usage_pct", c_void_p), ("mem_usage_pct", c_void_p)]
+
+
+class KpPodTable(ctypes.Structure):
+    _fields_ = [("n_pods", c_int64), ("req_cpu_milli", c_void_p), ("req_mem_bytes", c_void_p),
+                ("strategy_ids", c_void_p)]
+
+
+class PlacementError(RuntimeError):
+    def __init__(self, status: int, where: str, detail: str):
+        super().__init__(f"{where}: status {status} ({detail})")
+        self.status = status
+
+
+# every symbol include/k8s_place_b200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "kp_abi_version": (c_int, []),
+    "kp_status_string": (c_char_p, [c_int]),
+    "kp_last_error": (c_char_p, []),
+    "kp_device_info": (c_int, [c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "kp_launch_count": (c_int64, []),
+    "kp_profile_enable": (c_int, [c_int]),
+    "kp_profile_last_ms": (c_int, [POINTER(ctypes.c_float), POINTER(ctypes.c_float)]),
+    "kp_snapshot_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
+    "kp_snapshot_place": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
+                                  c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "kp_greedy_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "kp_greedy_place": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
+                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_void_p, c_size_t, c_void_p]),
+    "kp_node_scores": (c_int, [POINTER(KpNodeTable), c_int, c_int, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p]),
+    "kp_session_create": (c_int, [c_int, c_int64, c_int64, POINTER(c_void_p)]),
+    "kp_session_destroy": (None, [c_void_p]),
+    "kp_session_set_nodes": (c_int, [c_void_p, POINTER(KpNodeTable)]),
+    "kp_session_snapshot": (c_int, [c_void_p, POINTER(KpNodeTable), POINTER(KpPodTable), c_int,
+                                    c_int, c_void_p, c_void_p]),
+    "kp_session_greedy": (c_int, [c_void_p, POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "kp_session_last_copy_bytes": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),
+}
+
+_lib = None
+
+
+def load(path: Path | None = None) -> ctypes.CDLL:
+    """Load the CUDA library; raises if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise ImportError(
+            f"{p} not found: build it with `python -m k8s_llm_scheduler_b200.build` "
+            "(nvcc, sm_100a).  This package has no CPU fallback.")
+    lib = ctypes.CDLL(str(p))
+    for name, (restype, argtypes) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.kp_abi_version() != 1:
+        raise ImportError(f"{p}: ABI version {lib.kp_abi_version()} != 1")
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def check(status: int, where: str) -> None:
+    if status != KP_OK:
+        lib = load()
+        raise PlacementError(status, where,
+                             f"{lib.kp_status_string(status).decode()}: {lib.kp_last_error().decode()}")

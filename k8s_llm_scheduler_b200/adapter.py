@@ -1,0 +1,106 @@
+"""Drop-in for the reference's ``HuggingFaceClient._fallback_decision`` (scheduler.py:521-559).
+
+The reference has no plugin API: the boundary is that one private method plus the config
+key ``fallback.strategy`` (scheduler.py:526, config.yaml:34-36), read on every call.
+``FallbackPlacer.fallback_decision(node_metrics, reason)`` has the same arguments, the same
+return record and the same error behaviour (it never raises; "no result" is the in-band
+value ``selected_node == ""``, confidence 0.0), and ``install(scheduler_module)`` assigns
+it over the method without touching the reference file.
+
+The decision itself is computed on the GPU through the C ABI (kp_session_snapshot with
+one pod, KP_FILTER_READY -- the reference's own filter).  There is no CPU path here: if the
+CUDA library cannot be loaded the constructor raises.
+"""
+from __future__ import annotations
+
+import logging
+from typing import Any, Callable, List, Mapping, Optional, Sequence
+
+import numpy as np
+
+from ._lib import FILTER_CAPACITY, FILTER_READY, PlacementError
+from .placement import Session
+from .tables import NodeTable, PodTable, SchedulingDecision, strategy_id
+
+logger = logging.getLogger(__name__)
+
+
+class FallbackPlacer:
+    def __init__(self, config: Optional[Mapping[str, Any]] = None, device: int = 0,
+                 max_nodes: int = 65536, max_pods: int = 65536,
+                 decision_cls: Callable[..., Any] = SchedulingDecision):
+        # `config` is the reference's CONFIG mapping (a live reference, so a strategy flipped
+        # at run time is seen by the next call, like scheduler.py:526)
+        self.config = config if config is not None else {}
+        self.decision_cls = decision_cls
+        self.session = Session(device=device, max_nodes=max_nodes, max_pods=max_pods)
+        self._one_pod = PodTable.from_columns([0], [0])
+
+    def strategy(self) -> str:
+        return self.config.get("fallback", {}).get("strategy", "resource_balanced")
+
+    # ---- same shape as the reference method (minus self) ----
+    def fallback_decision(self, node_metrics: Sequence[Any], reason: str):
+        if not node_metrics:                                        # scheduler.py:523-524
+            return self.decision_cls("", 0.0, "No nodes available", True)
+        strategy = self.strategy()
+        try:
+            table = NodeTable.from_node_metrics(node_metrics, exact=False)   # Ready-only filter
+            idx, _ = self.session.snapshot(table, self._one_pod, strategy_id(strategy), FILTER_READY)
+            i = int(idx[0])
+        except PlacementError as e:        # never raise into the scheduling loop
+            logger.error("GPU fallback placement failed: %s", e)
+            i = -1
+        if i >= 0:                                                  # scheduler.py:551-557
+            return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
+                                     reasoning=f"Fallback ({strategy}): {reason}",
+                                     fallback_needed=True)
+        return self.decision_cls("", 0.0, f"Fallback failed: {reason}", True)   # :558-559
+
+    # ---- extension: the same decision with the capacity filter for a given pod ----
+    def fallback_decision_for_pod(self, node_metrics: Sequence[Any], pod_spec: Any, reason: str):
+        if not node_metrics:
+            return self.decision_cls("", 0.0, "No nodes available", True)
+        strategy = self.strategy()
+        try:
+            table = NodeTable.from_node_metrics(node_metrics)
+            pods = PodTable.from_pod_specs([pod_spec])
+            idx, _ = self.session.snapshot(table, pods, strategy_id(strategy), FILTER_CAPACITY)
+            i = int(idx[0])
+        except PlacementError as e:
+            logger.error("GPU fallback placement failed: %s", e)
+            i = -1
+        if i >= 0:
+            return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
+                                     reasoning=f"Fallback ({strategy}): {reason}",
+                                     fallback_needed=True)
+        return self.decision_cls("", 0.0, f"Fallback failed: {reason}", True)
+
+    # ---- batched forms over reference-style records ----
+    def place_snapshot(self, node_metrics: Sequence[Any], pod_specs: Sequence[Any],
+                       filter_mode: int = FILTER_CAPACITY) -> List[str]:
+        table = NodeTable.from_node_metrics(node_metrics)
+        pods = PodTable.from_pod_specs(pod_specs)
+        idx, _ = self.session.snapshot(table, pods, strategy_id(self.strategy()), filter_mode)
+        return [node_metrics[i].name if i >= 0 else "" for i in idx.tolist()]
+
+    def place_greedy(self, node_metrics: Sequence[Any], pod_specs: Sequence[Any],
+                     filter_mode: int = FILTER_CAPACITY) -> List[str]:
+        table = NodeTable.from_node_metrics(node_metrics)
+        pods = PodTable.from_pod_specs(pod_specs)
+        idx, *_ = self.session.greedy(table, pods, strategy_id(self.strategy()), filter_mode)
+        return [node_metrics[i].name if i >= 0 else "" for i in idx.tolist()]
+
+    def install(self, scheduler_module) -> None:
+        """Replace ``HuggingFaceClient._fallback_decision`` of an imported reference module."""
+        self.config = scheduler_module.CONFIG
+        self.decision_cls = scheduler_module.SchedulingDecision
+        placer = self
+
+        def _fallback_decision(_self, node_metrics, reason):
+            return placer.fallback_decision(node_metrics, reason)
+
+        scheduler_module.HuggingFaceClient._fallback_decision = _fallback_decision
+
+    def close(self):
+        self.session.close()

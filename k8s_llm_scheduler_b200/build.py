@@ -1,0 +1,61 @@
+"""Build recipe for libk8s_place_b200.so (explicit nvcc, in-tree, sm_100a only).
+
+The library is built next to this file so that it travels with the source tree; a JIT
+cache under ~/.cache would not.  Flags: -fmad=false keeps nvcc from contracting a*b+c
+(the kernels also use explicit round-to-nearest intrinsics), -lineinfo makes ncu's source
+page map to our code.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+from pathlib import Path
+
+PKG_DIR = Path(__file__).resolve().parent
+CSRC = PKG_DIR / "csrc"
+LIB_NAME = "libk8s_place_b200.so"
+LIB_PATH = PKG_DIR / LIB_NAME
+SOURCES = ["kp_api.cu", "kp_snapshot.cu", "kp_greedy.cu"]
+NVCC_FLAGS = [
+    "-shared", "-Xcompiler", "-fPIC", "-O3", "-std=c++17",
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-lineinfo", "-fmad=false",
+]
+
+
+def find_nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and Path(cand).exists():
+            return cand
+    raise RuntimeError("nvcc not found (set NVCC=/path/to/nvcc)")
+
+
+def _stale() -> bool:
+    if not LIB_PATH.exists():
+        return True
+    built = LIB_PATH.stat().st_mtime
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + \
+        [PKG_DIR.parent / "include" / "k8s_place_b200.h"]
+    return any(d.stat().st_mtime > built for d in deps)
+
+
+def build_library(force: bool = False, verbose: bool = False) -> Path:
+    """Compile the CUDA library if it is missing or older than its sources."""
+    if not force and not _stale():
+        return LIB_PATH
+    cmd = [find_nvcc(), *NVCC_FLAGS, "-o", str(LIB_PATH), *[str(CSRC / s) for s in SOURCES]]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+        print(" ".join(cmd))
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+if __name__ == "__main__":
+    print(build_library(force=True, verbose=True))

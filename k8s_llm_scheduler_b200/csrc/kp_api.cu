@@ -1,0 +1,450 @@
+// C ABI of the placement library (declared in include/k8s_place_b200.h).
+// Validation, error strings, device queries and the host-pointer "session" that owns its
+// device buffers.  No exceptions cross this boundary; every entry point returns a status.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "kp_common.cuh"
+
+namespace kp {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return KP_ERR_CUDA;
+}
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int sm_count_cached()
+{
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+            v = 148;
+        cached[dev] = v;
+    }
+    return cached[dev];
+}
+
+ProfileEvents &profile_events()
+{
+    static ProfileEvents pe{false, false, nullptr, nullptr, nullptr};
+    return pe;
+}
+
+static int check_tables(const kp_node_table *nodes, const kp_pod_table *pods)
+{
+    if (!nodes || !pods) { set_error("nodes / pods table pointer is NULL"); return KP_ERR_INVALID_ARG; }
+    if (nodes->n_nodes < 0 || pods->n_pods < 0) { set_error("negative table size"); return KP_ERR_INVALID_ARG; }
+    if (nodes->n_nodes >= (int64_t)0x7fffffff - 4096) { set_error("n_nodes too large"); return KP_ERR_INVALID_ARG; }
+    if (nodes->n_nodes > 0 &&
+        (!nodes->alloc_cpu_milli || !nodes->alloc_mem_bytes || !nodes->pod_count || !nodes->max_pods ||
+         !nodes->ready || !nodes->cpu_usage_pct || !nodes->mem_usage_pct)) {
+        set_error("node table has a NULL column");
+        return KP_ERR_INVALID_ARG;
+    }
+    if (pods->n_pods > 0 && (!pods->req_cpu_milli || !pods->req_mem_bytes)) {
+        set_error("pod table has a NULL column");
+        return KP_ERR_INVALID_ARG;
+    }
+    return KP_OK;
+}
+
+static int check_filter(int filter_mode)
+{
+    if (filter_mode != KP_FILTER_READY && filter_mode != KP_FILTER_CAPACITY) {
+        set_error("filter_mode must be KP_FILTER_READY (0) or KP_FILTER_CAPACITY (1), got %d", filter_mode);
+        return KP_ERR_INVALID_ARG;
+    }
+    return KP_OK;
+}
+
+}  // namespace kp
+
+using namespace kp;
+
+// ---------------------------------------------------------------------------------------
+// session
+// ---------------------------------------------------------------------------------------
+struct kp_session {
+    int device = 0;
+    int64_t max_nodes = 0, max_pods = 0;
+    cudaStream_t stream = nullptr;
+    // device buffers
+    unsigned char *d_nodes = nullptr;   // 4 x i64 + 2 x f64 columns + ready bytes
+    unsigned char *d_pods = nullptr;    // 3 x i64 columns
+    unsigned char *d_out = nullptr;     // idx i64 | score f64
+    unsigned char *d_state = nullptr;   // greedy: pc i64 | cu f64 | mu f64
+    void *d_ws = nullptr;
+    size_t ws_bytes = 0;
+    int64_t resident_nodes = -1;        // >= 0: a node table is resident
+    int64_t h2d = 0, d2h = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+kp_node_table session_node_view(const kp_session *s, int64_t n)
+{
+    const size_t col = align_up(sizeof(int64_t) * (size_t)s->max_nodes);
+    kp_node_table t{};
+    t.n_nodes = n;
+    t.alloc_cpu_milli = reinterpret_cast<const int64_t *>(s->d_nodes + 0 * col);
+    t.alloc_mem_bytes = reinterpret_cast<const int64_t *>(s->d_nodes + 1 * col);
+    t.pod_count = reinterpret_cast<const int64_t *>(s->d_nodes + 2 * col);
+    t.max_pods = reinterpret_cast<const int64_t *>(s->d_nodes + 3 * col);
+    t.cpu_usage_pct = reinterpret_cast<const double *>(s->d_nodes + 4 * col);
+    t.mem_usage_pct = reinterpret_cast<const double *>(s->d_nodes + 5 * col);
+    t.ready = reinterpret_cast<const uint8_t *>(s->d_nodes + 6 * col);
+    return t;
+}
+
+int upload_nodes(kp_session *s, const kp_node_table *nodes)
+{
+    const int64_t n = nodes->n_nodes;
+    if (n > s->max_nodes) {
+        set_error("session holds at most %lld nodes, got %lld", (long long)s->max_nodes, (long long)n);
+        return KP_ERR_CAPACITY;
+    }
+    const kp_node_table d = session_node_view(s, n);
+    const size_t b8 = sizeof(int64_t) * (size_t)n;
+    if (n > 0) {
+        KP_CUDA(cudaMemcpyAsync((void *)d.alloc_cpu_milli, nodes->alloc_cpu_milli, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.alloc_mem_bytes, nodes->alloc_mem_bytes, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.pod_count, nodes->pod_count, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.max_pods, nodes->max_pods, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.cpu_usage_pct, nodes->cpu_usage_pct, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.mem_usage_pct, nodes->mem_usage_pct, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)d.ready, nodes->ready, (size_t)n, cudaMemcpyHostToDevice, s->stream));
+    }
+    s->h2d += 6 * (int64_t)b8 + n;
+    s->resident_nodes = n;
+    return KP_OK;
+}
+
+int upload_pods(kp_session *s, const kp_pod_table *pods, kp_pod_table *dview)
+{
+    const int64_t p = pods->n_pods;
+    if (p > s->max_pods) {
+        set_error("session holds at most %lld pods, got %lld", (long long)s->max_pods, (long long)p);
+        return KP_ERR_CAPACITY;
+    }
+    const size_t col = align_up(sizeof(int64_t) * (size_t)s->max_pods);
+    const size_t b8 = sizeof(int64_t) * (size_t)p;
+    dview->n_pods = p;
+    dview->req_cpu_milli = reinterpret_cast<const int64_t *>(s->d_pods);
+    dview->req_mem_bytes = reinterpret_cast<const int64_t *>(s->d_pods + col);
+    dview->strategy_ids = pods->strategy_ids ? reinterpret_cast<const int64_t *>(s->d_pods + 2 * col) : nullptr;
+    if (p > 0) {
+        KP_CUDA(cudaMemcpyAsync((void *)dview->req_cpu_milli, pods->req_cpu_milli, b8, cudaMemcpyHostToDevice, s->stream));
+        KP_CUDA(cudaMemcpyAsync((void *)dview->req_mem_bytes, pods->req_mem_bytes, b8, cudaMemcpyHostToDevice, s->stream));
+        s->h2d += 2 * (int64_t)b8;
+        if (pods->strategy_ids) {
+            KP_CUDA(cudaMemcpyAsync((void *)dview->strategy_ids, pods->strategy_ids, b8, cudaMemcpyHostToDevice, s->stream));
+            s->h2d += (int64_t)b8;
+        }
+    }
+    return KP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kp_abi_version(void) { return KP_ABI_VERSION; }
+
+const char *kp_status_string(int status)
+{
+    switch (status) {
+        case KP_OK: return "ok";
+        case KP_ERR_INVALID_ARG: return "invalid argument";
+        case KP_ERR_WORKSPACE: return "workspace missing, misaligned or too small";
+        case KP_ERR_CUDA: return "CUDA runtime error";
+        case KP_ERR_NO_DEVICE: return "no usable sm_100 device";
+        case KP_ERR_CAPACITY: return "session capacity exceeded";
+        default: return "unknown status";
+    }
+}
+
+const char *kp_last_error(void) { return g_err; }
+
+int64_t kp_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int kp_profile_enable(int enable)
+{
+    ProfileEvents &pe = profile_events();
+    if (enable && !pe.e0) {
+        KP_CUDA(cudaEventCreate(&pe.e0));
+        KP_CUDA(cudaEventCreate(&pe.e1));
+        KP_CUDA(cudaEventCreate(&pe.e2));
+    }
+    pe.enabled = enable != 0;
+    pe.valid = false;
+    return KP_OK;
+}
+
+int kp_profile_last_ms(float *plan_ms, float *place_ms)
+{
+    ProfileEvents &pe = profile_events();
+    if (!pe.enabled || !pe.valid) { set_error("no profiled kp_snapshot_place call recorded"); return KP_ERR_INVALID_ARG; }
+    KP_CUDA(cudaEventSynchronize(pe.e2));
+    float a = 0.f, b = 0.f;
+    KP_CUDA(cudaEventElapsedTime(&a, pe.e0, pe.e1));
+    KP_CUDA(cudaEventElapsedTime(&b, pe.e1, pe.e2));
+    if (plan_ms) *plan_ms = a;
+    if (place_ms) *place_ms = b;
+    return KP_OK;
+}
+
+int kp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) {
+        set_error("CUDA device %d not available (%d devices visible)", device, count);
+        cudaGetLastError();
+        return KP_ERR_NO_DEVICE;
+    }
+    int sms = 0, maj = 0, min = 0;
+    KP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    KP_CUDA(cudaDeviceGetAttribute(&maj, cudaDevAttrComputeCapabilityMajor, device));
+    KP_CUDA(cudaDeviceGetAttribute(&min, cudaDevAttrComputeCapabilityMinor, device));
+    if (sm_count) *sm_count = sms;
+    if (cc_major) *cc_major = maj;
+    if (cc_minor) *cc_minor = min;
+    if (maj != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, maj, min);
+        return KP_ERR_NO_DEVICE;
+    }
+    return KP_OK;
+}
+
+size_t kp_snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, int per_pod_strategy)
+{
+    return snapshot_workspace_bytes(n_nodes, n_pods, per_pod_strategy != 0);
+}
+
+int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                      int filter_mode, int64_t *out_node_idx, double *out_score, void *workspace,
+                      size_t workspace_bytes, void *stream)
+{
+    int st = check_tables(nodes, pods);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) {
+        set_error("output pointer is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    return snapshot_place_device(*nodes, *pods, strategy, filter_mode, out_node_idx, out_score,
+                                 workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+size_t kp_greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods)
+{
+    return greedy_workspace_bytes(n_nodes, n_pods);
+}
+
+int kp_greedy_place(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                    int filter_mode, int64_t *out_node_idx, double *out_score,
+                    int64_t *out_pod_count, double *out_cpu_usage_pct, double *out_mem_usage_pct,
+                    void *workspace, size_t workspace_bytes, void *stream)
+{
+    int st = check_tables(nodes, pods);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) {
+        set_error("output pointer is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    return greedy_place_device(*nodes, *pods, strategy, filter_mode, out_node_idx, out_score,
+                               out_pod_count, out_cpu_usage_pct, out_mem_usage_pct, workspace,
+                               workspace_bytes, (cudaStream_t)stream);
+}
+
+int kp_node_scores(const kp_node_table *nodes, int strategy, int filter_mode, double *out_score,
+                   double *out_free_cpu, double *out_free_mem, uint8_t *out_eligible, void *stream)
+{
+    kp_pod_table none{};
+    int st = check_tables(nodes, &none);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    return node_scores_device(*nodes, strategy, filter_mode, out_score, out_free_cpu, out_free_mem,
+                              out_eligible, (cudaStream_t)stream);
+}
+
+int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_session **out)
+{
+    if (!out || max_nodes < 0 || max_pods < 0) { set_error("bad session arguments"); return KP_ERR_INVALID_ARG; }
+    *out = nullptr;
+    int st = kp_device_info(device, nullptr, nullptr, nullptr);
+    if (st != KP_OK) return st;
+    DeviceGuard guard(device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice");
+    kp_session *s = new (std::nothrow) kp_session();
+    if (!s) { set_error("out of host memory"); return KP_ERR_INVALID_ARG; }
+    s->device = device;
+    s->max_nodes = max_nodes;
+    s->max_pods = max_pods;
+    const size_t ncol = align_up(sizeof(int64_t) * (size_t)max_nodes);
+    const size_t pcol = align_up(sizeof(int64_t) * (size_t)max_pods);
+    const size_t ws_snap = snapshot_workspace_bytes(max_nodes, max_pods, true);
+    const size_t ws_greedy = greedy_workspace_bytes(max_nodes, max_pods);
+    s->ws_bytes = ws_snap > ws_greedy ? ws_snap : ws_greedy;
+    cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_nodes, 7 * ncol + kAlign);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_pods, 3 * pcol + kAlign);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_out, 2 * pcol + kAlign);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_state, 3 * ncol + kAlign);
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_ws, s->ws_bytes + kAlign);
+    if (e != cudaSuccess) {
+        kp_session_destroy(s);
+        return cuda_fail(e, "kp_session_create allocation");
+    }
+    *out = s;
+    return KP_OK;
+}
+
+void kp_session_destroy(kp_session *s)
+{
+    if (!s) return;
+    DeviceGuard guard(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    cudaFree(s->d_nodes);
+    cudaFree(s->d_pods);
+    cudaFree(s->d_out);
+    cudaFree(s->d_state);
+    cudaFree(s->d_ws);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int kp_session_set_nodes(kp_session *s, const kp_node_table *nodes)
+{
+    if (!s) { set_error("session is NULL"); return KP_ERR_INVALID_ARG; }
+    kp_pod_table none{};
+    int st = check_tables(nodes, &none);
+    if (st != KP_OK) return st;
+    DeviceGuard guard(s->device);
+    s->h2d = s->d2h = 0;
+    if ((st = upload_nodes(s, nodes)) != KP_OK) return st;
+    KP_CUDA(cudaStreamSynchronize(s->stream));
+    return KP_OK;
+}
+
+int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_table *pods,
+                        int strategy, int filter_mode, int64_t *out_node_idx, double *out_score)
+{
+    if (!s || !pods) { set_error("session / pods is NULL"); return KP_ERR_INVALID_ARG; }
+    int st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    DeviceGuard guard(s->device);
+    s->h2d = s->d2h = 0;
+    if (nodes) {
+        if ((st = check_tables(nodes, pods)) != KP_OK) return st;
+        if ((st = upload_nodes(s, nodes)) != KP_OK) return st;
+    } else if (s->resident_nodes < 0) {
+        set_error("no resident node table: pass nodes or call kp_session_set_nodes first");
+        return KP_ERR_INVALID_ARG;
+    }
+    const kp_node_table dn = session_node_view(s, s->resident_nodes);
+    if ((st = check_tables(&dn, pods)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return KP_ERR_INVALID_ARG; }
+    kp_pod_table dp{};
+    if ((st = upload_pods(s, pods, &dp)) != KP_OK) return st;
+    const size_t pcol = align_up(sizeof(int64_t) * (size_t)s->max_pods);
+    int64_t *d_idx = reinterpret_cast<int64_t *>(s->d_out);
+    double *d_score = reinterpret_cast<double *>(s->d_out + pcol);
+    st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream);
+    if (st != KP_OK) return st;
+    const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
+    if (b8) {
+        KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
+        KP_CUDA(cudaMemcpyAsync(out_score, d_score, b8, cudaMemcpyDeviceToHost, s->stream));
+        s->d2h += 2 * (int64_t)b8;
+    }
+    KP_CUDA(cudaStreamSynchronize(s->stream));
+    return KP_OK;
+}
+
+int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_table *pods,
+                      int strategy, int filter_mode, int64_t *out_node_idx, double *out_score,
+                      int64_t *out_pod_count, double *out_cpu_usage_pct, double *out_mem_usage_pct)
+{
+    if (!s || !pods) { set_error("session / pods is NULL"); return KP_ERR_INVALID_ARG; }
+    int st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    DeviceGuard guard(s->device);
+    s->h2d = s->d2h = 0;
+    if (nodes) {
+        if ((st = check_tables(nodes, pods)) != KP_OK) return st;
+        if ((st = upload_nodes(s, nodes)) != KP_OK) return st;
+    } else if (s->resident_nodes < 0) {
+        set_error("no resident node table: pass nodes or call kp_session_set_nodes first");
+        return KP_ERR_INVALID_ARG;
+    }
+    const int64_t n = s->resident_nodes;
+    const kp_node_table dn = session_node_view(s, n);
+    if ((st = check_tables(&dn, pods)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return KP_ERR_INVALID_ARG; }
+    kp_pod_table dp{};
+    if ((st = upload_pods(s, pods, &dp)) != KP_OK) return st;
+    const size_t pcol = align_up(sizeof(int64_t) * (size_t)s->max_pods);
+    const size_t ncol = align_up(sizeof(int64_t) * (size_t)s->max_nodes);
+    int64_t *d_idx = reinterpret_cast<int64_t *>(s->d_out);
+    double *d_score = reinterpret_cast<double *>(s->d_out + pcol);
+    int64_t *d_pc = reinterpret_cast<int64_t *>(s->d_state);
+    double *d_cu = reinterpret_cast<double *>(s->d_state + ncol);
+    double *d_mu = reinterpret_cast<double *>(s->d_state + 2 * ncol);
+    st = greedy_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, d_pc, d_cu, d_mu, s->d_ws,
+                             s->ws_bytes, s->stream);
+    if (st != KP_OK) return st;
+    const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
+    const size_t n8 = sizeof(int64_t) * (size_t)n;
+    if (b8) {
+        KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
+        KP_CUDA(cudaMemcpyAsync(out_score, d_score, b8, cudaMemcpyDeviceToHost, s->stream));
+        s->d2h += 2 * (int64_t)b8;
+    }
+    if (n8 && out_pod_count) { KP_CUDA(cudaMemcpyAsync(out_pod_count, d_pc, n8, cudaMemcpyDeviceToHost, s->stream)); s->d2h += n8; }
+    if (n8 && out_cpu_usage_pct) { KP_CUDA(cudaMemcpyAsync(out_cpu_usage_pct, d_cu, n8, cudaMemcpyDeviceToHost, s->stream)); s->d2h += n8; }
+    if (n8 && out_mem_usage_pct) { KP_CUDA(cudaMemcpyAsync(out_mem_usage_pct, d_mu, n8, cudaMemcpyDeviceToHost, s->stream)); s->d2h += n8; }
+    KP_CUDA(cudaStreamSynchronize(s->stream));
+    return KP_OK;
+}
+
+int kp_session_last_copy_bytes(const kp_session *s, int64_t *h2d, int64_t *d2h)
+{
+    if (!s) { set_error("session is NULL"); return KP_ERR_INVALID_ARG; }
+    if (h2d) *h2d = s->h2d;
+    if (d2h) *d2h = s->d2h;
+    return KP_OK;
+}
+
+}  // extern "C"

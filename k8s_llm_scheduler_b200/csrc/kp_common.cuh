@@ -1,0 +1,201 @@
+// Shared device/host helpers for the placement kernels (sm_100a only).
+//
+// Exact-arithmetic contract: every floating-point step is written with the IEEE
+// round-to-nearest intrinsics (__dadd_rn, __dmul_rn, __ddiv_rn, ...) in the reference's
+// own operation order, so that nvcc can never contract a*b+c into an FMA (a contraction
+// changes resource_balanced score bits).  The library is additionally
+// compiled with -fmad=false.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/k8s_place_b200.h"
+
+namespace kp {
+
+// ---------------------------------------------------------------------------------------
+// exact fp64 node arithmetic
+// ---------------------------------------------------------------------------------------
+
+// scheduler.py:150-151   (pod_count / max_pods) * 50 if max_pods > 0 else 0
+__device__ __forceinline__ double usage_a3(long long pc, long long mp)
+{
+    if (mp > 0) return __dmul_rn(__ddiv_rn((double)pc, (double)mp), 50.0);
+    return 0.0;
+}
+
+// scheduler.py:537-541   left-associated: ((cpu*0.35) + (mem*0.35)) + (pod*0.30)
+__device__ __forceinline__ double score_resource_balanced(double cu, double mu, long long pc,
+                                                          long long mp)
+{
+    const double cpu_score = __ddiv_rn(__dsub_rn(100.0, cu), 100.0);
+    const double mem_score = __ddiv_rn(__dsub_rn(100.0, mu), 100.0);
+    const double pod_score = mp > 0 ? __ddiv_rn((double)(mp - pc), (double)mp) : 0.0;
+    const double a = __dmul_rn(cpu_score, 0.35);
+    const double b = __dmul_rn(mem_score, 0.35);
+    const double c = __dmul_rn(pod_score, 0.30);
+    return __dadd_rn(__dadd_rn(a, b), c);
+}
+
+// scheduler.py:542-543   (100 - cpu%) + (100 - mem%)
+__device__ __forceinline__ double score_least_loaded(double cu, double mu)
+{
+    return __dadd_rn(__dsub_rn(100.0, cu), __dsub_rn(100.0, mu));
+}
+
+// scheduler.py:232-233   available * (100 - usage%) / 100.0, with available rebuilt from
+// the integer wire format: cores = milli / 1000.0 (scheduler.py:174-175),
+// GiB = bytes / 1024 / 1024 / 1024 (scheduler.py:187).
+__device__ __forceinline__ double free_cpu_cores(long long alloc_milli, double cu)
+{
+    const double avail = __ddiv_rn((double)alloc_milli, 1000.0);
+    return __ddiv_rn(__dmul_rn(avail, __dsub_rn(100.0, cu)), 100.0);
+}
+__device__ __forceinline__ double free_mem_gib(long long alloc_bytes, double mu)
+{
+    const double avail =
+        __ddiv_rn(__ddiv_rn(__ddiv_rn((double)alloc_bytes, 1024.0), 1024.0), 1024.0);
+    return __ddiv_rn(__dmul_rn(avail, __dsub_rn(100.0, mu)), 100.0);
+}
+// pod request in the reference's units (scheduler.py:742-753, single quantity)
+__device__ __forceinline__ double req_cores(long long milli)
+{
+    return __ddiv_rn((double)milli, 1000.0);
+}
+__device__ __forceinline__ double req_gib(long long bytes)
+{
+    return __ddiv_rn(__ddiv_rn(__ddiv_rn((double)bytes, 1024.0), 1024.0), 1024.0);
+}
+
+__host__ __device__ __forceinline__ int canon_strategy(long long sid)
+{
+    return sid == 0 ? 0 : (sid == 1 ? 1 : 2);   // scheduler.py:537/542/544
+}
+
+// ---------------------------------------------------------------------------------------
+// order-preserving 64-bit keys: a < b (as doubles / int64) <=> key(a) < key(b) (unsigned)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long f64_order_key(double x)
+{
+    x = __dadd_rn(x, 0.0);                                   // -0.0 -> +0.0 (they compare equal)
+    unsigned long long b = (unsigned long long)__double_as_longlong(x);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ unsigned long long i64_order_key(long long x)
+{
+    return (unsigned long long)x ^ 0x8000000000000000ull;
+}
+
+// Score of node under strategy s and whether it can ever beat the reference's -1 sentinel
+// with a strict '>' (scheduler.py:529,547).  NaN never wins (NaN > x is false).
+struct NodeScore {
+    double score;             // fp64 value reported to the caller
+    unsigned long long key;   // order-preserving, larger = better; 0 = cannot win
+};
+__device__ __forceinline__ NodeScore node_score(int s, double cu, double mu, long long pc,
+                                                long long mp)
+{
+    NodeScore r;
+    if (s == 2) {                                   // scheduler.py:544-545: int compare
+        r.score = (double)pc;
+        r.key = pc > -1 ? i64_order_key(pc) : 0ull;
+    } else {
+        r.score = s == 0 ? score_resource_balanced(cu, mu, pc, mp) : score_least_loaded(cu, mu);
+        r.key = r.score > -1.0 ? f64_order_key(r.score) : 0ull;
+    }
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------
+// small PTX wrappers: mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "KP_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra KP_DONE_%=;\n"
+        "bra KP_WAIT_%=;\n"
+        "KP_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy; bytes must be a multiple of 16, both addresses 16-B aligned
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes,
+                                          uint64_t *bar)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---------------------------------------------------------------------------------------
+// host-side helpers
+// ---------------------------------------------------------------------------------------
+constexpr int kMaxStrategies = 3;
+constexpr int kTileNodes = 4096;            // nodes per shared-memory tile of the snapshot kernel
+constexpr size_t kAlign = 256;
+
+inline size_t align_up(size_t x, size_t a = kAlign) { return (x + a - 1) / a * a; }
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);   // records message, returns KP_ERR_CUDA
+void count_launch(int n = 1);
+
+#define KP_CUDA(call)                                                     \
+    do {                                                                  \
+        cudaError_t e__ = (call);                                         \
+        if (e__ != cudaSuccess) return ::kp::cuda_fail(e__, #call);       \
+    } while (0)
+
+#define KP_LAUNCH_CHECK(name)                                             \
+    do {                                                                  \
+        ::kp::count_launch();                                             \
+        cudaError_t e__ = cudaGetLastError();                             \
+        if (e__ != cudaSuccess) return ::kp::cuda_fail(e__, name);        \
+    } while (0)
+
+// internal entry points (one per .cu file)
+int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
+                          int filter_mode, int64_t *out_idx, double *out_score, void *ws,
+                          size_t ws_bytes, cudaStream_t stream);
+size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod);
+int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
+                        int filter_mode, int64_t *out_idx, double *out_score,
+                        int64_t *out_pod_count, double *out_cu, double *out_mu, void *ws,
+                        size_t ws_bytes, cudaStream_t stream);
+size_t greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods);
+int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode,
+                       double *out_score, double *out_free_cpu, double *out_free_mem,
+                       uint8_t *out_eligible, cudaStream_t stream);
+int sm_count_cached();
+// diagnostics (kp_profile_enable): events around the node plan and the placement kernel
+struct ProfileEvents { bool enabled; bool valid; cudaEvent_t e0, e1, e2; };
+ProfileEvents &profile_events();
+
+}  // namespace kp

@@ -1,0 +1,276 @@
+"""Placement ops over CUDA tensors, and the host-buffer session -- thin callers of the C ABI.
+
+``snapshot_place`` / ``greedy_place`` / ``node_scores`` take int64 / float64 CUDA tensors
+(the PyTorch-facing form named by the north star) and launch on torch's current stream.
+``Session`` takes host numpy arrays (or pinned torch tensors) and is what the
+reference-facing adapter uses.  PyTorch is plumbing here: device memory and streams.
+Nothing in this module computes a placement on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import byref, c_int64, c_void_p
+from typing import Dict, Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FILTER_CAPACITY, FILTER_READY, KpNodeTable, KpPodTable, check
+from .tables import NODE_COLUMNS, NodeTable, PodTable
+
+_NODE_DTYPES = {"alloc_cpu_milli": torch.int64, "alloc_mem_bytes": torch.int64,
+                "pod_count": torch.int64, "max_pods": torch.int64, "ready": torch.uint8,
+                "cpu_usage_pct": torch.float64, "mem_usage_pct": torch.float64}
+
+
+def _dev_col(t: torch.Tensor, name: str, dtype: torch.dtype, device: torch.device, n: int):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f"{name}: expected a CUDA tensor")
+    if t.device != device:
+        raise ValueError(f"{name}: on {t.device}, expected {device}")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: dtype {t.dtype}, expected {dtype}")
+    if t.dim() != 1 or t.numel() != n:
+        raise ValueError(f"{name}: shape {tuple(t.shape)}, expected ({n},)")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: must be contiguous")
+    return t.data_ptr()
+
+
+def nodes_to_device(table: Union[NodeTable, Dict[str, np.ndarray]], device) -> Dict[str, torch.Tensor]:
+    cols = table.columns() if isinstance(table, NodeTable) else table
+    dev = torch.device(device)
+    return {k: torch.as_tensor(np.ascontiguousarray(cols[k])).to(_NODE_DTYPES[k]).to(dev)
+            for k in NODE_COLUMNS}
+
+
+def _node_struct(nodes: Dict[str, torch.Tensor]) -> Tuple[KpNodeTable, torch.device, int]:
+    pc = nodes["pod_count"]
+    device, n = pc.device, pc.numel()
+    st = KpNodeTable()
+    st.n_nodes = n
+    for k in NODE_COLUMNS:
+        setattr(st, k, _dev_col(nodes[k], k, _NODE_DTYPES[k], device, n))
+    return st, device, n
+
+
+def _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device):
+    p = req_cpu_milli.numel()
+    st = KpPodTable()
+    st.n_pods = p
+    st.req_cpu_milli = _dev_col(req_cpu_milli, "req_cpu_milli", torch.int64, device, p)
+    st.req_mem_bytes = _dev_col(req_mem_bytes, "req_mem_bytes", torch.int64, device, p)
+    if isinstance(strategy, torch.Tensor):
+        st.strategy_ids = _dev_col(strategy, "strategy_ids", torch.int64, device, p)
+        return st, p, 0, True
+    st.strategy_ids = None
+    return st, p, int(strategy), False
+
+
+def _workspace(nbytes: int, device, workspace: Optional[torch.Tensor]) -> torch.Tensor:
+    if workspace is None:
+        return torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+    if workspace.device != device or workspace.dtype != torch.uint8 or workspace.numel() < nbytes:
+        raise ValueError(f"workspace must be a uint8 tensor on {device} with >= {nbytes} bytes")
+    return workspace
+
+
+def snapshot_workspace_bytes(n_nodes: int, n_pods: int, per_pod_strategy: bool) -> int:
+    return int(_lib.load().kp_snapshot_workspace_bytes(n_nodes, n_pods, int(per_pod_strategy)))
+
+
+def greedy_workspace_bytes(n_nodes: int, n_pods: int) -> int:
+    return int(_lib.load().kp_greedy_workspace_bytes(n_nodes, n_pods))
+
+
+def snapshot_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
+                   req_mem_bytes: torch.Tensor, strategy: Union[int, torch.Tensor] = 0,
+                   filter_mode: int = FILTER_CAPACITY, workspace: Optional[torch.Tensor] = None,
+                   out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+    """P independent fallback decisions (scheduler.py:521-559) against one node table.
+
+    Returns (node_idx int64[P], score float64[P]); idx -1 / score -1.0 = no node.
+    """
+    lib = _lib.load()
+    nst, device, n = _node_struct(nodes)
+    pst, p, strat, per_pod = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
+    if out is None:
+        out_idx = torch.empty(p, dtype=torch.int64, device=device)
+        out_score = torch.empty(p, dtype=torch.float64, device=device)
+    else:
+        out_idx, out_score = out
+        _dev_col(out_idx, "out_idx", torch.int64, device, p)
+        _dev_col(out_score, "out_score", torch.float64, device, p)
+    ws = _workspace(snapshot_workspace_bytes(n, p, per_pod), device, workspace)
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        check(lib.kp_snapshot_place(byref(nst), byref(pst), strat, int(filter_mode),
+                                    out_idx.data_ptr(), out_score.data_ptr(), ws.data_ptr(),
+                                    ws.numel(), c_void_p(stream)), "kp_snapshot_place")
+    return out_idx, out_score
+
+
+def greedy_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
+                 req_mem_bytes: torch.Tensor, strategy: Union[int, torch.Tensor] = 0,
+                 filter_mode: int = FILTER_CAPACITY, workspace: Optional[torch.Tensor] = None):
+    """Pods in arrival order with commit (scheduler.py:690-729, :144-151).
+
+    Returns (node_idx, score, final_pod_count, final_cpu_usage_pct, final_mem_usage_pct).
+    The input node tensors are not modified.
+    """
+    lib = _lib.load()
+    nst, device, n = _node_struct(nodes)
+    pst, p, strat, _ = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
+    out_idx = torch.empty(p, dtype=torch.int64, device=device)
+    out_score = torch.empty(p, dtype=torch.float64, device=device)
+    out_pc = torch.empty(n, dtype=torch.int64, device=device)
+    out_cu = torch.empty(n, dtype=torch.float64, device=device)
+    out_mu = torch.empty(n, dtype=torch.float64, device=device)
+    ws = _workspace(greedy_workspace_bytes(n, p), device, workspace)
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        check(lib.kp_greedy_place(byref(nst), byref(pst), strat, int(filter_mode),
+                                  out_idx.data_ptr(), out_score.data_ptr(), out_pc.data_ptr(),
+                                  out_cu.data_ptr(), out_mu.data_ptr(), ws.data_ptr(), ws.numel(),
+                                  c_void_p(stream)), "kp_greedy_place")
+    return out_idx, out_score, out_pc, out_cu, out_mu
+
+
+def node_scores(nodes: Dict[str, torch.Tensor], strategy: int = 0, filter_mode: int = FILTER_CAPACITY):
+    """Per-node score, free cpu cores, free memory GiB, eligibility (scheduler.py:537-545, :232-233)."""
+    lib = _lib.load()
+    nst, device, n = _node_struct(nodes)
+    score = torch.empty(n, dtype=torch.float64, device=device)
+    fc = torch.empty(n, dtype=torch.float64, device=device)
+    fm = torch.empty(n, dtype=torch.float64, device=device)
+    el = torch.empty(n, dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        check(lib.kp_node_scores(byref(nst), int(strategy), int(filter_mode), score.data_ptr(),
+                                 fc.data_ptr(), fm.data_ptr(), el.data_ptr(), c_void_p(stream)),
+              "kp_node_scores")
+    return score, fc, fm, el
+
+
+def launch_count() -> int:
+    return int(_lib.load().kp_launch_count())
+
+
+# ---------------------------------------------------------------------------------------
+# host-buffer session
+# ---------------------------------------------------------------------------------------
+def _host_ptr(a, dtype) -> Tuple[int, object]:
+    """Pointer to host data of a numpy array or CPU torch tensor (kept alive by the caller)."""
+    if isinstance(a, torch.Tensor):
+        if a.is_cuda:
+            raise TypeError("Session takes host memory; use snapshot_place/greedy_place for CUDA tensors")
+        want = {np.int64: torch.int64, np.float64: torch.float64, np.uint8: torch.uint8}[dtype]
+        if a.dtype != want or not a.is_contiguous():
+            a = a.to(want).contiguous()
+        return a.data_ptr(), a
+    arr = np.ascontiguousarray(a, dtype=dtype)
+    return arr.ctypes.data, arr
+
+
+class Session:
+    """Owns device buffers for up to (max_nodes, max_pods); every call takes HOST arrays,
+    copies them in, runs the CUDA path, copies results out and waits."""
+
+    def __init__(self, device: int = 0, max_nodes: int = 65536, max_pods: int = 1 << 20):
+        self._lib = _lib.load()
+        self._h = c_void_p()
+        self.device, self.max_nodes, self.max_pods = device, max_nodes, max_pods
+        self._resident = -1
+        check(self._lib.kp_session_create(device, max_nodes, max_pods, byref(self._h)),
+              "kp_session_create")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.kp_session_destroy(self._h)
+            self._h = c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @staticmethod
+    def _node_struct(nodes):
+        cols = nodes.columns() if isinstance(nodes, NodeTable) else nodes
+        keep = []
+        st = KpNodeTable()
+        st.n_nodes = len(cols["pod_count"])
+        for k in NODE_COLUMNS:
+            dt = {torch.int64: np.int64, torch.float64: np.float64, torch.uint8: np.uint8}[_NODE_DTYPES[k]]
+            ptr, ref = _host_ptr(cols[k], dt)
+            keep.append(ref)
+            setattr(st, k, ptr)
+        return st, keep
+
+    @staticmethod
+    def _pod_struct(pods):
+        if isinstance(pods, PodTable):
+            rc, rm, sid = pods.req_cpu_milli, pods.req_mem_bytes, pods.strategy_ids
+        else:
+            rc, rm, sid = pods
+        keep = []
+        st = KpPodTable()
+        p1, r1 = _host_ptr(rc, np.int64)
+        p2, r2 = _host_ptr(rm, np.int64)
+        keep += [r1, r2]
+        st.n_pods = len(r1)
+        st.req_cpu_milli, st.req_mem_bytes = p1, p2
+        st.strategy_ids = None
+        if sid is not None:
+            p3, r3 = _host_ptr(sid, np.int64)
+            keep.append(r3)
+            st.strategy_ids = p3
+        return st, keep
+
+    def set_nodes(self, nodes) -> None:
+        st, keep = self._node_struct(nodes)
+        check(self._lib.kp_session_set_nodes(self._h, byref(st)), "kp_session_set_nodes")
+        self._resident = st.n_nodes
+
+    def snapshot(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY, out=None):
+        """nodes=None reuses the table kept by set_nodes().  Returns (idx, score) numpy arrays,
+        or fills ``out`` = (idx, score) host buffers (numpy or pinned torch)."""
+        nst, keep = self._node_struct(nodes) if nodes is not None else (None, [])
+        pst, keep2 = self._pod_struct(pods)
+        p = pst.n_pods
+        if out is None:
+            out = (np.empty(p, np.int64), np.empty(p, np.float64))
+        ip, iref = _host_ptr(out[0], np.int64)
+        sp, sref = _host_ptr(out[1], np.float64)
+        check(self._lib.kp_session_snapshot(self._h, byref(nst) if nst is not None else None,
+                                            byref(pst), int(strategy), int(filter_mode), ip, sp),
+              "kp_session_snapshot")
+        if nst is not None:
+            self._resident = nst.n_nodes
+        return out
+
+    def greedy(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY):
+        """Returns (idx, score, final_pod_count, final_cpu_usage, final_mem_usage) numpy arrays."""
+        nst, keep = self._node_struct(nodes) if nodes is not None else (None, [])
+        pst, keep2 = self._pod_struct(pods)
+        p = pst.n_pods
+        n = nst.n_nodes if nst is not None else self._resident
+        idx, score = np.empty(p, np.int64), np.empty(p, np.float64)
+        pc, cu, mu = np.empty(n, np.int64), np.empty(n, np.float64), np.empty(n, np.float64)
+        check(self._lib.kp_session_greedy(self._h, byref(nst) if nst is not None else None, byref(pst),
+                                          int(strategy), int(filter_mode), idx.ctypes.data,
+                                          score.ctypes.data, pc.ctypes.data, cu.ctypes.data,
+                                          mu.ctypes.data), "kp_session_greedy")
+        if nst is not None:
+            self._resident = nst.n_nodes
+        return idx, score, pc, cu, mu
+
+    def last_copy_bytes(self) -> Tuple[int, int]:
+        a, b = c_int64(), c_int64()
+        check(self._lib.kp_session_last_copy_bytes(self._h, byref(a), byref(b)),
+              "kp_session_last_copy_bytes")
+        return a.value, b.value

@@ -1,0 +1,120 @@
+"""Parity of the CUDA greedy-commit path (kp_greedy_place / kp_session_greedy) against the
+reference's own bind sequences (tests/golden/greedy.json) and the CPU oracle."""
+import json
+
+import numpy as np
+import pytest
+
+from k8s_llm_scheduler_b200 import synth
+from k8s_llm_scheduler_b200.tables import NodeTable, PodTable, strategy_id
+from tests.helpers import (COND, assert_same_f64, assert_same_idx, bits, device_greedy,
+                           oracle_greedy)
+
+pytestmark = pytest.mark.gpu
+
+
+def load(golden_dir, name):
+    return json.loads((golden_dir / name).read_text())
+
+
+def test_reference_bind_sequences(golden_dir):
+    """The reference's own loop (real get_node_metrics + _fallback_decision + bind)."""
+    for case in load(golden_dir, "greedy.json"):
+        rows = [dict(name=ns["name"], cpu=ns["cpu"], memory=ns["memory"], pods=ns["pods"],
+                     pod_count=ns["n_running"], conditions=COND[ns.get("cond", "ready")])
+                for ns in case["nodes"]]
+        nodes = NodeTable.from_allocatable(rows)
+        p = case["n_pods"]
+        pods = PodTable.from_columns([100] * p, [1 << 20] * p)
+        idx, score, pc, cu, mu = device_greedy(nodes, pods, strategy_id(case["strategy"]), 0)
+        assert idx.tolist() == case["idx_seq"], case["tag"]
+        assert [bits(s) for s in score] == case["score_bits_seq"], case["tag"]
+        assert pc.tolist() == case["final_pod_count"], case["tag"]
+
+
+def test_config1_bind_sequence(golden_dir):
+    g = load(golden_dir, "config1_trace.json")
+    nodes, pods = synth.config1()
+    for mode in (0, 1):
+        idx, score, pc, cu, mu = device_greedy(nodes, pods, 0, mode)
+        assert [nodes.names[i] for i in idx] == g["binds"] == ["minikube-m02", "minikube-m03", "minikube-m02"]
+        assert pc.tolist() == [f["pod_count"] for f in g["final_table"]]
+        assert [bits(x) for x in cu] == [f["cu_bits"] for f in g["final_table"]]
+
+
+@pytest.mark.parametrize("n,p", [(1, 40), (3, 100), (60, 3000), (1024, 1500), (1025, 1100), (2500, 2100),
+                                 (4096, 900), (5000, 2500), (6144, 600), (7000, 300)])
+def test_random_clusters_against_oracle(n, p):
+    nodes, pods = synth.config5(n, p, seed=2000 + n)
+    for mode in (0, 1):
+        for sid in (0, 1, 2):
+            g = device_greedy(nodes, pods, sid, mode)
+            o = oracle_greedy(nodes, pods, sid, mode)
+            assert_same_idx(g[0], o[0], f"n={n} mode={mode} strategy={sid}")
+            assert_same_f64(g[1], o[1])
+            assert np.array_equal(g[2], o[2])
+            assert_same_f64(g[3], o[3], "cpu usage")
+            assert_same_f64(g[4], o[4], "mem usage")
+        g = device_greedy(nodes, pods, 0, mode, per_pod=True)
+        o = oracle_greedy(nodes, pods, 0, mode, per_pod=True)
+        assert_same_idx(g[0], o[0], f"n={n} mode={mode} per-pod strategies")
+        assert_same_f64(g[1], o[1])
+        assert np.array_equal(g[2], o[2])
+
+
+def test_config3_reduced_depletion():
+    """Config-3 shape (homogeneous, pod_count ~ U{0..55}) with enough pods to fill nodes up."""
+    nodes, pods = synth.config3(300, 30_000)
+    g = device_greedy(nodes, pods, 0, 1)
+    o = oracle_greedy(nodes, pods, 0, 1)
+    assert_same_idx(g[0], o[0])
+    assert_same_f64(g[1], o[1])
+    assert np.array_equal(g[2], o[2])
+    assert (g[0] < 0).any() and (g[2] <= 110).all()            # cluster fills, then pods fail
+
+
+def test_config3_full_nodes_sampled_pods():
+    nodes, pods = synth.config3(5000, 40_000)
+    g = device_greedy(nodes, pods, 0, 1)
+    o = oracle_greedy(nodes, pods, 0, 1)
+    assert_same_idx(g[0], o[0])
+    assert_same_f64(g[1], o[1])
+    assert np.array_equal(g[2], o[2])
+
+
+def test_round_robin_piles_on_one_node():
+    nodes, pods = synth.config2(200, 500)
+    idx, score, pc, *_ = device_greedy(nodes, pods, 2, 0)
+    first = int(np.argmax(nodes.pod_count))
+    assert (idx == first).all() and pc[first] == nodes.pod_count[first] + 500
+
+
+def test_edge_cases():
+    nodes, pods = synth.config2(20, 10)
+    empty = PodTable.from_columns([], [])
+    idx, score, pc, cu, mu = device_greedy(nodes, empty, 0, 1)
+    assert idx.size == 0 and np.array_equal(pc, nodes.pod_count)
+    nodes.ready[:] = 0
+    idx, score, pc, *_ = device_greedy(nodes, pods, 0, 1)
+    assert (idx == -1).all() and (score == -1.0).all() and np.array_equal(pc, nodes.pod_count)
+    # custom usage that does not follow A3 is overwritten by the first commit
+    nodes, pods = synth.config2(4, 6)
+    nodes.cpu_usage_pct[:] = [10.0, 3.0, 3.0, 77.0]
+    nodes.mem_usage_pct[:] = [1.0, 3.0, 2.5, 0.0]
+    for sid in (0, 1):
+        g = device_greedy(nodes, pods, sid, 0)
+        o = oracle_greedy(nodes, pods, sid, 0)
+        assert_same_idx(g[0], o[0])
+        assert_same_f64(g[1], o[1])
+        assert_same_f64(g[3], o[3])
+
+
+def test_session_greedy_matches_device_api():
+    from k8s_llm_scheduler_b200.placement import Session
+    nodes, pods = synth.config5(1500, 4000, seed=9)
+    with Session(0, max_nodes=2048, max_pods=4096) as s:
+        h = s.greedy(nodes, pods, 0, 1)
+        d = device_greedy(nodes, pods, 0, 1, per_pod=True)
+        assert_same_idx(h[0], d[0])
+        assert_same_f64(h[1], d[1])
+        assert np.array_equal(h[2], d[2])

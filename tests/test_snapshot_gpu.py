@@ -1,0 +1,252 @@
+"""Parity of the CUDA snapshot path (kp_snapshot_place / kp_node_scores / kp_session_snapshot)
+against the reference-generated golden vectors and the CPU oracle.  Node indices must match
+exactly; scores are compared BIT-FOR-BIT (the north star allows 1e-9 relative)."""
+import ctypes
+import json
+
+import numpy as np
+import pytest
+
+from k8s_llm_scheduler_b200 import synth
+from k8s_llm_scheduler_b200.tables import NodeTable, PodTable, strategy_id
+from tests.helpers import (assert_same_f64, assert_same_idx, bits, device_snapshot, from_bits,
+                           oracle_snapshot)
+
+pytestmark = pytest.mark.gpu
+STRATS = ["resource_balanced", "least_loaded", "round_robin", "no_such_strategy"]
+
+
+def load(golden_dir, name):
+    return json.loads((golden_dir / name).read_text())
+
+
+def table_from_specs(specs):
+    """specs: list of (pc, mp, cu, mu, ready)."""
+    n = len(specs)
+    return NodeTable.from_columns(
+        alloc_cpu_milli=[8000] * n, alloc_mem_bytes=[16374576 * 1024] * n,
+        pod_count=[s[0] for s in specs], max_pods=[s[1] for s in specs],
+        ready=[s[4] for s in specs], cpu_usage_pct=[s[2] for s in specs],
+        mem_usage_pct=[s[3] for s in specs])
+
+
+def test_node_scores_match_reference_bits(golden_dir):
+    import torch
+    from k8s_llm_scheduler_b200 import placement
+    g = load(golden_dir, "kat_scores.json")
+    rows = g["a3_usage"]
+    specs = [(r["pc"], r["mp"], from_bits(r["usage_bits"]), from_bits(r["usage_bits"]), 1) for r in rows]
+    specs += [(r["pc"], r["mp"], r["cu"], r["mu"], 1) for r in g["custom_usage"]]
+    allrows = rows + g["custom_usage"]
+    dn = placement.nodes_to_device(table_from_specs(specs), "cuda:0")
+    for sid, s in enumerate(STRATS[:3]):
+        score, _, _, elig = placement.node_scores(dn, sid, filter_mode=0)
+        score, elig = score.cpu().numpy(), elig.cpu().numpy()
+        for i, r in enumerate(allrows):
+            assert bool(elig[i]) == r[s]["selected"], (i, s)
+            if r[s]["selected"]:
+                assert bits(score[i]) == r[s]["score_bits"], (r["pc"], r["mp"], s)
+
+
+def test_reference_decisions_ready_filter(golden_dir):
+    """Every golden decision of the unmodified reference, through the GPU path."""
+    for case in load(golden_dir, "decisions.json"):
+        if not case["nodes"]:
+            continue
+        specs = [(n["pc"], n["mp"], from_bits(n["cu_bits"]), from_bits(n["mu_bits"]),
+                  int(n["cond"] in ("ready", "ready_second"))) for n in case["nodes"]]
+        nodes = table_from_specs(specs)
+        pods = PodTable.from_columns([100, 250000, 1], [1 << 20, 1 << 45, 0])
+        for s in STRATS:
+            exp = case["expect"][s]
+            idx, score = device_snapshot(nodes, pods, strategy_id(s), filter_mode=0)
+            assert idx.tolist() == [exp["idx"]] * 3, (case["tag"], s)
+            assert [bits(x) for x in score] == [exp["score_bits"]] * 3, (case["tag"], s)
+
+
+@pytest.mark.parametrize("n,p", [(1, 1), (3, 5), (7, 257), (100, 3000), (1000, 2049), (4096, 700),
+                                 (4097, 1500), (5000, 300), (9001, 4099)])
+def test_random_clusters_capacity_filter(n, p):
+    nodes, pods = synth.config5(n, p, seed=1000 + n)
+    for sid in (0, 1, 2):
+        gi, gs = device_snapshot(nodes, pods, sid, 1)
+        oi, os_ = oracle_snapshot(nodes, pods, sid, 1)
+        assert_same_idx(gi, oi, f"n={n} p={p} strategy={sid}")
+        assert_same_f64(gs, os_)
+    gi, gs = device_snapshot(nodes, pods, 0, 1, per_pod=True)
+    oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
+    assert_same_idx(gi, oi, f"n={n} p={p} per-pod strategies")
+    assert_same_f64(gs, os_)
+    gi, gs = device_snapshot(nodes, pods, 0, 0, per_pod=True)      # reference filter, mixed
+    oi, os_ = oracle_snapshot(nodes, pods, 0, 0, per_pod=True)
+    assert_same_idx(gi, oi)
+    assert_same_f64(gs, os_)
+
+
+def test_config1_snapshot():
+    nodes, pods = synth.config1()
+    for mode in (0, 1):
+        idx, score = device_snapshot(nodes, pods, 0, mode)
+        assert idx.tolist() == [1, 1, 1]                      # m02 (ties with m03, first wins)
+        assert [bits(s) for s in score] == ["3fef9f2f79f2f79f"] * 3
+
+
+def test_config2_full_size_least_loaded():
+    """BASELINE config 2 at full size: 1k nodes x 100k pods, every pod checked."""
+    nodes, pods = synth.config2()
+    gi, gs = device_snapshot(nodes, pods, 1, 1)
+    oi, os_ = oracle_snapshot(nodes, pods, 1, 1)
+    assert_same_idx(gi, oi)
+    assert_same_f64(gs, os_)
+    assert (gi >= 0).all()
+
+
+def test_config5_reduced_mixed_strategies():
+    nodes, pods = synth.config5(5000, 60_000)
+    gi, gs = device_snapshot(nodes, pods, 0, 1, per_pod=True)
+    oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
+    assert_same_idx(gi, oi)
+    assert_same_f64(gs, os_)
+    assert 0.27 < (gi < 0).mean() < 0.33
+
+
+def test_all_equal_nodes_first_wins():
+    nodes = synth.all_equal_nodes(6000)
+    nodes.ready[:5] = 0
+    nodes.pod_count[5] = 110                                  # full: ineligible under capacity
+    nodes.cpu_usage_pct[5] = nodes.mem_usage_pct[5] = 50.0
+    _, pods = synth.config2(10, 1000)
+    for sid in (0, 1):
+        idx, _ = device_snapshot(nodes, pods, sid, 1)
+        assert (idx == 6).all()
+        idx, _ = device_snapshot(nodes, pods, sid, 0)
+        assert (idx == 6).all()        # node 5 scores lower (pc=110), so 6 still wins
+    idx, _ = device_snapshot(nodes, pods, 2, 0)
+    assert (idx == 5).all()            # round_robin = MOST pods (scheduler.py:544-549)
+
+
+def test_edge_cases():
+    nodes, pods = synth.config2(50, 40)
+    empty_pods = PodTable.from_columns([], [])
+    idx, score = device_snapshot(nodes, empty_pods, 0, 1)
+    assert idx.size == 0 and score.size == 0
+    empty_nodes = NodeTable.from_columns(alloc_cpu_milli=[], alloc_mem_bytes=[], pod_count=[],
+                                         max_pods=[], ready=[], cpu_usage_pct=[], mem_usage_pct=[])
+    for mode in (0, 1):
+        idx, score = device_snapshot(empty_nodes, pods, 0, mode)
+        assert (idx == -1).all() and (score == -1.0).all()
+    nodes.ready[:] = 0
+    for mode in (0, 1):
+        idx, score = device_snapshot(nodes, pods, 1, mode)
+        assert (idx == -1).all() and (score == -1.0).all()
+    # nothing fits: every pod larger than every node
+    nodes, pods = synth.config2(300, 64)
+    pods.req_cpu_milli[:] = 10 ** 9
+    idx, score = device_snapshot(nodes, pods, 0, 1)
+    assert (idx == -1).all() and (score == -1.0).all()
+    # sentinel: score <= -1 never wins (scheduler.py:529,547); NaN usage never wins; max_pods == 0
+    specs = [(341, 110, 155.0, 155.0, 1), (0, 0, 0.0, 0.0, 1), (5, 110, float("nan"), 1.0, 1),
+             (223, 110, 101.36363636363636, 101.36363636363636, 1)]
+    t = table_from_specs(specs)
+    one = PodTable.from_columns([1], [1])
+    for sid in (0, 1, 2):
+        gi, gs = device_snapshot(t, one, sid, 0)
+        oi, os_ = oracle_snapshot(t, one, sid, 0)
+        assert_same_idx(gi, oi)
+        assert_same_f64(gs, os_)
+        gi, gs = device_snapshot(t, one, sid, 1)
+        oi, os_ = oracle_snapshot(t, one, sid, 1)
+        assert_same_idx(gi, oi)
+        assert_same_f64(gs, os_)
+
+
+def test_large_values_and_negative_requests():
+    rng = np.random.Generator(np.random.PCG64(77))
+    n, p = 500, 2000
+    mp = rng.integers(1, 10 ** 6, n)
+    pc = (rng.random(n) * mp * 1.2).astype(np.int64)
+    u = synth.usage_a3(pc, mp)
+    nodes = NodeTable.from_columns(alloc_cpu_milli=rng.integers(1, 2 ** 50, n),
+                                   alloc_mem_bytes=rng.integers(1, 2 ** 52, n), pod_count=pc,
+                                   max_pods=mp, ready=np.ones(n, np.uint8), cpu_usage_pct=u,
+                                   mem_usage_pct=u * rng.random(n))
+    pods = PodTable.from_columns(rng.integers(-5, 2 ** 49, p), rng.integers(-5, 2 ** 51, p))
+    for sid in (0, 1, 2):
+        gi, gs = device_snapshot(nodes, pods, sid, 1)
+        oi, os_ = oracle_snapshot(nodes, pods, sid, 1)
+        assert_same_idx(gi, oi)
+        assert_same_f64(gs, os_)
+
+
+def test_full_size_properties_config4_shard():
+    """50k nodes x 160k pods (a config-4 shard): too big for the oracle at full P, so check
+    size-independent properties plus the oracle on a seeded subsample."""
+    import torch
+    from k8s_llm_scheduler_b200 import placement
+    nodes, pods = synth.config4(50_000, 160_000)
+    gi, gs = device_snapshot(nodes, pods, 0, 1)
+    gi2, gs2 = device_snapshot(nodes, pods, 0, 1)
+    assert np.array_equal(gi, gi2) and np.array_equal(gs.view(np.uint64), gs2.view(np.uint64))
+    # pod-permutation equivariance
+    perm = np.random.Generator(np.random.PCG64(5)).permutation(len(pods))
+    shuffled = PodTable.from_columns(pods.req_cpu_milli[perm], pods.req_mem_bytes[perm])
+    pi, ps = device_snapshot(nodes, shuffled, 0, 1)
+    assert np.array_equal(pi, gi[perm]) and np.array_equal(ps.view(np.uint64), gs[perm].view(np.uint64))
+    # the chosen node fits, and reports its own score
+    dn = placement.nodes_to_device(nodes, "cuda:0")
+    score, fc, fm, el = (t.cpu().numpy() for t in placement.node_scores(dn, 0, 1))
+    ok = gi >= 0
+    assert ok.all()
+    assert el[gi].all()
+    assert (pods.req_cpu_milli / 1000.0 <= fc[gi]).all()
+    assert (pods.req_mem_bytes / 1024 / 1024 / 1024 <= fm[gi]).all()
+    assert np.array_equal(score[gi].view(np.uint64), gs.view(np.uint64))
+    # oracle on a subsample
+    sub = np.random.Generator(np.random.PCG64(6)).choice(len(pods), 1500, replace=False)
+    sp = PodTable.from_columns(pods.req_cpu_milli[sub], pods.req_mem_bytes[sub])
+    oi, os_ = oracle_snapshot(nodes, sp, 0, 1)
+    assert_same_idx(gi[sub], oi)
+    assert_same_f64(gs[sub], os_)
+
+
+def test_session_host_api_matches_device_api():
+    from k8s_llm_scheduler_b200.placement import Session
+    nodes, pods = synth.config5(3000, 20_000, seed=42)
+    with Session(0, max_nodes=4000, max_pods=32_768) as s:
+        for mode in (0, 1):
+            hi, hs = s.snapshot(nodes, pods, 1, mode)
+            di, ds = device_snapshot(nodes, pods, 1, mode)
+            assert_same_idx(hi, di)
+            assert_same_f64(hs, ds)
+        hi, hs = s.snapshot(nodes, PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes,
+                                                         pods.strategy_ids), 0, 1)
+        oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
+        assert_same_idx(hi, oi)
+        assert_same_f64(hs, os_)
+        h2d, d2h = s.last_copy_bytes()
+        assert h2d == 6 * 8 * 3000 + 3000 + 3 * 8 * 20_000 and d2h == 16 * 20_000
+        s.set_nodes(nodes)
+        ri, rs = s.snapshot(None, pods, 0, 1)                      # resident table reused
+        oi, os_ = oracle_snapshot(nodes, pods, 0, 1)
+        assert_same_idx(ri, oi)
+        from k8s_llm_scheduler_b200 import PlacementError
+        with pytest.raises(PlacementError):
+            s.snapshot(nodes, PodTable.from_columns(np.zeros(40_000), np.zeros(40_000)), 0, 1)
+
+
+def test_workspace_errors_are_reported():
+    import torch
+    from k8s_llm_scheduler_b200 import PlacementError, placement
+    nodes, pods = synth.config2(100, 100)
+    dn = placement.nodes_to_device(nodes, "cuda:0")
+    rc, rm = torch.as_tensor(pods.req_cpu_milli).cuda(), torch.as_tensor(pods.req_mem_bytes).cuda()
+    with pytest.raises(ValueError):
+        placement.snapshot_place(dn, rc, rm, 0, 1, workspace=torch.empty(16, dtype=torch.uint8, device="cuda"))
+    lib = placement._lib.load()
+    nst, _, _ = placement._node_struct(dn)
+    pst, *_ = placement._pod_struct(rc, rm, 0, rc.device)
+    out_i, out_s = torch.empty(100, dtype=torch.int64, device="cuda"), torch.empty(100, dtype=torch.float64, device="cuda")
+    ws = torch.empty(1024, dtype=torch.uint8, device="cuda")
+    st = lib.kp_snapshot_place(ctypes.byref(nst), ctypes.byref(pst), 0, 1, out_i.data_ptr(), out_s.data_ptr(),
+                               ws.data_ptr(), 1024, None)
+    assert st == 2 and b"workspace" in lib.kp_last_error()
