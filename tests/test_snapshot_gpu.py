@@ -212,22 +212,22 @@ def test_full_size_properties_config4_shard():
 def test_session_host_api_matches_device_api():
     from k8s_llm_scheduler_b200.placement import Session
     nodes, pods = synth.config5(3000, 20_000, seed=42)
+    uniform = PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes)   # no per-pod strategy ids
     with Session(0, max_nodes=4000, max_pods=32_768) as s:
         for mode in (0, 1):
-            hi, hs = s.snapshot(nodes, pods, 1, mode)
-            di, ds = device_snapshot(nodes, pods, 1, mode)
+            hi, hs = s.snapshot(nodes, uniform, 1, mode)
+            di, ds = device_snapshot(nodes, uniform, 1, mode)
             assert_same_idx(hi, di)
             assert_same_f64(hs, ds)
-        hi, hs = s.snapshot(nodes, PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes,
-                                                         pods.strategy_ids), 0, 1)
+        hi, hs = s.snapshot(nodes, pods, 0, 1)                      # per-pod strategy ids travel too
         oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
         assert_same_idx(hi, oi)
         assert_same_f64(hs, os_)
         h2d, d2h = s.last_copy_bytes()
         assert h2d == 6 * 8 * 3000 + 3000 + 3 * 8 * 20_000 and d2h == 16 * 20_000
         s.set_nodes(nodes)
-        ri, rs = s.snapshot(None, pods, 0, 1)                      # resident table reused
-        oi, os_ = oracle_snapshot(nodes, pods, 0, 1)
+        ri, rs = s.snapshot(None, uniform, 0, 1)                   # resident table reused
+        oi, os_ = oracle_snapshot(nodes, uniform, 0, 1)
         assert_same_idx(ri, oi)
         from k8s_llm_scheduler_b200 import PlacementError
         with pytest.raises(PlacementError):
