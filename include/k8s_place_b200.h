@@ -114,6 +114,29 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
                       int filter_mode, int64_t *out_node_idx, double *out_score,
                       void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- snapshot placement without a workspace, device pointers -------------------------
+ * No counterpart in the reference: this entry point exists for hosts that cannot give
+ * kp_snapshot_place a workspace because they cannot allocate device memory at the time
+ * of the call -- e.g. a scheduler sidecar sharing its GPU with an inference server whose
+ * memory pool already owns all of HBM, or a placement loop with a latency budget that
+ * must stay clear of cudaMalloc/cudaFree (both take the driver's allocator lock and
+ * synchronise the device).  Same inputs, outputs and results as kp_snapshot_place; the
+ * scratch is a fixed 1.5 MiB array inside the library's device image (resident on every
+ * GPU that loads the library, until the process exits), so the call allocates nothing.
+ *
+ * Limits: n_nodes <= 8192; with pods->strategy_ids set, n_pods <= 65536 (no pod limit for
+ * a uniform strategy).  Larger calls return KP_ERR_CAPACITY with a message and do no work.
+ *
+ * The first call on each device looks up the array's device address (the device that is
+ * current at the call); make that first call before starting any stream capture.  All
+ * calls on a device share the one array: calls that may overlap on the GPU (different
+ * streams, different threads) race on it -- serialise them, or use kp_snapshot_place with
+ * separate workspaces.  Nothing needs clearing between calls; each call resets what it uses.
+ */
+int kp_snapshot_place_noalloc(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                              int filter_mode, int64_t *out_node_idx, double *out_score,
+                              void *stream);
+
 /* ---- greedy placement with commit, device pointers ---------------------------------
  * Replaces: the sequential loop `_schedule_pod` -> `_fallback_decision` -> bind ->
  * next `get_node_metrics()` (scheduler.py:690-729, :598, :144-151).  Pods are placed in

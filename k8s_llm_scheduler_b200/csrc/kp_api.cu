@@ -266,6 +266,20 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
                                  workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+int kp_snapshot_place_noalloc(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
+                              int filter_mode, int64_t *out_node_idx, double *out_score, void *stream)
+{
+    int st = check_tables(nodes, pods);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) {
+        set_error("output pointer is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    return snapshot_place_noalloc(*nodes, *pods, strategy, filter_mode, out_node_idx, out_score,
+                                  (cudaStream_t)stream);
+}
+
 size_t kp_greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods)
 {
     return greedy_workspace_bytes(n_nodes, n_pods);

@@ -731,4 +731,57 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     return st;
 }
 
+// ---------------------------------------------------------------------------------------
+// kp_snapshot_place_noalloc: the snapshot path for callers that cannot provide scratch
+// ---------------------------------------------------------------------------------------
+// Some hosts of this library cannot hand us a workspace: a scheduler sidecar that shares
+// its GPU with an inference server whose allocator already owns all of HBM has nothing to
+// cudaMalloc from, and a placement loop with a latency budget must not call cudaMalloc /
+// cudaFree at all (both take the driver's allocator lock and synchronise the device).
+// For them the node plan lives in this fixed array instead, which is part of the loaded
+// module: every GPU that loads the library carries these 1.5 MiB until the process exits.
+//
+// The array's name is only a host-side handle in host code.  The device address is
+// looked up with cudaGetSymbolAddress, once per device, while that device is current.
+constexpr int64_t kNoAllocMaxNodes = 8192;
+constexpr int64_t kNoAllocMaxPodsPerPodStrategy = 65536;
+constexpr size_t kNoAllocScratchBytes = 3u << 19;          // 1.5 MiB >= layout(8192 nodes, 65536 pods, per-pod)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
+                           int filter_mode, int64_t *out_idx, double *out_score, cudaStream_t stream)
+{
+    const bool per_pod = pods.strategy_ids != nullptr;
+    if (nodes.n_nodes > kNoAllocMaxNodes) {
+        set_error("kp_snapshot_place_noalloc: %lld nodes exceed the built-in scratch limit of %lld "
+                  "(use kp_snapshot_place with a caller-provided workspace)",
+                  (long long)nodes.n_nodes, (long long)kNoAllocMaxNodes);
+        return KP_ERR_CAPACITY;
+    }
+    if (per_pod && pods.n_pods > kNoAllocMaxPodsPerPodStrategy) {
+        set_error("kp_snapshot_place_noalloc: %lld pods with per-pod strategy ids exceed the built-in "
+                  "scratch limit of %lld (uniform-strategy calls have no pod limit)",
+                  (long long)pods.n_pods, (long long)kNoAllocMaxPodsPerPodStrategy);
+        return KP_ERR_CAPACITY;
+    }
+    if (make_layout(nodes.n_nodes, pods.n_pods, per_pod).total > kNoAllocScratchBytes) {
+        set_error("kp_snapshot_place_noalloc: internal scratch too small for this call");
+        return KP_ERR_CAPACITY;
+    }
+    // per-device set-up on the first call: resolve the array's device address
+    static void *scratch_addr[64] = {nullptr};
+    int dev = -1;
+    KP_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("kp_snapshot_place_noalloc: device ordinal %d unsupported", dev); return KP_ERR_NO_DEVICE; }
+    if (!scratch_addr[dev]) {
+        void *ptr = nullptr;
+        KP_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        scratch_addr[dev] = ptr;
+    }
+    // the array keeps the previous call's contents; snapshot_place_device re-zeroes the
+    // counters / rank accumulators and re-fills the padding of the rank table on every call
+    return snapshot_place_device(nodes, pods, strategy, filter_mode, out_idx, out_score,
+                                 scratch_addr[dev], kNoAllocScratchBytes, stream);
+}
+
 }  // namespace kp
