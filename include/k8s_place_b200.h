@@ -121,7 +121,7 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
  * memory pool already owns all of HBM, or a placement loop with a latency budget that
  * must stay clear of cudaMalloc/cudaFree (both take the driver's allocator lock and
  * synchronise the device).  Same inputs, outputs and results as kp_snapshot_place; the
- * scratch is a fixed 1.5 MiB array inside the library's device image (resident on every
+ * scratch is a fixed 2 MiB array inside the library's device image (resident on every
  * GPU that loads the library, until the process exits), so the call allocates nothing.
  *
  * Limits: n_nodes <= 8192; with pods->strategy_ids set, n_pods <= 65536 (no pod limit for

@@ -65,7 +65,8 @@ def test_reference_decisions_ready_filter(golden_dir):
 
 
 @pytest.mark.parametrize("n,p", [(1, 1), (3, 5), (7, 257), (100, 3000), (1000, 2049), (4096, 700),
-                                 (4097, 1500), (5000, 300), (9001, 4099)])
+                                 (4097, 1500), (5000, 300), (9001, 4099), (8192, 600), (8193, 600),
+                                 (20000, 1000)])
 def test_random_clusters_capacity_filter(n, p):
     nodes, pods = synth.config5(n, p, seed=1000 + n)
     for sid in (0, 1, 2):
@@ -156,6 +157,31 @@ def test_edge_cases():
         assert_same_f64(gs, os_)
         gi, gs = device_snapshot(t, one, sid, 1)
         oi, os_ = oracle_snapshot(t, one, sid, 1)
+        assert_same_idx(gi, oi)
+        assert_same_f64(gs, os_)
+
+
+def test_many_distinct_thresholds_take_the_wide_path():
+    """More than 32000 distinct free-cpu / free-memory values: the packed 15-bit rank table
+    cannot be used and place_kernel falls back to two 32-bit rank compares per pair.  Also a
+    table with distinct values but below the limit, and continuous (non-A3) usage values."""
+    rng = np.random.Generator(np.random.PCG64(31))
+    for n, p in ((40_000, 3000), (6_000, 2000)):
+        mp = np.full(n, 110, dtype=np.int64)
+        pc = rng.integers(0, 110, n)
+        nodes = NodeTable.from_columns(alloc_cpu_milli=rng.integers(4000, 96000, n),
+                                       alloc_mem_bytes=rng.integers(16, 768, n) << 30, pod_count=pc,
+                                       max_pods=mp, ready=(rng.random(n) > 0.02).astype(np.uint8),
+                                       cpu_usage_pct=rng.random(n) * 90.0, mem_usage_pct=rng.random(n) * 90.0)
+        pods = PodTable.from_columns(rng.integers(50, 60000, p), rng.integers(64, 400 * 1024, p) << 20,
+                                     rng.integers(0, 3, p))
+        for sid in (0, 1):
+            gi, gs = device_snapshot(nodes, pods, sid, 1)
+            oi, os_ = oracle_snapshot(nodes, pods, sid, 1)
+            assert_same_idx(gi, oi, f"n={n} strategy={sid}")
+            assert_same_f64(gs, os_)
+        gi, gs = device_snapshot(nodes, pods, 0, 1, per_pod=True)
+        oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
         assert_same_idx(gi, oi)
         assert_same_f64(gs, os_)
 

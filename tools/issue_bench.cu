@@ -39,6 +39,12 @@ __device__ __forceinline__ void upd_swar(int &best, uint32_t x, uint32_t w, int 
     asm volatile("{ .reg .pred p; .reg .b32 t, d; sub.u32 t, %1, %2; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0; @!p mov.s32 %0, %3; }"
                  : "+r"(best) : "r"(w), "r"(x), "r"(pos));
 }
+// same test, but the update is a guarded IMAD (FMA pipe): best_enc = pos * one + x; decode pos = best_enc - x
+__device__ __forceinline__ void upd_swar_fma(int &best_enc, uint32_t x, uint32_t w, int pos, int one)
+{
+    asm volatile("{ .reg .pred p; .reg .b32 t, d; sub.u32 t, %1, %2; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0; @!p mad.lo.s32 %0, %3, %4, %2; }"
+                 : "+r"(best_enc) : "r"(w), "r"(x), "r"(pos), "r"(one));
+}
 __device__ __forceinline__ void upd_f64(int &best, double a, double b, double A, double B, int pos)
 {
     if (a <= A && b <= B) best = pos;
@@ -50,7 +56,7 @@ __device__ __forceinline__ void upd_mixed(int &best, double a, int rb, double A,
 
 template <char V, int R>
 __global__ void __launch_bounds__(THREADS) bench_kernel(const Tile *__restrict__ g, int iters, int *__restrict__ out,
-                                                        unsigned long long *__restrict__ clk)
+                                                        unsigned long long *__restrict__ clk, int one)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     // layout depends on variant
@@ -60,7 +66,7 @@ __global__ void __launch_bounds__(THREADS) bench_kernel(const Tile *__restrict__
     // E: {ta (double), rb (int), pad}
     for (int i = threadIdx.x; i < TILE; i += THREADS) {
         if (V == 'A') s_ab[i] = make_uint2(g->ra[i], g->rb[i]);
-        if (V == 'C') s_pk[i] = g->packed[i];
+        if (V == 'C' || V == 'B' || V == 'F') s_pk[i] = g->packed[i];
         if (V == 'D') s_t[i] = make_double2(g->ta[i], g->tb[i]);
         if (V == 'E') { s_t[i].x = g->ta[i]; reinterpret_cast<int *>(&s_t[i].y)[0] = (int)g->rb[i]; }
         if (V == 'M') { s_t[i] = make_double2(g->ta[i], g->tb[i]); reinterpret_cast<uint32_t *>(smem + TILE * 16)[i] = g->packed[i]; }
@@ -103,6 +109,21 @@ __global__ void __launch_bounds__(THREADS) bench_kernel(const Tile *__restrict__
                     upd_swar(best[r], x[r], v.z, 4 * i + 2);
                     upd_swar(best[r], x[r], v.y, 4 * i + 1);
                     upd_swar(best[r], x[r], v.x, 4 * i);
+                }
+            }
+        } else if (V == 'B' || V == 'F') {
+            // B: half the pods update with SEL (ALU), half with a guarded IMAD (FMA); F: all IMAD
+            const uint4 *tp = reinterpret_cast<const uint4 *>(s_pk);
+            for (int i = TILE / 4 - 1; i >= 0; --i) {
+                const uint4 v = tp[i];
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 3; k >= 0; --k) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        if (V == 'F' || (r & 1)) upd_swar_fma(best[r], x[r], w[k], 4 * i + k, one);
+                        else upd_swar(best[r], x[r], w[k], 4 * i + k);
+                    }
                 }
             }
         } else if (V == 'D') {
@@ -170,12 +191,12 @@ static void run(const char *what, const Tile *d_tile, int sms, int ctas_per_sm, 
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    bench_kernel<V, R><<<grid, THREADS, smem>>>(d_tile, 2, out, clk);
+    bench_kernel<V, R><<<grid, THREADS, smem>>>(d_tile, 2, out, clk, 1);
     CK(cudaDeviceSynchronize());
     float best_ms = 1e30f;
     for (int rep = 0; rep < 5; ++rep) {
         CK(cudaEventRecord(e0));
-        bench_kernel<V, R><<<grid, THREADS, smem>>>(d_tile, iters, out, clk);
+        bench_kernel<V, R><<<grid, THREADS, smem>>>(d_tile, iters, out, clk, 1);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
         float ms;
@@ -214,6 +235,8 @@ int main()
     for (int occ : {1, 2, 4}) {
         run<'A', 8>("A  ISETP+ISETP+SEL", d, sms, occ, iters);
         run<'C', 8>("C  SWAR IMAD.IADD+LOP3.P+SEL", d, sms, occ, iters);
+        run<'B', 8>("B  SWAR, half SEL half @P IMAD", d, sms, occ, iters);
+        run<'F', 8>("F  SWAR, all @P IMAD", d, sms, occ, iters);
         run<'D', 8>("D  DSETP+DSETP+SEL", d, sms, occ, iters);
         run<'E', 8>("E  DSETP+ISETP+SEL", d, sms, occ, iters);
         run<'M', 8>("M  half SWAR, half DSETPx2", d, sms, occ, iters);
@@ -222,6 +245,9 @@ int main()
     run<'A', 4>("A  ISETP+ISETP+SEL", d, sms, 4, iters);
     run<'A', 16>("A  ISETP+ISETP+SEL", d, sms, 2, iters);
     run<'C', 16>("C  SWAR", d, sms, 2, iters);
+    run<'B', 16>("B  SWAR half/half", d, sms, 2, iters);
+    run<'B', 4>("B  SWAR half/half", d, sms, 4, iters);
+    run<'B', 6>("B  SWAR half/half", d, sms, 4, iters);
     run<'M', 16>("M  half SWAR, half DSETPx2", d, sms, 2, iters);
     return 0;
 }
