@@ -307,7 +307,8 @@ def run_ours(args):
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def flush():
-        flush_buf.zero_()
+        if not args.no_flush:
+            flush_buf.zero_()
 
     hbm_peak, sm_max_mhz, peak_src = measured_peaks()
     sampler = ClockSampler(local)
@@ -442,7 +443,7 @@ def run_ours(args):
         "config": {"workload": meta["desc"], "nodes": n, "pods_per_gpu": p,
                    "strategy": "per-pod mix" if meta["per_pod"] else STRATEGY_NAMES[meta["strategy"]],
                    "filter": "capacity" if meta["filter"] == 1 else "ready", "mode": meta["mode"],
-                   "l2": "flushed between timed steps (256 MiB write)",
+                   "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)",
                    "sharding": "pods sharded per rank, node table broadcast from rank 0 (NCCL)" if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": float(e2e_s.item()) * 1e3, "api": "kp_session_snapshot" if snapshot else "kp_session_greedy"},
@@ -510,6 +511,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--extra", action=argparse.BooleanOptionalAction, default=True)
+    ap.add_argument("--no-flush", action="store_true", help="diagnostic: do not flush L2 between timed steps")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

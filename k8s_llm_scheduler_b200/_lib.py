@@ -70,7 +70,8 @@ def load(path: Path | None = None) -> ctypes.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = Path(path) if path else LIB_PATH
+    import os
+    p = Path(path) if path else Path(os.environ.get("KP_LIB_PATH", str(LIB_PATH)))
     if not p.exists():
         raise ImportError(
             f"{p} not found: build it with `python -m k8s_llm_scheduler_b200.build` "

@@ -44,7 +44,9 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     """Compile the CUDA library if it is missing or older than its sources."""
     if not force and not _stale():
         return LIB_PATH
-    cmd = [find_nvcc(), *NVCC_FLAGS, "-o", str(LIB_PATH), *[str(CSRC / s) for s in SOURCES]]
+    extra = os.environ.get("KP_NVCC_EXTRA", "").split()          # experiments only (e.g. -DKP_UPDATE_MODE=1)
+    out = Path(os.environ.get("KP_LIB_OUT", str(LIB_PATH)))
+    cmd = [find_nvcc(), *NVCC_FLAGS, *extra, "-o", str(out), *[str(CSRC / s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -1,0 +1,339 @@
+// place_kernel: the hot loop of snapshot placement (included by kp_snapshot.cu).
+//
+// Work decomposition.  grid.x = pod chunks, grid.y = node segments (a whole number of
+// shared-memory tiles each).  Inside a CTA the warps form a PODW x NSPLIT arrangement: warp
+// (podw, split) owns 32*R pods (R per lane, in registers) and scans slice `split` of every
+// tile.  Small inputs use NSPLIT > 1 so that a CTA carries few pods but many warps (fills the
+// machine when there are few pods); large tables use grid.y > 1 so that there are many more
+// CTAs than resident slots (no wave-quantisation tail).
+//
+// Tiles of the best-first node table are staged in shared memory with 1-D bulk async copies
+// (TMA engine, SASS UBLKCP) on a 2-deep mbarrier ring; every lane reads the same nodes
+// (one broadcast LDS.128 = 4 packed nodes).  Scanning worst -> best and overwriting the
+// candidate whenever the pod fits leaves the best-ranked fitting node of the range; ranges
+// are merged by taking the minimum rank position: across the warps of a CTA through shared
+// memory, across node segments with atomicMin in global memory, after which the CTA that
+// finishes a pod chunk last maps position -> node index / fp64 score and stores the result.
+//
+// Per pod x node pair, packed form (use_swar):
+//     t = node_word - pod_word           IMAD.IADD   (FMA pipe)
+//     p = (~t & 0x80008000) != 0         LOP3 -> P   (ALU pipe)   both guard bits survive iff
+//     @!p best = pos * 1 + pod_word      IMAD        (FMA pipe)   neither 15-bit field borrowed
+// tools/issue_bench.cu measured this mix (variant F) at 11.0 Tpairs/s on B200 = 89 % of the
+// 3-instruction issue bound, against 6.0 for two integer compares + select (ALU pipe only).
+// The wide form (more than 32000 distinct thresholds) uses two 32-bit compares + select.
+#pragma once
+
+#include "kp_common.cuh"
+
+namespace kp {
+
+#ifndef KP_TILE_BYTES
+#define KP_TILE_BYTES 8192
+#endif
+#ifndef KP_UPDATE_MODE
+#define KP_UPDATE_MODE 2      // candidate update: 0 = SEL (ALU pipe), 1 = alternate per pod, 2 = guarded IMAD (FMA pipe)
+#endif
+constexpr int kTileBytes = KP_TILE_BYTES;              // per shared-memory tile buffer
+constexpr int kTileNodesPacked = kTileBytes / 4;       // 2048
+constexpr int kTileNodesWide = kTileBytes / 8;         // 1024
+constexpr uint32_t kSwarGuards = 0x80008000u;
+constexpr uint32_t kSwarDeadPod = 0x7fff7fffu;         // larger than any node field: never fits
+constexpr uint32_t kNoPos = 0xffffffffu;
+
+struct PlaceParams {
+    const long long *req_cpu, *req_mem;
+    const uint32_t *perm;              // slot -> pod (per-pod strategies), NULL = identity
+    long long n_pods;
+    int n_nodes, npad, uniform_strategy;
+    int one;                           // always 1; run-time value so the IMAD update is not folded away
+    int tiles_per_seg_wide;            // tiles (of 1024 nodes) per node segment; the packed form uses half
+    const double *uniq;                // [2][npad] ascending distinct thresholds
+    const uint2 *ab;                   // [3][npad] best-first {RA, RB}
+    const uint32_t *packed;            // [3][npad] best-first packed ranks
+    const uint32_t *order;             // [3][npad] rank position -> node index
+    const double *score;               // [3][n]
+    const SnapHeader *hdr;
+    uint32_t *chunk_done;              // [chunks] finished node segments per pod chunk (zeroed; grid.y > 1)
+    uint32_t *best_pos;                // [slots] merged best rank position (0xffffffff; grid.y > 1)
+    long long *out_idx;
+    double *out_score;
+};
+
+// #{i : arr[i] < x} in an ascending array
+__device__ __forceinline__ int lower_bound_lt(const double *arr, int n, double x)
+{
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (arr[mid] < x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ void group_begins(const SnapHeader *hdr, int chunk_pods,
+                                             long long begin[kMaxStrategies])
+{
+    long long o = 0;
+#pragma unroll
+    for (int s = 0; s < kMaxStrategies; ++s) {
+        begin[s] = o;
+        const long long c = hdr->group_count[s];
+        o += (c + chunk_pods - 1) / chunk_pods * chunk_pods;
+    }
+}
+
+// packed test + update on the FMA pipe: best_enc = pos * 1 + x   (decoded later as best_enc - x)
+__device__ __forceinline__ void swar_update(int &best_enc, uint32_t x, uint32_t w, int pos, int one)
+{
+    asm volatile(
+        "{ .reg .pred p; .reg .b32 t, d;\n"
+        "  sub.u32 t, %1, %2;\n"
+        "  lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0;\n"      // d = ~t & guards ; p = (d != 0) = does not fit
+        "  @!p mad.lo.s32 %0, %3, %4, %2; }"
+        : "+r"(best_enc) : "r"(w), "r"(x), "r"(pos), "r"(one));
+}
+
+// packed test + update on the ALU pipe (SEL): best = pos
+__device__ __forceinline__ void swar_update_alu(int &best, uint32_t x, uint32_t w, int pos)
+{
+    asm volatile(
+        "{ .reg .pred p; .reg .b32 t, d;\n"
+        "  sub.u32 t, %1, %2;\n"
+        "  lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0;\n"
+        "  @!p mov.s32 %0, %3; }"
+        : "+r"(best) : "r"(w), "r"(x), "r"(pos));
+}
+__device__ __forceinline__ constexpr bool update_on_fma(int r)
+{
+    return KP_UPDATE_MODE == 2 || (KP_UPDATE_MODE == 1 && (r & 1));
+}
+__device__ __forceinline__ void swar_step(int &best, uint32_t x, uint32_t w, int pos, int one, int r)
+{
+    if (update_on_fma(r)) swar_update(best, x, w, pos, one);
+    else swar_update_alu(best, x, w, pos);
+}
+
+template <int THREADS, int R, int NSPLIT>
+__global__ void __launch_bounds__(THREADS)
+place_kernel(const PlaceParams p)
+{
+    constexpr int W = THREADS / 32;
+    constexpr int PODW = W / NSPLIT;                         // pod-warps per CTA
+    constexpr int CHUNK = 32 * R * PODW;                     // pods per CTA
+    static_assert(PODW * NSPLIT == W, "warps must factor into pod-warps x node splits");
+
+    __shared__ __align__(128) unsigned char tiles[2][kTileBytes];
+    __shared__ uint64_t bars[2];
+    __shared__ int comb[NSPLIT > 1 ? NSPLIT : 1][NSPLIT > 1 ? CHUNK : 1];
+    __shared__ int s_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int podw = warp / NSPLIT, split = warp % NSPLIT;
+    const long long slot0 = (long long)blockIdx.x * CHUNK;
+    int s = p.uniform_strategy;
+    long long gbegin = 0, gcount = p.n_pods;
+    if (s < 0) {
+        long long begin[kMaxStrategies];
+        group_begins(p.hdr, CHUNK, begin);
+        s = 0;
+#pragma unroll
+        for (int g = 1; g < kMaxStrategies; ++g) if (slot0 >= begin[g]) s = g;
+        gbegin = begin[s];
+        gcount = p.hdr->group_count[s];
+    }
+    if (slot0 - gbegin >= gcount) return;                    // CTA-uniform
+
+    const int nvalid4 = ((int)p.hdr->nvalid[s] + 3) & ~3;
+    const bool swar = p.hdr->use_swar != 0;
+    const int da = (int)p.hdr->distinct[0], db = (int)p.hdr->distinct[1];
+    const int tile_nodes = swar ? kTileNodesPacked : kTileNodesWide;
+    const int elem = swar ? 4 : 8;
+    const int tiles_per_seg = swar ? (p.tiles_per_seg_wide + 1) / 2 : p.tiles_per_seg_wide;
+    const int ntiles_all = (nvalid4 + tile_nodes - 1) / tile_nodes;
+    const int t_lo = min(ntiles_all, (int)blockIdx.y * tiles_per_seg);          // this CTA's tiles [t_lo, t_hi)
+    const int t_hi = min(ntiles_all, t_lo + tiles_per_seg);
+    const unsigned char *table = swar ? reinterpret_cast<const unsigned char *>(p.packed + (size_t)s * p.npad)
+                                      : reinterpret_cast<const unsigned char *>(p.ab + (size_t)s * p.npad);
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+
+    // ---- pod prologue: requests -> dense threshold ranks (exact, see kp_snapshot.cu) ----
+    const double *ua = p.uniq, *ub = p.uniq + p.npad;
+    const bool stage = da <= kTileBytes / 8 && db <= kTileBytes / 8;
+    if (stage) {        // both unique-threshold arrays fit the (still unused) tile buffers
+        double *sa = reinterpret_cast<double *>(tiles[0]);
+        double *sb = reinterpret_cast<double *>(tiles[1]);
+        for (int i = tid; i < da; i += THREADS) sa[i] = ua[i];
+        for (int i = tid; i < db; i += THREADS) sb[i] = ub[i];
+        ua = sa;
+        ub = sb;
+    }
+    __syncthreads();
+    uint32_t ra[R], rb[R];
+    bool live[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const long long slot = slot0 + (podw * R + r) * 32 + lane;
+        live[r] = slot - gbegin < gcount;
+        ra[r] = rb[r] = 0;
+        if (live[r]) {
+            const long long pod = p.perm ? (long long)p.perm[slot] : slot;
+            ra[r] = (uint32_t)lower_bound_lt(ua, da, req_cores(p.req_cpu[pod]));
+            rb[r] = (uint32_t)lower_bound_lt(ub, db, req_gib(p.req_mem[pod]));
+        }
+    }
+    if (stage) {
+        // generic-proxy accesses to the buffers are done; order them before the async-proxy writes
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto tile_count = [&](int t) { return min(tile_nodes, nvalid4 - t * tile_nodes); };
+    if (tid == 0 && t_hi > t_lo) {
+        const int t = t_hi - 1;
+        const uint32_t bytes = (uint32_t)(tile_count(t) * elem);
+        mbar_expect_tx(&bars[0], bytes);
+        bulk_load(tiles[0], table + (size_t)t * tile_nodes * elem, bytes, &bars[0]);
+    }
+
+    int best[R];
+    if (swar) {
+        uint32_t x[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            x[r] = live[r] ? ((rb[r] + 1u) << 16) | (ra[r] + 1u) : kSwarDeadPod;
+            best[r] = update_on_fma(r) ? (int)x[r] - 1 : -1;  // FMA form holds pos + x; pos = -1
+        }
+        int it = 0;
+        for (int t = t_hi - 1; t >= t_lo; --t, ++it) {
+            const int buf = it & 1;
+            if (tid == 0 && t > t_lo) {
+                const uint32_t bytes = (uint32_t)(tile_count(t - 1) * elem);
+                mbar_expect_tx(&bars[buf ^ 1], bytes);
+                bulk_load(tiles[buf ^ 1], table + (size_t)(t - 1) * tile_nodes * elem, bytes, &bars[buf ^ 1]);
+            }
+            mbar_wait(&bars[buf], (uint32_t)(it >> 1) & 1u);
+            const uint4 *tp = reinterpret_cast<const uint4 *>(tiles[buf]);
+            const int base = t * tile_nodes;
+            const int nquad = tile_count(t) >> 2;
+            const int q0 = NSPLIT > 1 ? (nquad * split) / NSPLIT : 0;
+            const int q1 = NSPLIT > 1 ? (nquad * (split + 1)) / NSPLIT : nquad;
+#pragma unroll(R >= 8 ? 1 : 2)
+            for (int i = q1 - 1; i >= q0; --i) {
+                const uint4 v = tp[i];                       // four nodes, same address in every lane
+                const int pos = base + 4 * i;
+#pragma unroll
+                for (int r = 0; r < R; ++r) swar_step(best[r], x[r], v.w, pos + 3, p.one, r);
+#pragma unroll
+                for (int r = 0; r < R; ++r) swar_step(best[r], x[r], v.z, pos + 2, p.one, r);
+#pragma unroll
+                for (int r = 0; r < R; ++r) swar_step(best[r], x[r], v.y, pos + 1, p.one, r);
+#pragma unroll
+                for (int r = 0; r < R; ++r) swar_step(best[r], x[r], v.x, pos, p.one, r);
+            }
+            __syncthreads();                                 // buffer free for the next prefetch
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) if (update_on_fma(r)) best[r] -= (int)x[r];
+    } else {
+        int a[R], b[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            a[r] = live[r] ? (int)ra[r] : 0x7fffffff;
+            b[r] = live[r] ? (int)rb[r] : 0x7fffffff;
+            best[r] = -1;
+        }
+        int it = 0;
+        for (int t = t_hi - 1; t >= t_lo; --t, ++it) {
+            const int buf = it & 1;
+            if (tid == 0 && t > t_lo) {
+                const uint32_t bytes = (uint32_t)(tile_count(t - 1) * elem);
+                mbar_expect_tx(&bars[buf ^ 1], bytes);
+                bulk_load(tiles[buf ^ 1], table + (size_t)(t - 1) * tile_nodes * elem, bytes, &bars[buf ^ 1]);
+            }
+            mbar_wait(&bars[buf], (uint32_t)(it >> 1) & 1u);
+            const uint4 *tp = reinterpret_cast<const uint4 *>(tiles[buf]);
+            const int base = t * tile_nodes;
+            const int npair = tile_count(t) >> 1;
+            const int q0 = NSPLIT > 1 ? (npair * split) / NSPLIT : 0;
+            const int q1 = NSPLIT > 1 ? (npair * (split + 1)) / NSPLIT : npair;
+#pragma unroll 2
+            for (int i = q1 - 1; i >= q0; --i) {
+                const uint4 v = tp[i];                       // two nodes
+                const int pos = base + 2 * i;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (a[r] <= (int)v.z && b[r] <= (int)v.w) best[r] = pos + 1;
+                    if (a[r] <= (int)v.x && b[r] <= (int)v.y) best[r] = pos;
+                }
+            }
+            __syncthreads();
+        }
+    }
+
+    // ---- merge the node splits of this CTA (minimum rank position wins) ----
+    if (NSPLIT > 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            comb[split][(podw * R + r) * 32 + lane] = best[r] >= 0 ? best[r] : 0x7fffffff;
+        __syncthreads();
+        if (split == 0) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                int m = 0x7fffffff;
+#pragma unroll
+                for (int q = 0; q < NSPLIT; ++q) m = min(m, comb[q][(podw * R + r) * 32 + lane]);
+                best[r] = m == 0x7fffffff ? -1 : m;
+            }
+        }
+    }
+
+    // ---- merge the node segments (grid.y) through global memory ----
+    if (gridDim.y > 1) {
+        if (split == 0) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (live[r] && best[r] >= 0)
+                    atomicMin(p.best_pos + slot0 + (podw * R + r) * 32 + lane, (uint32_t)best[r]);
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_last = atomicAdd(p.chunk_done + blockIdx.x, 1u) == gridDim.y - 1;
+        __syncthreads();
+        if (!s_last) return;                                 // another segment's CTA will finish this chunk
+        __threadfence();
+        if (split == 0) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint32_t bp = *reinterpret_cast<volatile uint32_t *>(p.best_pos + slot0 + (podw * R + r) * 32 + lane);
+                best[r] = bp == kNoPos ? -1 : (int)bp;
+            }
+        }
+    }
+
+    // ---- epilogue: rank position -> node index and score ----
+    if (split != 0) return;
+    const uint32_t *order = p.order + (size_t)s * p.npad;
+    const double *score = p.score + (size_t)s * p.n_nodes;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (!live[r]) continue;
+        const long long slot = slot0 + (podw * R + r) * 32 + lane;
+        const long long pod = p.perm ? (long long)p.perm[slot] : slot;
+        long long idx = -1;
+        double sc = -1.0;
+        if (best[r] >= 0) {
+            idx = order[best[r]];
+            sc = score[idx];
+        }
+        p.out_idx[pod] = idx;
+        p.out_score[pod] = sc;
+    }
+}
+
+}  // namespace kp
