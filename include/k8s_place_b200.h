@@ -124,10 +124,8 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
  * scratch is a fixed 2 MiB array inside the library's device image (resident on every
  * GPU that loads the library, until the process exits), so the call allocates nothing.
  *
- * Limits: n_nodes <= 8192; n_pods <= 65536 when pods->strategy_ids is set or the table has
- * more than 4096 nodes (those calls keep per-pod scratch); a uniform strategy over at most
- * 4096 nodes has no pod limit.  Larger calls return KP_ERR_CAPACITY with a message and do
- * no work.
+ * Limits: n_nodes <= 8192; with pods->strategy_ids set, n_pods <= 65536 (no pod limit for
+ * a uniform strategy).  Larger calls return KP_ERR_CAPACITY with a message and do no work.
  *
  * The first call on each device looks up the array's device address (the device that is
  * current at the call); make that first call before starting any stream capture.  All

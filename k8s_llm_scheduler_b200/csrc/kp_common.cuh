@@ -53,10 +53,16 @@ __device__ __forceinline__ double free_cpu_cores(long long alloc_milli, double c
     const double avail = __ddiv_rn((double)alloc_milli, 1000.0);
     return __ddiv_rn(__dmul_rn(avail, __dsub_rn(100.0, cu)), 100.0);
 }
+// bytes / 1024 / 1024 / 1024: each division by a power of two is exact for |bytes| < 2^53
+// (no underflow: the smallest non-zero magnitude is 2^-30), so the three divisions equal ONE
+// multiplication by 2^-30 bit for bit -- one instruction instead of three division sequences.
+__device__ __forceinline__ double bytes_to_gib(long long bytes)
+{
+    return __dmul_rn((double)bytes, 9.31322574615478515625e-10);   // 2^-30
+}
 __device__ __forceinline__ double free_mem_gib(long long alloc_bytes, double mu)
 {
-    const double avail =
-        __ddiv_rn(__ddiv_rn(__ddiv_rn((double)alloc_bytes, 1024.0), 1024.0), 1024.0);
+    const double avail = bytes_to_gib(alloc_bytes);
     return __ddiv_rn(__dmul_rn(avail, __dsub_rn(100.0, mu)), 100.0);
 }
 // pod request in the reference's units (scheduler.py:742-753, single quantity)
@@ -66,7 +72,7 @@ __device__ __forceinline__ double req_cores(long long milli)
 }
 __device__ __forceinline__ double req_gib(long long bytes)
 {
-    return __ddiv_rn(__ddiv_rn(__ddiv_rn((double)bytes, 1024.0), 1024.0), 1024.0);
+    return bytes_to_gib(bytes);
 }
 
 __host__ __device__ __forceinline__ int canon_strategy(long long sid)

@@ -11,13 +11,17 @@
 // This is a P-step dependent chain, so it is latency-bound, not throughput-bound.  One
 // persistent CTA of 1024 threads owns the whole node table: every thread keeps the "hot"
 // state of its nodes in registers (the two capacity thresholds as fp64 and one
-// order-preserving 64-bit score key per strategy in play); pods are staged through shared
-// memory in batches.  Per pod: every thread tests its nodes (2 fp64 compares + 1 key
-// compare each), a warp-level then block-level (key desc, index asc) reduction finds the
-// winner with ONE block barrier, and the owning thread commits -- recomputing that node's
-// usage, score key and thresholds with the same exact-fp64 routines as the snapshot path.
-// Tables larger than the register budget use the same kernel with the hot state in
-// global memory (slower; a thread-block-cluster version is the planned replacement).
+// order-preserving 64-bit score key per strategy in play); the "cold" per-node constants a
+// commit needs (available cores / GiB, max_pods, pod_count) sit in shared memory; pods are
+// staged through shared memory in batches.  Per pod: every thread tests its nodes (2 fp64
+// compares + 1 key compare each), a warp-level then block-level (key desc, index asc)
+// reduction built from hardware REDUX finds the winner with ONE block barrier, and the owning
+// thread commits: it recomputes that node's usage, thresholds and score key with the same
+// exact-fp64 operation sequence as the snapshot path (cu == mu after a commit, so the shared
+// sub-expression 100 - usage is computed once; the dependent chain is two divisions deep).
+// Usage outputs are derived once at the end from the final pod counts.  Tables beyond the
+// register budget use the same kernel with the hot state in global memory (slower; a
+// thread-block-cluster version is the planned replacement).
 #include <algorithm>
 
 #include "kp_common.cuh"
@@ -26,6 +30,8 @@ namespace kp {
 
 constexpr int kGreedyThreads = 1024;
 constexpr int kPodBatch = 1024;
+constexpr int kGreedyColdBytes = 32;          // per node in shared memory: avail_cpu, avail_mem, max_pods, pod_count
+constexpr int kGreedySmemNodes = 6144;        // cold state fits shared memory up to here (192 KB)
 
 struct GreedyParams {
     const long long *alloc_cpu, *alloc_mem, *pod_count0, *max_pods;
@@ -36,9 +42,9 @@ struct GreedyParams {
     long long n_pods;
     int uniform_strategy;
     int capacity;
-    // mutable state (workspace)
-    long long *pc;
-    double *cu, *mu;
+    // cold state when it does not fit shared memory: [n] each
+    double *g_avail_cpu, *g_avail_mem;
+    long long *g_pc;
     // spilled hot state (only used by the NPT == 0 variant): [n] each
     double *g_ta, *g_tb;
     unsigned long long *g_key;   // [3][n]
@@ -53,24 +59,65 @@ struct Hot {
     unsigned long long key[kMaxStrategies];
 };
 
-// Hot state of one node from its current (pc, mp, usage); key 0 = cannot be chosen.
+struct Cold {               // per-node constants + the mutable pod count
+    double *avail_cpu, *avail_mem;
+    long long *mp, *pc;
+};
+
+// hot state from (pc, mp, cu, mu): initial table, arbitrary usage values (scheduler.py:150-151
+// need not hold for the caller's table)
 template <bool MULTI>
-__device__ __forceinline__ Hot make_hot(const GreedyParams &g, int n, long long pc, double cu,
-                                        double mu)
+__device__ __forceinline__ Hot hot_initial(const GreedyParams &g, int n, double avail_cpu, double avail_mem,
+                                           long long pc, long long mp, double cu, double mu)
 {
     Hot h;
-    const long long mp = g.max_pods[n];
     bool ok = g.ready[n] != 0;
     h.ta = h.tb = __longlong_as_double(0x7ff0000000000000ll);
     if (g.capacity) {
-        h.ta = free_cpu_cores(g.alloc_cpu[n], cu);
-        h.tb = free_mem_gib(g.alloc_mem[n], mu);
+        h.ta = __ddiv_rn(__dmul_rn(avail_cpu, __dsub_rn(100.0, cu)), 100.0);     // scheduler.py:232
+        h.tb = __ddiv_rn(__dmul_rn(avail_mem, __dsub_rn(100.0, mu)), 100.0);     // scheduler.py:233
         ok = ok && pc < mp;            // NaN thresholds fail the compares on their own
     }
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {
-        if (!MULTI && s != g.uniform_strategy) { h.key[s] = 0ull; continue; }
-        h.key[s] = ok ? node_score(s, cu, mu, pc, mp).key : 0ull;
+        h.key[s] = 0ull;
+        if (!MULTI && s != g.uniform_strategy) continue;
+        if (ok) h.key[s] = node_score(s, cu, mu, pc, mp).key;
+    }
+    return h;
+}
+
+// hot state after a commit: cu == mu == (pc / mp) * 50, so 100 - usage is shared.  Every
+// value is produced by the same operation sequence as free_cpu_cores / free_mem_gib /
+// score_resource_balanced / score_least_loaded would produce from (cu, mu) = (u, u).
+template <bool MULTI>
+__device__ __forceinline__ Hot hot_after_commit(const GreedyParams &g, double avail_cpu, double avail_mem,
+                                                long long pc, long long mp)
+{
+    Hot h;
+    const double u = usage_a3(pc, mp);
+    const double hm = __dsub_rn(100.0, u);
+    bool ok = true;                                   // the node was just chosen, so it is Ready
+    h.ta = h.tb = __longlong_as_double(0x7ff0000000000000ll);
+    if (g.capacity) {
+        h.ta = __ddiv_rn(__dmul_rn(avail_cpu, hm), 100.0);
+        h.tb = __ddiv_rn(__dmul_rn(avail_mem, hm), 100.0);
+        ok = pc < mp;
+    }
+    h.key[0] = h.key[1] = h.key[2] = 0ull;
+    if (ok) {
+        if (MULTI || g.uniform_strategy == 0) {
+            const double cs = __ddiv_rn(hm, 100.0);
+            const double ps = mp > 0 ? __ddiv_rn((double)(mp - pc), (double)mp) : 0.0;
+            const double a = __dmul_rn(cs, 0.35);
+            const double sc = __dadd_rn(__dadd_rn(a, a), __dmul_rn(ps, 0.30));       // scheduler.py:541
+            h.key[0] = sc > -1.0 ? f64_order_key(sc) : 0ull;
+        }
+        if (MULTI || g.uniform_strategy == 1) {
+            const double sc = __dadd_rn(hm, hm);                                       // scheduler.py:543
+            h.key[1] = sc > -1.0 ? f64_order_key(sc) : 0ull;
+        }
+        if (MULTI || g.uniform_strategy == 2) h.key[2] = pc > -1 ? i64_order_key(pc) : 0ull;   // :545
     }
     return h;
 }
@@ -94,10 +141,12 @@ __device__ __forceinline__ void warp_argmax(unsigned long long &key, uint32_t &i
 }
 
 // NPT > 0: hot state of nodes {k * 1024 + tid} in registers.  NPT == 0: hot state in global memory.
-template <int NPT, bool MULTI>
+// SMEM_COLD: cold state in dynamic shared memory (n <= kGreedySmemNodes), else in global memory.
+template <int NPT, bool MULTI, bool SMEM_COLD>
 __global__ void __launch_bounds__(kGreedyThreads, 1)
 greedy_kernel(const GreedyParams g)
 {
+    extern __shared__ __align__(16) unsigned char cold_raw[];
     __shared__ double s_a[kPodBatch], s_b[kPodBatch];
     __shared__ int s_s[kPodBatch];
     __shared__ unsigned long long w_key[2][32];
@@ -109,32 +158,48 @@ greedy_kernel(const GreedyParams g)
     double ta[NREG], tb[NREG];
     unsigned long long key[KS][NREG];
 
+    Cold c;
+    if (SMEM_COLD) {
+        c.avail_cpu = reinterpret_cast<double *>(cold_raw);
+        c.avail_mem = c.avail_cpu + g.n_nodes;
+        c.mp = reinterpret_cast<long long *>(c.avail_mem + g.n_nodes);
+        c.pc = c.mp + g.n_nodes;
+    } else {
+        c.avail_cpu = g.g_avail_cpu;
+        c.avail_mem = g.g_avail_mem;
+        c.mp = const_cast<long long *>(g.max_pods);
+        c.pc = g.g_pc;
+    }
+    const int us = g.uniform_strategy;
+
     // ---- initial state ----
     const int per_thread = NPT > 0 ? NPT : (g.n_nodes + kGreedyThreads - 1) / kGreedyThreads;
-    for (int k = 0; k < per_thread; ++k) {
-        const int n = k * kGreedyThreads + tid;
-        Hot h;
-        h.ta = h.tb = 0.0;
-        h.key[0] = h.key[1] = h.key[2] = 0ull;
-        if (n < g.n_nodes) {
-            const long long pc = g.pod_count0[n];
-            const double cu = g.cu0[n], mu = g.mu0[n];
-            g.pc[n] = pc; g.cu[n] = cu; g.mu[n] = mu;
-            h = make_hot<MULTI>(g, n, pc, cu, mu);
-        }
-        if (NPT > 0) {
 #pragma unroll
-            for (int kk = 0; kk < NREG; ++kk) {
-                if (kk == k) {
-                    ta[kk] = h.ta; tb[kk] = h.tb;
-#pragma unroll
-                    for (int s = 0; s < KS; ++s) key[s][kk] = h.key[MULTI ? s : g.uniform_strategy];
-                }
+    for (int k = 0; k < (NPT > 0 ? NPT : 1); ++k) {
+        for (int kk = k; kk < per_thread; kk += (NPT > 0 ? per_thread : 1)) {
+            const int n = kk * kGreedyThreads + tid;
+            Hot h;
+            h.ta = h.tb = 0.0;
+            h.key[0] = h.key[1] = h.key[2] = 0ull;
+            if (n < g.n_nodes) {
+                const long long pc = g.pod_count0[n], mp = g.max_pods[n];
+                const double avail_cpu = __ddiv_rn((double)g.alloc_cpu[n], 1000.0);                       // :174-175
+                const double avail_mem = bytes_to_gib(g.alloc_mem[n]);                                  // :187
+                c.avail_cpu[n] = avail_cpu;
+                c.avail_mem[n] = avail_mem;
+                if (SMEM_COLD) c.mp[n] = mp;
+                c.pc[n] = pc;
+                h = hot_initial<MULTI>(g, n, avail_cpu, avail_mem, pc, mp, g.cu0[n], g.mu0[n]);
             }
-        } else if (n < g.n_nodes) {
-            g.g_ta[n] = h.ta; g.g_tb[n] = h.tb;
+            if (NPT > 0) {
+                ta[k] = h.ta; tb[k] = h.tb;
+                if (MULTI) { key[0][k] = h.key[0]; key[KS > 1 ? 1 : 0][k] = h.key[1]; key[KS > 2 ? 2 : 0][k] = h.key[2]; }
+                else key[0][k] = us == 0 ? h.key[0] : (us == 1 ? h.key[1] : h.key[2]);
+            } else if (n < g.n_nodes) {
+                g.g_ta[n] = h.ta; g.g_tb[n] = h.tb;
 #pragma unroll
-            for (int s = 0; s < kMaxStrategies; ++s) g.g_key[(size_t)s * g.n_nodes + n] = h.key[s];
+                for (int s = 0; s < kMaxStrategies; ++s) g.g_key[(size_t)s * g.n_nodes + n] = h.key[s];
+            }
         }
     }
     __syncthreads();
@@ -145,7 +210,7 @@ greedy_kernel(const GreedyParams g)
         if (tid < cnt) {
             s_a[tid] = req_cores(g.req_cpu[base + tid]);
             s_b[tid] = req_gib(g.req_mem[base + tid]);
-            s_s[tid] = g.sid ? canon_strategy(g.sid[base + tid]) : g.uniform_strategy;
+            s_s[tid] = g.sid ? canon_strategy(g.sid[base + tid]) : us;
         }
         __syncthreads();
         for (int j = 0; j < cnt; ++j) {
@@ -184,21 +249,18 @@ greedy_kernel(const GreedyParams g)
             }
             if ((int)(bi % kGreedyThreads) == tid) {
                 const int n = (int)bi;
-                g.out_idx[base + j] = n;
-                g.out_score[base + j] = key_score(s, bk);
                 // commit (scheduler.py:598 -> :144-151)
-                const long long pc = g.pc[n] + 1;
-                const double u = usage_a3(pc, g.max_pods[n]);
-                g.pc[n] = pc; g.cu[n] = u; g.mu[n] = u;
-                const Hot h = make_hot<MULTI>(g, n, pc, u, u);
+                const long long pc = c.pc[n] + 1;
+                c.pc[n] = pc;
+                const Hot h = hot_after_commit<MULTI>(g, c.avail_cpu[n], c.avail_mem[n], pc, c.mp[n]);
                 if (NPT > 0) {
                     const int k = n / kGreedyThreads;
 #pragma unroll
                     for (int kk = 0; kk < NREG; ++kk) {
                         if (kk == k) {
                             ta[kk] = h.ta; tb[kk] = h.tb;
-#pragma unroll
-                            for (int q = 0; q < KS; ++q) key[q][kk] = h.key[MULTI ? q : g.uniform_strategy];
+                            if (MULTI) { key[0][kk] = h.key[0]; key[KS > 1 ? 1 : 0][kk] = h.key[1]; key[KS > 2 ? 2 : 0][kk] = h.key[2]; }
+                            else key[0][kk] = us == 0 ? h.key[0] : (us == 1 ? h.key[1] : h.key[2]);
                         }
                     }
                 } else {
@@ -206,30 +268,36 @@ greedy_kernel(const GreedyParams g)
 #pragma unroll
                     for (int q = 0; q < kMaxStrategies; ++q) g.g_key[(size_t)q * g.n_nodes + n] = h.key[q];
                 }
+                g.out_idx[base + j] = n;
+                g.out_score[base + j] = key_score(s, bk);
             }
             if (NPT == 0) __syncthreads();     // global hot state must be visible to the block
         }
     }
     __syncthreads();
+    // final state: usage follows scheduler.py:150-151 for every node that received a pod
     for (int n = tid; n < g.n_nodes; n += kGreedyThreads) {
-        if (g.out_pc) g.out_pc[n] = g.pc[n];
-        if (g.out_cu) g.out_cu[n] = g.cu[n];
-        if (g.out_mu) g.out_mu[n] = g.mu[n];
+        const long long pc = c.pc[n];
+        const bool touched = pc != g.pod_count0[n];
+        const double u = usage_a3(pc, g.max_pods[n]);
+        if (g.out_pc) g.out_pc[n] = pc;
+        if (g.out_cu) g.out_cu[n] = touched ? u : g.cu0[n];
+        if (g.out_mu) g.out_mu[n] = touched ? u : g.mu0[n];
     }
 }
 
-// workspace: pc[n] i64 | cu[n] f64 | mu[n] f64 | g_ta[n] | g_tb[n] | g_key[3][n]
-struct GreedyLayout { size_t off_pc, off_cu, off_mu, off_ta, off_tb, off_key, total; };
+// workspace: avail_cpu[n] | avail_mem[n] | pc[n] | g_ta[n] | g_tb[n] | g_key[3][n]
+struct GreedyLayout { size_t off_acpu, off_amem, off_pc, off_ta, off_tb, off_key, total; };
 static GreedyLayout greedy_layout(int64_t n)
 {
     GreedyLayout L{};
     size_t o = 0;
-    L.off_pc = o;  o = align_up(o + sizeof(long long) * n);
-    L.off_cu = o;  o = align_up(o + sizeof(double) * n);
-    L.off_mu = o;  o = align_up(o + sizeof(double) * n);
-    L.off_ta = o;  o = align_up(o + sizeof(double) * n);
-    L.off_tb = o;  o = align_up(o + sizeof(double) * n);
-    L.off_key = o; o = align_up(o + sizeof(unsigned long long) * kMaxStrategies * n);
+    L.off_acpu = o; o = align_up(o + sizeof(double) * n);
+    L.off_amem = o; o = align_up(o + sizeof(double) * n);
+    L.off_pc = o;   o = align_up(o + sizeof(long long) * n);
+    L.off_ta = o;   o = align_up(o + sizeof(double) * n);
+    L.off_tb = o;   o = align_up(o + sizeof(double) * n);
+    L.off_key = o;  o = align_up(o + sizeof(unsigned long long) * kMaxStrategies * n);
     L.total = std::max<size_t>(o, kAlign);
     return L;
 }
@@ -243,7 +311,18 @@ size_t greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods)
 template <int NPT, bool MULTI>
 static int launch_greedy(const GreedyParams &g, cudaStream_t stream)
 {
-    greedy_kernel<NPT, MULTI><<<1, kGreedyThreads, 0, stream>>>(g);
+    if (g.n_nodes <= kGreedySmemNodes) {
+        const size_t smem = (size_t)kGreedyColdBytes * g.n_nodes;
+        static size_t attr_bytes = 0;
+        if (smem > attr_bytes) {
+            KP_CUDA(cudaFuncSetAttribute(greedy_kernel<NPT, MULTI, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kGreedyColdBytes * kGreedySmemNodes));
+            attr_bytes = (size_t)kGreedyColdBytes * kGreedySmemNodes;
+        }
+        greedy_kernel<NPT, MULTI, true><<<1, kGreedyThreads, smem, stream>>>(g);
+    } else {
+        greedy_kernel<NPT, MULTI, false><<<1, kGreedyThreads, 0, stream>>>(g);
+    }
     KP_LAUNCH_CHECK("greedy_kernel");
     return KP_OK;
 }
@@ -276,9 +355,9 @@ int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, in
     g.n_pods = pods.n_pods;
     g.uniform_strategy = canon_strategy(strategy);
     g.capacity = filter_mode == KP_FILTER_CAPACITY;
-    g.pc = reinterpret_cast<long long *>(w + L.off_pc);
-    g.cu = reinterpret_cast<double *>(w + L.off_cu);
-    g.mu = reinterpret_cast<double *>(w + L.off_mu);
+    g.g_avail_cpu = reinterpret_cast<double *>(w + L.off_acpu);
+    g.g_avail_mem = reinterpret_cast<double *>(w + L.off_amem);
+    g.g_pc = reinterpret_cast<long long *>(w + L.off_pc);
     g.g_ta = reinterpret_cast<double *>(w + L.off_ta);
     g.g_tb = reinterpret_cast<double *>(w + L.off_tb);
     g.g_key = reinterpret_cast<unsigned long long *>(w + L.off_key);
@@ -294,8 +373,8 @@ int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, in
     if (!multi) {
         if (npt <= 1) return launch_greedy<1, false>(g, stream);
         if (npt <= 2) return launch_greedy<2, false>(g, stream);
-        if (npt <= 4) return launch_greedy<4, false>(g, stream);
-        if (npt <= 6) return launch_greedy<6, false>(g, stream);
+        if (npt <= 3) return launch_greedy<3, false>(g, stream);
+        if (npt <= 5) return launch_greedy<5, false>(g, stream);
         return launch_greedy<0, false>(g, stream);
     }
     if (npt <= 1) return launch_greedy<1, true>(g, stream);

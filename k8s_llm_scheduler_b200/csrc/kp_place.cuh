@@ -32,7 +32,7 @@ namespace kp {
 #define KP_TILE_BYTES 8192
 #endif
 #ifndef KP_UPDATE_MODE
-#define KP_UPDATE_MODE 2      // candidate update: 0 = SEL (ALU pipe), 1 = alternate per pod, 2 = guarded IMAD (FMA pipe)
+#define KP_UPDATE_MODE 1      // candidate update: 0 = SEL (ALU pipe), 1 = alternate per pod, 2 = guarded IMAD (FMA pipe)
 #endif
 constexpr int kTileBytes = KP_TILE_BYTES;              // per shared-memory tile buffer
 constexpr int kTileNodesPacked = kTileBytes / 4;       // 2048
@@ -115,7 +115,7 @@ __device__ __forceinline__ void swar_step(int &best, uint32_t x, uint32_t w, int
 }
 
 template <int THREADS, int R, int NSPLIT>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (NSPLIT > 1 && R < 8) ? 6 : 3)
 place_kernel(const PlaceParams p)
 {
     constexpr int W = THREADS / 32;
@@ -176,12 +176,32 @@ place_kernel(const PlaceParams p)
     __syncthreads();
     uint32_t ra[R], rb[R];
     bool live[R];
+    if (NSPLIT > 1) {
+        // the NSPLIT warps that share a pod would each repeat its division + binary searches:
+        // compute every (pod, dimension) rank once per CTA and hand it over in shared memory
+        for (int item = tid; item < 2 * CHUNK; item += THREADS) {
+            const int q = item % CHUNK, dim = item / CHUNK;
+            const long long slot = slot0 + q;
+            uint32_t rk = 0;
+            if (slot - gbegin < gcount) {
+                const long long pod = p.perm ? (long long)p.perm[slot] : slot;
+                rk = dim == 0 ? (uint32_t)lower_bound_lt(ua, da, req_cores(p.req_cpu[pod]))
+                              : (uint32_t)lower_bound_lt(ub, db, req_gib(p.req_mem[pod]));
+            }
+            comb[dim][q] = (int)rk;                          // comb is free until the merge step
+        }
+        __syncthreads();
+    }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const long long slot = slot0 + (podw * R + r) * 32 + lane;
+        const int q = (podw * R + r) * 32 + lane;
+        const long long slot = slot0 + q;
         live[r] = slot - gbegin < gcount;
         ra[r] = rb[r] = 0;
-        if (live[r]) {
+        if (NSPLIT > 1) {
+            ra[r] = (uint32_t)comb[0][q];
+            rb[r] = (uint32_t)comb[1][q];
+        } else if (live[r]) {
             const long long pod = p.perm ? (long long)p.perm[slot] : slot;
             ra[r] = (uint32_t)lower_bound_lt(ua, da, req_cores(p.req_cpu[pod]));
             rb[r] = (uint32_t)lower_bound_lt(ub, db, req_gib(p.req_mem[pod]));

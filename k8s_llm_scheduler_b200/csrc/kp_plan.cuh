@@ -14,11 +14,9 @@
 //     into ONE 32-bit word with a guard bit above each 15-bit field.
 //
 // Two implementations:
-//   plan_small_kernel  (<= 4096 nodes) ONE launch of a thread-block CLUSTER with one CTA per
-//                      independent sort (free-cpu ranks, free-mem ranks, one per strategy);
-//                      bitonic sorts held in registers (warp shuffles below distance 32,
-//                      shared memory above); rank arrays cross CTAs through global memory
-//                      over a cluster barrier.
+//   small tables       (<= 8192 nodes) derive + plan_count_kernel: no sort -- every node counts
+//                      its own sorted position against the whole table, in parallel over the
+//                      whole GPU; plain "number of smaller thresholds" ranks (no dense pass).
 //   multi-kernel path  (any size) derive -> counting rank -> sorted thresholds -> dense ranks
 //                      -> tables.
 #pragma once
@@ -32,7 +30,7 @@ namespace kp {
 namespace cg = cooperative_groups;
 
 constexpr int kKeyArrays = kMaxStrategies + 2;   // 3 score orders + cpu threshold + mem threshold
-constexpr int kSmallMaxNodes = 4096;             // plan_small_kernel limit
+constexpr int kSmallMaxNodes = 8192;             // plan_count_kernel limit (one key array in shared memory)
 constexpr uint32_t kSwarMaxDistinct = 32000;     // fields hold rank+1 <= 32001 < 0x7fff
 
 struct NodePtrs {
@@ -96,7 +94,6 @@ struct PlanOut {
     uint32_t *order;    // [3][npad]
     uint2 *ab;          // [3][npad]
     uint32_t *packed;   // [3][npad]
-    uint32_t *rank;     // [2][npad] dense threshold rank per node (small plan: exchanged between CTAs)
     int npad;
 };
 
@@ -129,188 +126,125 @@ __device__ __forceinline__ uint32_t block_exclusive_1024(uint32_t cnt, uint32_t 
 }
 
 // ---------------------------------------------------------------------------------------
-// plan_small_kernel
+// small-table plan (n <= kSmallMaxNodes): derive_kernel<false> + plan_count_kernel
 // ---------------------------------------------------------------------------------------
-// Bitonic sort of m = 1024 * E (key, idx) pairs, E in {1, 2, 4}.  Thread t holds elements
-// e * 1024 + t in registers.  Compare-exchange partners at distance j are: another element of
-// the same thread (j >= 1024), the same element slot of a lane in the same warp (j < 32:
-// __shfl_xor), or of another warp (32 <= j < 1024: through shared memory, double-buffered so
-// that one barrier per stage suffices).
-struct SmallSmem {
-    unsigned long long xkey[2][kSmallMaxNodes];   // exchange buffers for the cross-warp stages
-    uint16_t xidx[2][kSmallMaxNodes];
-    unsigned long long key[kSmallMaxNodes];       // sorted result
-    uint16_t idx[kSmallMaxNodes];
-    uint32_t warp_sums[32];
-    uint32_t total;
-};
+// No sort at all: every node finds its own place by counting, fully in parallel over the
+// whole GPU.  For a key array K (ascending order wanted, ties broken by node index):
+//     pos[n]  = #{m : K[m] < K[n]  or  (K[m] == K[n] and m < n)}      stable sorted position
+//     less[n] = #{m : K[m] < K[n]}                                     threshold rank
+// Below 32 k nodes the plain count `less` already fits the packed 15-bit rank fields, so no
+// dense-rank pass is needed: req <= thr[n]  <=>  #{m : thr[m] < req} <= less[n], with the pod
+// side found by binary search in the sorted threshold array (duplicates kept).
+//
+// A thread-block CLUSTER of 8 CTAs owns 32 nodes (one per lane).  Its 64 warps each count
+// over one 64th of the table (every lane reads the same key: broadcast loads) and add their
+// partial counts into the leader CTA's shared memory with distributed-shared-memory atomics;
+// after a cluster barrier the leader writes the nodes' entries of the sorted threshold arrays
+// and of every best-first table.  Cluster 0 also counts the eligible nodes per strategy and
+// writes the padding behind them.
+constexpr int kCountThreads = 256;
+constexpr int kCountNodes = 32;
+constexpr int kCountCluster = 8;
+constexpr int kCountChunks = kCountCluster * (kCountThreads / 32);
 
-// compare-exchange between two elements held by the same thread (distance JE * 1024)
-template <int E, int JE>
-__device__ __forceinline__ void in_thread_stage(unsigned long long (&key)[E], uint32_t (&idx)[E], int k)
+__device__ __forceinline__ void dsmem_add(cg::cluster_group &cluster, uint32_t *local, uint32_t v)
 {
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-        const int f = e ^ JE;
-        if (f > e && f < E) {
-            const int i = e * 1024 + (int)threadIdx.x;
-            const bool asc = (i & k) == 0;
-            const bool gt = key[e] > key[f] || (key[e] == key[f] && idx[e] > idx[f]);
-            if (gt == asc) {
-                const unsigned long long tk = key[e]; key[e] = key[f]; key[f] = tk;
-                const uint32_t ti = idx[e]; idx[e] = idx[f]; idx[f] = ti;
-            }
-        }
-    }
+    if (v) atomicAdd(cluster.map_shared_rank(local, 0), v);
 }
 
-template <int E>
-__device__ __forceinline__ void bitonic_sort_regs(unsigned long long (&key)[E], uint32_t (&idx)[E], SmallSmem &sm)
+__global__ void __cluster_dims__(kCountCluster, 1, 1) __launch_bounds__(kCountThreads)
+plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_mask, PlanOut o)
 {
-    const int tid = threadIdx.x;
-    int buf = 0;
-    constexpr int m = 1024 * E;
-    for (int k = 2; k <= m; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j >= 1024) {
-                if (E >= 4 && j == 2048) in_thread_stage<E, (E >= 4 ? 2 : 1)>(key, idx, k);
-                else in_thread_stage<E, 1>(key, idx, k);
-                continue;
-            }
-            if (j >= 32) {
-#pragma unroll
-                for (int e = 0; e < E; ++e) {
-                    sm.xkey[buf][e * 1024 + tid] = key[e];
-                    sm.xidx[buf][e * 1024 + tid] = (uint16_t)idx[e];
-                }
-                __syncthreads();
-            }
-#pragma unroll
-            for (int e = 0; e < E; ++e) {
-                const int i = e * 1024 + tid;
-                unsigned long long ok;
-                uint32_t oi;
-                if (j >= 32) {
-                    ok = sm.xkey[buf][i ^ j];
-                    oi = sm.xidx[buf][i ^ j];
-                } else {
-                    ok = __shfl_xor_sync(0xffffffffu, key[e], j);
-                    oi = __shfl_xor_sync(0xffffffffu, idx[e], j);
-                }
-                const bool lower = (i & j) == 0;             // lower partner keeps the smaller (if ascending)
-                const bool asc = (i & k) == 0;
-                const bool mine_gt = key[e] > ok || (key[e] == ok && idx[e] > oi);
-                if (mine_gt == (lower == asc)) { key[e] = ok; idx[e] = oi; }   // keep min iff lower == asc
-            }
-            if (j >= 32) buf ^= 1;
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-        sm.key[e * 1024 + tid] = key[e];
-        sm.idx[e * 1024 + tid] = (uint16_t)idx[e];
-    }
-    __syncthreads();
-}
+    __shared__ uint32_t acc_pos[kKeyArrays][kCountNodes];      // accumulated in the leader CTA only
+    __shared__ uint32_t acc_less[2][kCountNodes];
+    __shared__ uint32_t acc_live[kMaxStrategies];
 
-// One cluster, one CTA per sort.  CTA 0: free-cpu thresholds, CTA 1: free-memory thresholds,
-// CTA 2 + i: best-first order of the i-th strategy in strat_mask.
-template <int E>
-__global__ void __launch_bounds__(1024, 1)
-plan_small_kernel(NodePtrs t, int strat_mask, PlanOut o)
-{
-    extern __shared__ __align__(128) unsigned char plan_smem_raw[];
-    SmallSmem &sm = *reinterpret_cast<SmallSmem *>(plan_smem_raw);
     cg::cluster_group cluster = cg::this_cluster();
-    const int role = (int)cluster.block_rank();
-    const int tid = threadIdx.x;
-    const int n = t.n;
+    const int crank = (int)cluster.block_rank();
+    const int group = blockIdx.x / kCountCluster;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g0 = group * kCountNodes;
+    const int node = g0 + lane;
+    const int chunk = crank * (kCountThreads / 32) + warp;
+    const int m0 = (int)(((long long)n * chunk) / kCountChunks), m1 = (int)(((long long)n * (chunk + 1)) / kCountChunks);
 
-    int my_s = -1;                                   // strategy sorted by this CTA (role >= 2)
-    if (role >= 2) {
-        int seen = 0;
+    for (int i = tid; i < kKeyArrays * kCountNodes; i += kCountThreads) (&acc_pos[0][0])[i] = 0;
+    if (tid < 2 * kCountNodes) (&acc_less[0][0])[tid] = 0;
+    if (tid < kMaxStrategies) acc_live[tid] = 0;
+    cluster.sync();                                            // every CTA's accumulators are initialised
+
+    for (int j = kKeyArrays - 1; j >= 0; --j) {                // thresholds (3, 4), then strategies
+        if (j < kMaxStrategies && !(strat_mask & (1 << j))) continue;
+        const unsigned long long *K = keys + (size_t)j * n;
+        const unsigned long long kn = node < n ? K[node] : 0ull;
+        uint32_t c_pos = 0, c_less = 0;
+        if (m1 <= g0) {                                        // every m is below the node group: ties count
+#pragma unroll 8
+            for (int m = m0; m < m1; ++m) {
+                const unsigned long long km = K[m];            // same address in every lane
+                c_pos += km <= kn;
+                if (j >= kMaxStrategies) c_less += km < kn;
+            }
+        } else if (m0 >= g0 + kCountNodes) {                   // every m is above: ties do not count
+#pragma unroll 8
+            for (int m = m0; m < m1; ++m) c_pos += K[m] < kn;
+            c_less = c_pos;
+        } else {
+            for (int m = m0; m < m1; ++m) {
+                const unsigned long long km = K[m];
+                const uint32_t lt = km < kn;
+                c_less += lt;
+                c_pos += lt | (uint32_t)((km == kn) & (m < node));
+            }
+        }
+        dsmem_add(cluster, &acc_pos[j][lane], c_pos);
+        if (j >= kMaxStrategies) dsmem_add(cluster, &acc_less[j - kMaxStrategies][lane], c_less);
+        if (j < kMaxStrategies && group == 0) {                // eligible nodes of this strategy table
+            uint32_t live = 0;
+            for (int m = m0 + lane; m < m1; m += 32) live += K[m] != ~0ull;
 #pragma unroll
-        for (int s = 0; s < kMaxStrategies; ++s)
-            if (strat_mask & (1 << s)) { if (seen == role - 2) my_s = s; ++seen; }
+            for (int d = 16; d > 0; d >>= 1) live += __shfl_xor_sync(0xffffffffu, live, d);
+            if (lane == 0) dsmem_add(cluster, &acc_live[j], live);
+        }
     }
-
-    // derive the one key array this CTA sorts; element e * 1024 + tid lives in this thread
-    unsigned long long key[E];
-    uint32_t idx[E];
+    cluster.sync();                                            // all partial counts have landed in the leader
+    if (crank != 0) return;
+    if (group == 0) {
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-        const int i = e * 1024 + tid;
-        key[e] = ~0ull;
-        idx[e] = (uint32_t)i;
-        if (i < n) {
-            const Derived d = derive_node(t, i, role >= 2 ? (1 << my_s) : 0);
-            if (role < 2) key[e] = d.tkey[role];
-            else {
-                key[e] = d.skey[my_s];
-                o.score[(size_t)my_s * n + i] = d.score[my_s];
+        for (int s = 0; s < kMaxStrategies; ++s) {
+            if (!(strat_mask & (1 << s))) continue;
+            const int nv = (int)acc_live[s];
+            if (tid == 0) o.hdr->nvalid[s] = (uint32_t)nv;
+            for (int i = nv + tid; i < o.npad; i += kCountThreads) {   // padding behind the eligible nodes
+                o.ab[(size_t)s * o.npad + i] = make_uint2(0xffffffffu, 0xffffffffu);
+                o.packed[(size_t)s * o.npad + i] = kSwarGuards;
             }
         }
     }
-    if (role == 0) {
-        if (tid < kMaxStrategies) {
-            o.hdr->group_count[tid] = 0;
-            o.hdr->group_cursor[tid] = 0;
-            if (!(strat_mask & (1 << tid))) o.hdr->nvalid[tid] = 0;
-        }
-        if (tid == 0) { o.hdr->ticket = 0; o.hdr->use_swar = 1; o.hdr->reserved = 0; }
-    }
-    bitonic_sort_regs<E>(key, idx, sm);
-
-    if (role < 2) {
-        // dense ranks + unique values; each thread owns E contiguous sorted positions
-        const int i0 = tid * E;
-        uint32_t cnt = 0;
+    if (warp == 0 && node < n) {
+        const uint2 r = make_uint2(acc_less[0][lane], acc_less[1][lane]);
 #pragma unroll
-        for (int q = 0; q < E; ++q) {
-            const int i = i0 + q;
-            cnt += (i < n && (i == 0 || sm.key[i] != sm.key[i - 1])) ? 1u : 0u;
-        }
-        uint32_t run = block_exclusive_1024(cnt, sm.warp_sums, &sm.total);   // distinct values before i0
+        for (int jt = 0; jt < 2; ++jt)
+            o.uniq[(size_t)jt * o.npad + acc_pos[kMaxStrategies + jt][lane]] =
+                key_to_f64(keys[(size_t)(kMaxStrategies + jt) * n + node]);
 #pragma unroll
-        for (int q = 0; q < E; ++q) {
-            const int i = i0 + q;
-            if (i < n) {
-                const bool first = i == 0 || sm.key[i] != sm.key[i - 1];
-                if (first) { o.uniq[(size_t)role * o.npad + run] = key_to_f64(sm.key[i]); ++run; }
-                o.rank[(size_t)role * o.npad + sm.idx[i]] = run - 1;
-            }
+        for (int s = 0; s < kMaxStrategies; ++s) {
+            if (!(strat_mask & (1 << s))) continue;
+            if (keys[(size_t)s * n + node] == ~0ull) continue;            // ineligible: not in the table
+            const uint32_t p = acc_pos[s][lane];
+            o.order[(size_t)s * o.npad + p] = (uint32_t)node;
+            o.ab[(size_t)s * o.npad + p] = r;
+            o.packed[(size_t)s * o.npad + p] = pack_ranks(r.x, r.y);
         }
-        if (tid == 0) o.hdr->distinct[role] = sm.total;
-        __threadfence();
-    }
-    cluster.sync();                                  // rank arrays of CTAs 0 and 1 are now visible
-    if (role >= 2) {
-        const volatile uint32_t *rank_a = o.rank;
-        const volatile uint32_t *rank_b = o.rank + o.npad;
-        uint32_t mine = 0;
-        for (int i = tid; i < o.npad; i += 1024) {
-            const bool live = i < n && sm.key[i] != ~0ull;
-            uint2 r = make_uint2(0xffffffffu, 0xffffffffu);
-            uint32_t pk = kSwarGuards;                 // pad: fields 0 < every pod field
-            if (live) {
-                const uint32_t node = sm.idx[i];
-                r = make_uint2(rank_a[node], rank_b[node]);
-                pk = pack_ranks(r.x, r.y);
-                o.order[(size_t)my_s * o.npad + i] = node;
-                ++mine;
-            }
-            o.ab[(size_t)my_s * o.npad + i] = r;
-            o.packed[(size_t)my_s * o.npad + i] = pk;
-        }
-        (void)block_exclusive_1024(mine, sm.warp_sums, &sm.total);
-        if (tid == 0) o.hdr->nvalid[my_s] = sm.total;
     }
 }
 
 // ---------------------------------------------------------------------------------------
 // multi-kernel plan (any n)
 // ---------------------------------------------------------------------------------------
+// COUNT: accumulate the eligible-node counts with atomics (header zeroed beforehand); the
+// small-table path instead initialises the header here and counts in plan_count_kernel.
+template <bool COUNT>
 __global__ void __launch_bounds__(256)
 derive_kernel(NodePtrs t, int strat_mask, unsigned long long *__restrict__ keys,
               double *__restrict__ score, SnapHeader *__restrict__ hdr)
@@ -323,6 +257,18 @@ derive_kernel(NodePtrs t, int strat_mask, unsigned long long *__restrict__ keys,
         keys[(size_t)3 * t.n + n] = d.tkey[0];
         keys[(size_t)4 * t.n + n] = d.tkey[1];
     }
+    if (!COUNT && n < kMaxStrategies) {
+        hdr->group_count[n] = 0;
+        hdr->group_cursor[n] = 0;
+        if (!(strat_mask & (1 << n))) hdr->nvalid[n] = 0;
+        if (n == 0) {
+            hdr->ticket = 0;
+            hdr->use_swar = 1;
+            hdr->reserved = 0;
+            hdr->distinct[0] = (uint32_t)t.n;       // sorted threshold arrays keep duplicates
+            hdr->distinct[1] = (uint32_t)t.n;
+        }
+    }
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {
         if (!(strat_mask & (1 << s))) continue;
@@ -332,8 +278,10 @@ derive_kernel(NodePtrs t, int strat_mask, unsigned long long *__restrict__ keys,
             score[(size_t)s * t.n + n] = d.score[s];
             keys[(size_t)s * t.n + n] = d.skey[s];
         }
-        const unsigned ballot = __ballot_sync(0xffffffffu, elig);
-        if ((threadIdx.x & 31) == 0 && ballot) atomicAdd(&hdr->nvalid[s], __popc(ballot));
+        if (COUNT) {
+            const unsigned ballot = __ballot_sync(0xffffffffu, elig);
+            if ((threadIdx.x & 31) == 0 && ballot) atomicAdd(&hdr->nvalid[s], __popc(ballot));
+        }
     }
 }
 

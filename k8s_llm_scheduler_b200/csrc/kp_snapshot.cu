@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "kp_common.cuh"
 
@@ -47,7 +48,7 @@ struct SnapLayout {
     int64_t slots;       // pod slots incl. per-strategy chunk padding
     int64_t chunks;      // pod chunks at the smallest chunk size (32)
     size_t off_header, off_chunk_done, off_pos, zero_bytes;   // zeroed together (multi-kernel plan)
-    size_t off_keys, off_score, off_sorted, off_uniq, off_dense, off_rank, off_order, off_ab, off_packed,
+    size_t off_keys, off_score, off_sorted, off_uniq, off_dense, off_order, off_ab, off_packed,
         off_partial, off_perm, off_best, total;
 };
 
@@ -65,12 +66,11 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_chunk_done = o; o = align_up(o + sizeof(uint32_t) * (big ? L.chunks : 0));
     L.off_pos = o;        o = align_up(o + sizeof(uint32_t) * kKeyArrays * (big ? n : 0));
     L.zero_bytes = o;
-    L.off_keys = o;    o = align_up(o + sizeof(uint64_t) * kKeyArrays * (big ? n : 0));
+    L.off_keys = o;    o = align_up(o + sizeof(uint64_t) * kKeyArrays * n);
     L.off_score = o;   o = align_up(o + sizeof(double) * kMaxStrategies * n);
     L.off_sorted = o;  o = align_up(o + sizeof(double) * 2 * (big ? L.npad : 0));
     L.off_uniq = o;    o = align_up(o + sizeof(double) * 2 * L.npad);
     L.off_dense = o;   o = align_up(o + sizeof(uint32_t) * 2 * (big ? L.npad : 0));
-    L.off_rank = o;    o = align_up(o + sizeof(uint32_t) * 2 * (big ? 0 : L.npad));
     L.off_order = o;   o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
     L.off_packed = o;  o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
@@ -287,6 +287,7 @@ int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode
 struct PlaceCfg { int threads, r, nsplit, chunk; };
 constexpr PlaceCfg kPlaceCfgs[] = {
     {256, 8, 1, 2048}, {128, 8, 1, 1024}, {128, 4, 1, 512}, {256, 4, 4, 256}, {256, 4, 8, 128}, {256, 2, 8, 64},
+    {256, 8, 8, 256},     // not in the size ladder: few pods, one wave of 8-warp CTAs with 8 pods per lane
 };
 constexpr int kNumPlaceCfgs = sizeof(kPlaceCfgs) / sizeof(kPlaceCfgs[0]);
 constexpr int kFallbackCfg = 4;          // few pods: 128 pods per CTA, 8 warps splitting the nodes
@@ -312,7 +313,8 @@ static int cfg_occupancy(int c)
         case 2: return place_occupancy<128, 4, 1>();
         case 3: return place_occupancy<256, 4, 4>();
         case 4: return place_occupancy<256, 4, 8>();
-        default: return place_occupancy<256, 2, 8>();
+        case 5: return place_occupancy<256, 2, 8>();
+        default: return place_occupancy<256, 8, 8>();
     }
 }
 
@@ -324,37 +326,10 @@ static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_
         case 2: place_kernel<128, 4, 1><<<grid, 128, 0, stream>>>(pp); break;
         case 3: place_kernel<256, 4, 4><<<grid, 256, 0, stream>>>(pp); break;
         case 4: place_kernel<256, 4, 8><<<grid, 256, 0, stream>>>(pp); break;
-        default: place_kernel<256, 2, 8><<<grid, 256, 0, stream>>>(pp); break;
+        case 5: place_kernel<256, 2, 8><<<grid, 256, 0, stream>>>(pp); break;
+        default: place_kernel<256, 8, 8><<<grid, 256, 0, stream>>>(pp); break;
     }
     KP_LAUNCH_CHECK("place_kernel");
-    return KP_OK;
-}
-
-template <int E>
-static int launch_plan_small(const NodePtrs &t, int strat_mask, const PlanOut &po, cudaStream_t stream)
-{
-    static bool attr_set = false;
-    if (!attr_set) {
-        KP_CUDA(cudaFuncSetAttribute(plan_small_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(SmallSmem)));
-        attr_set = true;
-    }
-    int ctas = 2;
-    for (int s = 0; s < kMaxStrategies; ++s) ctas += (strat_mask >> s) & 1;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(ctas, 1, 1);
-    cfg.blockDim = dim3(1024, 1, 1);
-    cfg.dynamicSmemBytes = sizeof(SmallSmem);
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = ctas;                 // one cluster: one CTA per independent sort
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    KP_CUDA(cudaLaunchKernelEx(&cfg, plan_small_kernel<E>, t, strat_mask, po));
-    count_launch();
     return KP_OK;
 }
 
@@ -406,9 +381,13 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     const int ntiles_wide = (int)((L.npad + kTileNodesWide - 1) / kTileNodesWide);
     const int max_nseg = big ? ntiles_wide : 1;
     int cfg = kFallbackCfg;
-    for (int c = 0; c < kNumPlaceCfgs; ++c) {
+    for (int c = 0; c < kNumPlaceCfgs - 1; ++c) {
         const int64_t chunks = (P + kPlaceCfgs[c].chunk - 1) / kPlaceCfgs[c].chunk;
         if (chunks * max_nseg >= (int64_t)4 * sms * cfg_occupancy(c)) { cfg = c; break; }
+    }
+    if (const char *force = getenv("KP_FORCE_PLACE_CFG")) {      // experiments only
+        const int c = atoi(force);
+        if (c >= 0 && c < kNumPlaceCfgs) cfg = c;
     }
     const int chunk_pods = kPlaceCfgs[cfg].chunk;
     const int64_t n_chunks = (P + chunk_pods - 1) / chunk_pods + (per_pod ? kMaxStrategies - 1 : 0);
@@ -440,21 +419,22 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     po.order = reinterpret_cast<uint32_t *>(w + L.off_order);
     po.ab = reinterpret_cast<uint2 *>(w + L.off_ab);
     po.packed = reinterpret_cast<uint32_t *>(w + L.off_packed);
-    po.rank = reinterpret_cast<uint32_t *>(w + L.off_rank);
     po.npad = (int)L.npad;
 
     ProfileEvents &pe = profile_events();
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e0, stream));
     if (!big) {
-        int st;
-        if (n <= 1024) st = launch_plan_small<1>(t, strat_mask, po, stream);
-        else if (n <= 2048) st = launch_plan_small<2>(t, strat_mask, po, stream);
-        else st = launch_plan_small<4>(t, strat_mask, po, stream);
-        if (st != KP_OK) return st;
+        // no sort, no memset: derive, then every node counts its own sorted positions
+        const int nb = (int)((n + 255) / 256);
+        derive_kernel<false><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr);
+        KP_LAUNCH_CHECK("derive_kernel");
+        const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
+        plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(keys, (int)n, strat_mask, po);
+        KP_LAUNCH_CHECK("plan_count_kernel");
     } else {
         KP_CUDA(cudaMemsetAsync(w, 0, L.zero_bytes, stream));
         const int nb = (int)((n + 255) / 256);
-        derive_kernel<<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr);
+        derive_kernel<true><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr);
         KP_LAUNCH_CHECK("derive_kernel");
         RankList list{};
         for (int s = 0; s < kMaxStrategies; ++s) if (strat_mask & (1 << s)) list.idx[list.count++] = s;
@@ -543,11 +523,10 @@ int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods,
                   (long long)nodes.n_nodes, (long long)kNoAllocMaxNodes);
         return KP_ERR_CAPACITY;
     }
-    const bool pod_scratch = per_pod || nodes.n_nodes > kSmallMaxNodes;   // these calls keep per-pod state
-    if (pod_scratch && pods.n_pods > kNoAllocMaxPods) {
-        set_error("kp_snapshot_place_noalloc: %lld pods exceed the built-in scratch limit of %lld that "
-                  "applies with per-pod strategy ids or more than %d nodes",
-                  (long long)pods.n_pods, (long long)kNoAllocMaxPods, kSmallMaxNodes);
+    if (per_pod && pods.n_pods > kNoAllocMaxPods) {
+        set_error("kp_snapshot_place_noalloc: %lld pods with per-pod strategy ids exceed the built-in "
+                  "scratch limit of %lld (uniform-strategy calls have no pod limit)",
+                  (long long)pods.n_pods, (long long)kNoAllocMaxPods);
         return KP_ERR_CAPACITY;
     }
     if (make_layout(nodes.n_nodes, pods.n_pods, per_pod).total > kNoAllocScratchBytes) {
