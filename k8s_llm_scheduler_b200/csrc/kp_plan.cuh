@@ -17,8 +17,8 @@
 //   small tables       (<= 8192 nodes) derive + plan_count_kernel: no sort -- every node counts
 //                      its own sorted position against the whole table, in parallel over the
 //                      whole GPU; plain "number of smaller thresholds" ranks (no dense pass).
-//   multi-kernel path  (any size) derive -> counting rank -> sorted thresholds -> dense ranks
-//                      -> tables.
+//   large tables       (any size) derive -> radix sorts (kp_sort.cu) -> post_sort -> scan of the
+//                      run starts (dense ranks) -> tables.
 #pragma once
 
 #include <cooperative_groups.h>
@@ -96,34 +96,6 @@ struct PlanOut {
     uint32_t *packed;   // [3][npad]
     int npad;
 };
-
-// block-wide scan helper for 1024 threads: returns the exclusive prefix of `cnt`
-// and leaves the block total in *total
-__device__ __forceinline__ uint32_t block_exclusive_1024(uint32_t cnt, uint32_t *warp_sums, uint32_t *total)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t incl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += v;
-    }
-    __syncthreads();                       // warp_sums may still be read from a previous call
-    if (lane == 31) warp_sums[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = warp_sums[lane];
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, w, d);
-            if (lane >= d) w += v;
-        }
-        warp_sums[lane] = w;
-        if (lane == 31) *total = w;
-    }
-    __syncthreads();
-    return incl - cnt + (warp > 0 ? warp_sums[warp - 1] : 0u);
-}
 
 // ---------------------------------------------------------------------------------------
 // small-table plan (n <= kSmallMaxNodes): derive_kernel<false> + plan_count_kernel
@@ -240,19 +212,20 @@ plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_
 }
 
 // ---------------------------------------------------------------------------------------
-// multi-kernel plan (any n)
+// large-table plan (any n)
 // ---------------------------------------------------------------------------------------
 // COUNT: accumulate the eligible-node counts with atomics (header zeroed beforehand); the
 // small-table path instead initialises the header here and counts in plan_count_kernel.
 template <bool COUNT>
 __global__ void __launch_bounds__(256)
 derive_kernel(NodePtrs t, int strat_mask, unsigned long long *__restrict__ keys,
-              double *__restrict__ score, SnapHeader *__restrict__ hdr)
+              double *__restrict__ score, SnapHeader *__restrict__ hdr, uint32_t *__restrict__ iota)
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = n < t.n;
     Derived d;
     if (live) {
+        if (iota) iota[n] = (uint32_t)n;
         d = derive_node(t, n, strat_mask);
         keys[(size_t)3 * t.n + n] = d.tkey[0];
         keys[(size_t)4 * t.n + n] = d.tkey[1];
@@ -285,93 +258,53 @@ derive_kernel(NodePtrs t, int strat_mask, unsigned long long *__restrict__ keys,
     }
 }
 
-// Stable ascending rank by counting, tiled through shared memory.
-//   pos[j][n]  = #{m : K[m] < K[n]  or  (K[m] == K[n] and m < n)}
-// grid = (ceil(n/256), chunks, active arrays); partial counts are added atomically.
-struct RankList { int idx[kKeyArrays]; int count; };
-constexpr int kRankTile = 1024;
+// After the radix sorts (kp_sort.cu): kout[j] / vout[j] = keys of array j in ascending order and
+// the node index of every sorted position.  One pass turns that into what the tables need:
+//   pos[j][node] = sorted position of the node in array j,
+//   sorted[t][i] = threshold value at sorted position i,  flag[t][i] = 1 iff it starts a new run
+// (the inclusive scan of flag gives dense rank + 1).
+struct SortList { int idx[kKeyArrays]; int count; };
 
 __global__ void __launch_bounds__(256)
-rank_kernel(const unsigned long long *__restrict__ keys, uint32_t *__restrict__ pos, int n_nodes,
-            int chunk_len, RankList list)
+post_sort_kernel(const unsigned long long *__restrict__ kout, const uint32_t *__restrict__ vout,
+                 int n_nodes, int npad, SortList list, uint32_t *__restrict__ pos,
+                 double *__restrict__ sorted, uint32_t *__restrict__ flag)
 {
-    __shared__ unsigned long long tile[kRankTile];
-    const int j = list.idx[blockIdx.z];
-    const unsigned long long *K = keys + (size_t)j * n_nodes;
-    const int n = blockIdx.x * 256 + threadIdx.x;
-    const unsigned long long kn = n < n_nodes ? K[n] : 0ull;
-    const int m0 = blockIdx.y * chunk_len;
-    const int m1 = min(n_nodes, m0 + chunk_len);
-    uint32_t c_pos = 0;
-    for (int base = m0; base < m1; base += kRankTile) {
-        for (int i = threadIdx.x; i < kRankTile; i += 256) {
-            const int m = base + i;
-            tile[i] = m < m1 ? K[m] : ~0ull;
-        }
-        __syncthreads();
-        const int cnt = min(kRankTile, m1 - base);
-        if (base + cnt <= n) {                 // every m in the tile is < n: ties count
-#pragma unroll 8
-            for (int i = 0; i < cnt; ++i) c_pos += tile[i] <= kn;
-        } else if (base > n) {                 // every m is > n: ties do not count
-#pragma unroll 8
-            for (int i = 0; i < cnt; ++i) c_pos += tile[i] < kn;
-        } else {
-            for (int i = 0; i < cnt; ++i) {
-                const unsigned long long km = tile[i];
-                c_pos += (km < kn) | ((km == kn) & (base + i < n));
-            }
-        }
-        __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const int j = list.idx[blockIdx.y];
+    const unsigned long long k = kout[(size_t)j * n_nodes + i];
+    pos[(size_t)j * n_nodes + vout[(size_t)j * n_nodes + i]] = (uint32_t)i;
+    if (j >= kMaxStrategies) {
+        const int t = j - kMaxStrategies;
+        sorted[(size_t)t * npad + i] = key_to_f64(k);
+        flag[(size_t)t * npad + i] = (i == 0 || kout[(size_t)j * n_nodes + i - 1] != k) ? 1u : 0u;
     }
-    if (n < n_nodes) atomicAdd(&pos[(size_t)j * n_nodes + n], c_pos);
 }
 
-__global__ void __launch_bounds__(256)
-scatter_sorted_kernel(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ pos,
-                      int n_nodes, int npad, double *__restrict__ sorted)
-{
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= n_nodes) return;
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-        sorted[(size_t)j * npad + pos[(size_t)(3 + j) * n_nodes + n]] = key_to_f64(keys[(size_t)(3 + j) * n_nodes + n]);
-}
-
-// one CTA per threshold array: dense rank of every sorted position + unique values
-__global__ void __launch_bounds__(1024, 1)
-dense_kernel(const double *__restrict__ sorted, int n_nodes, int npad, uint32_t *__restrict__ dense,
-             double *__restrict__ uniq, SnapHeader *__restrict__ hdr)
-{
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t total;
-    const int tid = threadIdx.x;
-    const int j = blockIdx.x;
-    const int per = (n_nodes + 1023) / 1024;
-    const int i0 = min(n_nodes, tid * per), i1 = min(n_nodes, i0 + per);
-    const double *S = sorted + (size_t)j * npad;
-    uint32_t cnt = 0;
-    for (int i = i0; i < i1; ++i) cnt += (i == 0 || S[i] != S[i - 1]) ? 1u : 0u;
-    uint32_t run = block_exclusive_1024(cnt, warp_sums, &total);
-    for (int i = i0; i < i1; ++i) {
-        if (i == 0 || S[i] != S[i - 1]) { uniq[(size_t)j * npad + run] = S[i]; ++run; }
-        dense[(size_t)j * npad + i] = run - 1;
-    }
-    if (tid == 0) hdr->distinct[j] = total;
-}
-
+// incl[t][i] = inclusive scan of flag[t]: dense rank of sorted position i is incl - 1 and the
+// number of distinct thresholds is incl[t][n - 1].
 __global__ void __launch_bounds__(256)
 scatter_tables_kernel(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ pos,
-                      const uint32_t *__restrict__ dense, int n_nodes, int strat_mask, PlanOut o)
+                      const double *__restrict__ sorted, const uint32_t *__restrict__ flag,
+                      const uint32_t *__restrict__ incl, int n_nodes, int strat_mask, PlanOut o)
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= o.npad) return;
-    const bool swar = o.hdr->distinct[0] <= kSwarMaxDistinct && o.hdr->distinct[1] <= kSwarMaxDistinct;
-    if (n == 0) o.hdr->use_swar = swar ? 1u : 0u;
+    const uint32_t d0 = incl[n_nodes - 1], d1 = incl[(size_t)o.npad + n_nodes - 1];
+    const bool swar = d0 <= kSwarMaxDistinct && d1 <= kSwarMaxDistinct;
+    if (n == 0) {
+        o.hdr->distinct[0] = d0;
+        o.hdr->distinct[1] = d1;
+        o.hdr->use_swar = swar ? 1u : 0u;
+    }
     uint2 r = make_uint2(0u, 0u);
     if (n < n_nodes) {
-        r.x = dense[pos[(size_t)3 * n_nodes + n]];
-        r.y = dense[(size_t)o.npad + pos[(size_t)4 * n_nodes + n]];
+#pragma unroll
+        for (int t = 0; t < 2; ++t)                                // unique threshold values, ascending
+            if (flag[(size_t)t * o.npad + n]) o.uniq[(size_t)t * o.npad + incl[(size_t)t * o.npad + n] - 1] = sorted[(size_t)t * o.npad + n];
+        r.x = incl[pos[(size_t)3 * n_nodes + n]] - 1;
+        r.y = incl[(size_t)o.npad + pos[(size_t)4 * n_nodes + n]] - 1;
     }
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {

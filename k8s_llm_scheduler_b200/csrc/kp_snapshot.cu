@@ -47,9 +47,10 @@ struct SnapLayout {
     int64_t npad;        // n rounded up to a multiple of 4, plus slack for 16-byte copies
     int64_t slots;       // pod slots incl. per-strategy chunk padding
     int64_t chunks;      // pod chunks at the smallest chunk size (32)
-    size_t off_header, off_chunk_done, off_pos, zero_bytes;   // zeroed together (multi-kernel plan)
-    size_t off_keys, off_score, off_sorted, off_uniq, off_dense, off_order, off_ab, off_packed,
-        off_partial, off_perm, off_best, total;
+    size_t off_header, off_chunk_done, zero_bytes;            // zeroed together (large-table plan)
+    size_t off_keys, off_score, off_uniq, off_order, off_ab, off_packed, off_partial, off_perm;
+    size_t off_pos, off_kout, off_vout, off_iota, off_sorted, off_flag, off_incl, off_sort_tmp, off_best;   // large tables
+    size_t sort_tmp_bytes, total;
 };
 
 static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
@@ -64,19 +65,26 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     size_t o = 0;
     L.off_header = o;     o = align_up(o + sizeof(SnapHeader));
     L.off_chunk_done = o; o = align_up(o + sizeof(uint32_t) * (big ? L.chunks : 0));
-    L.off_pos = o;        o = align_up(o + sizeof(uint32_t) * kKeyArrays * (big ? n : 0));
     L.zero_bytes = o;
     L.off_keys = o;    o = align_up(o + sizeof(uint64_t) * kKeyArrays * n);
     L.off_score = o;   o = align_up(o + sizeof(double) * kMaxStrategies * n);
-    L.off_sorted = o;  o = align_up(o + sizeof(double) * 2 * (big ? L.npad : 0));
     L.off_uniq = o;    o = align_up(o + sizeof(double) * 2 * L.npad);
-    L.off_dense = o;   o = align_up(o + sizeof(uint32_t) * 2 * (big ? L.npad : 0));
     L.off_order = o;   o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
     L.off_packed = o;  o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_partial = o; o = align_up(o + (sizeof(uint64_t) + sizeof(uint32_t) * 2) * kMaxStrategies * kArgmaxMaxBlocks);
     L.off_perm = o;    o = align_up(o + sizeof(uint32_t) * (per_pod ? L.slots : 0));
-    L.off_best = o;    o = align_up(o + sizeof(uint32_t) * (big ? L.slots : 0));
+    const int64_t nb = big ? n : 0, npb = big ? L.npad : 0;
+    L.sort_tmp_bytes = big ? sort_temp_bytes(n) : 0;
+    L.off_pos = o;      o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
+    L.off_kout = o;     o = align_up(o + sizeof(uint64_t) * kKeyArrays * nb);
+    L.off_vout = o;     o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
+    L.off_iota = o;     o = align_up(o + sizeof(uint32_t) * nb);
+    L.off_sorted = o;   o = align_up(o + sizeof(double) * 2 * npb);
+    L.off_flag = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
+    L.off_incl = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
+    L.off_sort_tmp = o; o = align_up(o + L.sort_tmp_bytes);
+    L.off_best = o;     o = align_up(o + sizeof(uint32_t) * (big ? L.slots : 0));
     L.total = o;
     return L;
 }
@@ -409,7 +417,6 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(w + L.off_keys);
     uint32_t *pos = reinterpret_cast<uint32_t *>(w + L.off_pos);
     double *sorted = reinterpret_cast<double *>(w + L.off_sorted);
-    uint32_t *dense = reinterpret_cast<uint32_t *>(w + L.off_dense);
     uint32_t *perm = per_pod ? reinterpret_cast<uint32_t *>(w + L.off_perm) : nullptr;
     uint32_t *best_pos = reinterpret_cast<uint32_t *>(w + L.off_best);
     PlanOut po{};
@@ -426,7 +433,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     if (!big) {
         // no sort, no memset: derive, then every node counts its own sorted positions
         const int nb = (int)((n + 255) / 256);
-        derive_kernel<false><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr);
+        derive_kernel<false><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr, nullptr);
         KP_LAUNCH_CHECK("derive_kernel");
         const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
         plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(keys, (int)n, strat_mask, po);
@@ -434,26 +441,32 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     } else {
         KP_CUDA(cudaMemsetAsync(w, 0, L.zero_bytes, stream));
         const int nb = (int)((n + 255) / 256);
-        derive_kernel<true><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr);
+        uint32_t *iota = reinterpret_cast<uint32_t *>(w + L.off_iota);
+        unsigned long long *kout = reinterpret_cast<unsigned long long *>(w + L.off_kout);
+        uint32_t *vout = reinterpret_cast<uint32_t *>(w + L.off_vout);
+        uint32_t *flag = reinterpret_cast<uint32_t *>(w + L.off_flag);
+        uint32_t *incl = reinterpret_cast<uint32_t *>(w + L.off_incl);
+        void *tmp = w + L.off_sort_tmp;
+        derive_kernel<true><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr, iota);
         KP_LAUNCH_CHECK("derive_kernel");
-        RankList list{};
+        SortList list{};
         for (int s = 0; s < kMaxStrategies; ++s) if (strat_mask & (1 << s)) list.idx[list.count++] = s;
         list.idx[list.count++] = 3;
         list.idx[list.count++] = 4;
-        {
-            // enough chunks to give every SM a few CTAs, but at least one rank tile each
-            int chunks = std::max(1, (4 * sms) / std::max(1, nb * list.count));
-            chunks = (int)std::min<int64_t>(chunks, (n + kRankTile - 1) / kRankTile);
-            const int chunk_len = (int)(((n + chunks - 1) / chunks + kRankTile - 1) / kRankTile * kRankTile);
-            chunks = (int)((n + chunk_len - 1) / chunk_len);
-            rank_kernel<<<dim3(nb, chunks, list.count), 256, 0, stream>>>(keys, pos, (int)n, chunk_len, list);
-            KP_LAUNCH_CHECK("rank_kernel");
+        for (int q = 0; q < list.count; ++q) {
+            const int j = list.idx[q];
+            const int st = sort_pairs_u64(tmp, L.sort_tmp_bytes, keys + (size_t)j * n, kout + (size_t)j * n, iota,
+                                          vout + (size_t)j * n, (int)n, stream);
+            if (st != KP_OK) return st;
         }
-        scatter_sorted_kernel<<<nb, 256, 0, stream>>>(keys, pos, (int)n, (int)L.npad, sorted);
-        KP_LAUNCH_CHECK("scatter_sorted_kernel");
-        dense_kernel<<<2, 1024, 0, stream>>>(sorted, (int)n, (int)L.npad, dense, po.uniq, hdr);
-        KP_LAUNCH_CHECK("dense_kernel");
-        scatter_tables_kernel<<<(int)((L.npad + 255) / 256), 256, 0, stream>>>(keys, pos, dense, (int)n,
+        post_sort_kernel<<<dim3(nb, list.count), 256, 0, stream>>>(kout, vout, (int)n, (int)L.npad, list, pos, sorted, flag);
+        KP_LAUNCH_CHECK("post_sort_kernel");
+        for (int tq = 0; tq < 2; ++tq) {
+            const int st = inclusive_sum_u32(tmp, L.sort_tmp_bytes, flag + (size_t)tq * L.npad, incl + (size_t)tq * L.npad,
+                                             (int)n, stream);
+            if (st != KP_OK) return st;
+        }
+        scatter_tables_kernel<<<(int)((L.npad + 255) / 256), 256, 0, stream>>>(keys, pos, sorted, flag, incl, (int)n,
                                                                                strat_mask, po);
         KP_LAUNCH_CHECK("scatter_tables_kernel");
     }
