@@ -1,0 +1,62 @@
+#!/usr/bin/env python3
+"""Multi-GPU parity check (NCCL): pod-sharded and node-sharded snapshot placement against the
+CPU oracle.  Launch with
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29511 tools/dist_check.py
+Prints one line per mode on rank 0 (test infrastructure: uses oracle/)."""
+import os
+import sys
+import time
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from k8s_llm_scheduler_b200 import dist as kdist
+from k8s_llm_scheduler_b200 import placement, synth
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    nodes, pods = synth.config5(20_000, 200_000, seed=5)
+    dn = placement.nodes_to_device(nodes, dev)
+    rc = torch.as_tensor(pods.req_cpu_milli).to(dev)
+    rm = torch.as_tensor(pods.req_mem_bytes).to(dev)
+    sid = torch.as_tensor(pods.strategy_ids).to(dev)
+    if rank == 0:
+        from oracle import c_oracle
+        oi, os_ = c_oracle.snapshot(nodes.columns(), pods.req_cpu_milli, pods.req_mem_bytes,
+                                    strategy_ids=pods.strategy_ids, filter_mode=1, threads=16)
+        o0i, o0s = c_oracle.snapshot(nodes.columns(), pods.req_cpu_milli, pods.req_mem_bytes, strategy=0,
+                                     filter_mode=1, threads=16)
+
+    # pod-sharded: ranks other than 0 start from a zeroed table and receive rank 0's by broadcast
+    mine = dn if rank == 0 else {k: torch.zeros_like(v) for k, v in dn.items()}
+    torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
+    gi, gs = kdist.snapshot_pod_sharded(mine, rc, rm, sid, 1, gather=True)
+    torch.cuda.synchronize(); dt = time.perf_counter() - t
+    if rank == 0:
+        ok = np.array_equal(gi.cpu().numpy(), oi) and np.array_equal(gs.cpu().numpy().view(np.uint64), os_.view(np.uint64))
+        print(f"pod-sharded  world={world} 20000 nodes x 200000 pods mixed strategies: parity={'OK' if ok else 'FAIL'} ({dt*1e3:.2f} ms incl. broadcast + all-gather)", flush=True)
+
+    # node-sharded: contiguous node ranges + (score, idx) arg-max reduce over NCCL
+    lo, hi = kdist.shard_bounds(len(nodes), rank, world)
+    local_nodes = kdist.slice_nodes(dn, lo, hi)
+    torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
+    ni, ns = kdist.snapshot_node_sharded(local_nodes, lo, rc, rm, 0, 1)
+    torch.cuda.synchronize(); dt = time.perf_counter() - t
+    if rank == 0:
+        ok = np.array_equal(ni.cpu().numpy(), o0i) and np.array_equal(ns.cpu().numpy().view(np.uint64), o0s.view(np.uint64))
+        print(f"node-sharded world={world} 20000 nodes x 200000 pods resource_balanced: parity={'OK' if ok else 'FAIL'} ({dt*1e3:.2f} ms incl. 2 all-reduces)", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
