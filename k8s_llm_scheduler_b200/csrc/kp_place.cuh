@@ -29,17 +29,18 @@
 namespace kp {
 
 #ifndef KP_TILE_BYTES
-#define KP_TILE_BYTES 8192
+#define KP_TILE_BYTES 4096
 #endif
 #ifndef KP_UPDATE_MODE
 #define KP_UPDATE_MODE 1      // candidate update: 0 = SEL (ALU pipe), 1 = alternate per pod, 2 = guarded IMAD (FMA pipe)
 #endif
 constexpr int kTileBytes = KP_TILE_BYTES;              // per shared-memory tile buffer
-constexpr int kTileNodesPacked = kTileBytes / 4;       // 2048
-constexpr int kTileNodesWide = kTileBytes / 8;         // 1024
+constexpr int kTileNodesPacked = kTileBytes / 4;       // 1024
+constexpr int kTileNodesWide = kTileBytes / 8;         // 512
 constexpr uint32_t kSwarGuards = 0x80008000u;
 constexpr uint32_t kSwarDeadPod = 0x7fff7fffu;         // larger than any node field: never fits
 constexpr uint32_t kNoPos = 0xffffffffu;
+constexpr int kUniqStage = 1024;                       // sorted thresholds staged in shared memory up to this many
 
 struct PlaceParams {
     const long long *req_cpu, *req_mem;
@@ -127,10 +128,35 @@ place_kernel(const PlaceParams p)
     __shared__ uint64_t bars[2];
     __shared__ int comb[NSPLIT > 1 ? NSPLIT : 1][NSPLIT > 1 ? CHUNK : 1];
     __shared__ int s_last;
+    __shared__ double s_uniq[2][kUniqStage];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int podw = warp / NSPLIT, split = warp % NSPLIT;
     const long long slot0 = (long long)blockIdx.x * CHUNK;
+
+    // ---- before the node plan is needed: barrier set-up and the pods' requests ----
+    // (launched with programmatic dependent launch, this part overlaps the tail of the plan)
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+    constexpr int ITEMS = NSPLIT > 1 ? (2 * CHUNK + THREADS - 1) / THREADS : 1;
+    double pre_req[ITEMS];
+    const bool prefetched = NSPLIT > 1 && p.uniform_strategy >= 0;       // slot == pod: requests need no plan data
+    if (prefetched) {
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) {
+            const int item = tid + e * THREADS;
+            const int q = item % CHUNK, dim = item / CHUNK;
+            const long long pod = slot0 + q;
+            pre_req[e] = 0.0;
+            if (item < 2 * CHUNK && pod < p.n_pods)
+                pre_req[e] = dim == 0 ? req_cores(p.req_cpu[pod]) : req_gib(p.req_mem[pod]);
+        }
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");                   // the plan kernels have completed
+
     int s = p.uniform_strategy;
     long long gbegin = 0, gcount = p.n_pods;
     if (s < 0) {
@@ -156,37 +182,44 @@ place_kernel(const PlaceParams p)
     const unsigned char *table = swar ? reinterpret_cast<const unsigned char *>(p.packed + (size_t)s * p.npad)
                                       : reinterpret_cast<const unsigned char *>(p.ab + (size_t)s * p.npad);
 
-    if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
-        mbar_fence_init();
+    // first tile on its way while the pods are ranked
+    auto tile_count = [&](int t) { return min(tile_nodes, nvalid4 - t * tile_nodes); };
+    __syncthreads();                                         // barrier objects initialised
+    if (tid == 0 && t_hi > t_lo) {
+        const int t = t_hi - 1;
+        const uint32_t bytes = (uint32_t)(tile_count(t) * elem);
+        mbar_expect_tx(&bars[0], bytes);
+        bulk_load(tiles[0], table + (size_t)t * tile_nodes * elem, bytes, &bars[0]);
     }
 
-    // ---- pod prologue: requests -> dense threshold ranks (exact, see kp_snapshot.cu) ----
+    // ---- pod prologue: requests -> threshold ranks (exact, see kp_plan.cuh) ----
     const double *ua = p.uniq, *ub = p.uniq + p.npad;
-    const bool stage = da <= kTileBytes / 8 && db <= kTileBytes / 8;
-    if (stage) {        // both unique-threshold arrays fit the (still unused) tile buffers
-        double *sa = reinterpret_cast<double *>(tiles[0]);
-        double *sb = reinterpret_cast<double *>(tiles[1]);
-        for (int i = tid; i < da; i += THREADS) sa[i] = ua[i];
-        for (int i = tid; i < db; i += THREADS) sb[i] = ub[i];
-        ua = sa;
-        ub = sb;
+    if (da <= kUniqStage && db <= kUniqStage) {              // both sorted threshold arrays fit shared memory
+        for (int i = tid; i < da; i += THREADS) s_uniq[0][i] = ua[i];
+        for (int i = tid; i < db; i += THREADS) s_uniq[1][i] = ub[i];
+        ua = s_uniq[0];
+        ub = s_uniq[1];
+        __syncthreads();
     }
-    __syncthreads();
     uint32_t ra[R], rb[R];
     bool live[R];
     if (NSPLIT > 1) {
         // the NSPLIT warps that share a pod would each repeat its division + binary searches:
         // compute every (pod, dimension) rank once per CTA and hand it over in shared memory
-        for (int item = tid; item < 2 * CHUNK; item += THREADS) {
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) {
+            const int item = tid + e * THREADS;
+            if (item >= 2 * CHUNK) break;
             const int q = item % CHUNK, dim = item / CHUNK;
             const long long slot = slot0 + q;
             uint32_t rk = 0;
             if (slot - gbegin < gcount) {
-                const long long pod = p.perm ? (long long)p.perm[slot] : slot;
-                rk = dim == 0 ? (uint32_t)lower_bound_lt(ua, da, req_cores(p.req_cpu[pod]))
-                              : (uint32_t)lower_bound_lt(ub, db, req_gib(p.req_mem[pod]));
+                double req = pre_req[e];
+                if (!prefetched) {
+                    const long long pod = p.perm ? (long long)p.perm[slot] : slot;
+                    req = dim == 0 ? req_cores(p.req_cpu[pod]) : req_gib(p.req_mem[pod]);
+                }
+                rk = dim == 0 ? (uint32_t)lower_bound_lt(ua, da, req) : (uint32_t)lower_bound_lt(ub, db, req);
             }
             comb[dim][q] = (int)rk;                          // comb is free until the merge step
         }
@@ -207,19 +240,7 @@ place_kernel(const PlaceParams p)
             rb[r] = (uint32_t)lower_bound_lt(ub, db, req_gib(p.req_mem[pod]));
         }
     }
-    if (stage) {
-        // generic-proxy accesses to the buffers are done; order them before the async-proxy writes
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-
-    auto tile_count = [&](int t) { return min(tile_nodes, nvalid4 - t * tile_nodes); };
-    if (tid == 0 && t_hi > t_lo) {
-        const int t = t_hi - 1;
-        const uint32_t bytes = (uint32_t)(tile_count(t) * elem);
-        mbar_expect_tx(&bars[0], bytes);
-        bulk_load(tiles[0], table + (size_t)t * tile_nodes * elem, bytes, &bars[0]);
-    }
+    if (NSPLIT > 1) __syncthreads();                         // comb fully read before the merge step reuses it
 
     int best[R];
     if (swar) {

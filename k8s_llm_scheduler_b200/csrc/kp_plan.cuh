@@ -14,7 +14,7 @@
 //     into ONE 32-bit word with a guard bit above each 15-bit field.
 //
 // Two implementations:
-//   small tables       (<= 8192 nodes) derive + plan_count_kernel: no sort -- every node counts
+//   small tables       (<= 8192 nodes) plan_count_kernel, one launch: no sort -- every node counts
 //                      its own sorted position against the whole table, in parallel over the
 //                      whole GPU; plain "number of smaller thresholds" ranks (no dense pass).
 //   large tables       (any size) derive -> radix sorts (kp_sort.cu) -> post_sort -> scan of the
@@ -98,7 +98,7 @@ struct PlanOut {
 };
 
 // ---------------------------------------------------------------------------------------
-// small-table plan (n <= kSmallMaxNodes): derive_kernel<false> + plan_count_kernel
+// small-table plan (n <= kSmallMaxNodes): plan_count_kernel, ONE launch
 // ---------------------------------------------------------------------------------------
 // No sort at all: every node finds its own place by counting, fully in parallel over the
 // whole GPU.  For a key array K (ascending order wanted, ties broken by node index):
@@ -108,7 +108,9 @@ struct PlanOut {
 // dense-rank pass is needed: req <= thr[n]  <=>  #{m : thr[m] < req} <= less[n], with the pod
 // side found by binary search in the sorted threshold array (duplicates kept).
 //
-// A thread-block CLUSTER of 8 CTAs owns 32 nodes (one per lane).  Its 64 warps each count
+// A thread-block CLUSTER of 8 CTAs owns 32 nodes (one per lane).  Every CTA first derives the
+// keys it needs itself (its eighth of the table and the 32 nodes) into shared memory, so there
+// is no separate derive pass and no key array in global memory.  The 64 warps then each count
 // over one 64th of the table (every lane reads the same key: broadcast loads) and add their
 // partial counts into the leader CTA's shared memory with distributed-shared-memory atomics;
 // after a cluster barrier the leader writes the nodes' entries of the sorted threshold arrays
@@ -119,15 +121,19 @@ constexpr int kCountNodes = 32;
 constexpr int kCountCluster = 8;
 constexpr int kCountChunks = kCountCluster * (kCountThreads / 32);
 
+constexpr int kCountMaxChunk = kSmallMaxNodes / kCountCluster + 2;   // table rows one CTA counts over
+
 __device__ __forceinline__ void dsmem_add(cg::cluster_group &cluster, uint32_t *local, uint32_t v)
 {
     if (v) atomicAdd(cluster.map_shared_rank(local, 0), v);
 }
 
 __global__ void __cluster_dims__(kCountCluster, 1, 1) __launch_bounds__(kCountThreads)
-plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_mask, PlanOut o)
+plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
 {
-    __shared__ uint32_t acc_pos[kKeyArrays][kCountNodes];      // accumulated in the leader CTA only
+    __shared__ unsigned long long s_mkeys[kKeyArrays][kCountMaxChunk];   // keys of this CTA's table rows
+    __shared__ unsigned long long s_nkeys[kKeyArrays][kCountNodes];      // keys of the cluster's 32 nodes
+    __shared__ uint32_t acc_pos[kKeyArrays][kCountNodes];               // accumulated in the leader CTA only
     __shared__ uint32_t acc_less[2][kCountNodes];
     __shared__ uint32_t acc_live[kMaxStrategies];
 
@@ -135,20 +141,60 @@ plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_
     const int crank = (int)cluster.block_rank();
     const int group = blockIdx.x / kCountCluster;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = kCountThreads / 32;
+    const int n = t.n;
     const int g0 = group * kCountNodes;
     const int node = g0 + lane;
-    const int chunk = crank * (kCountThreads / 32) + warp;
+    const int chunk = crank * NW + warp;
     const int m0 = (int)(((long long)n * chunk) / kCountChunks), m1 = (int)(((long long)n * (chunk + 1)) / kCountChunks);
+    const int cta_m0 = (int)(((long long)n * (crank * NW)) / kCountChunks);
+    const int cta_m1 = (int)(((long long)n * (crank * NW + NW)) / kCountChunks);
+    const int mcount = cta_m1 - cta_m0;
 
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // place_kernel may start its prologue
     for (int i = tid; i < kKeyArrays * kCountNodes; i += kCountThreads) (&acc_pos[0][0])[i] = 0;
     if (tid < 2 * kCountNodes) (&acc_less[0][0])[tid] = 0;
     if (tid < kMaxStrategies) acc_live[tid] = 0;
+    if (group == 0 && crank == 0 && tid < kMaxStrategies) {           // header of the snapshot
+        o.hdr->group_count[tid] = 0;
+        o.hdr->group_cursor[tid] = 0;
+        if (!(strat_mask & (1 << tid))) o.hdr->nvalid[tid] = 0;
+        if (tid == 0) {
+            o.hdr->ticket = 0;
+            o.hdr->use_swar = 1;
+            o.hdr->reserved = 0;
+            o.hdr->distinct[0] = (uint32_t)n;                           // sorted threshold arrays keep duplicates
+            o.hdr->distinct[1] = (uint32_t)n;
+        }
+    }
+    // derive exactly the keys this CTA needs: its table rows and the cluster's 32 nodes
+    for (int i = tid; i < mcount + kCountNodes; i += kCountThreads) {
+        const bool is_row = i < mcount;
+        const int id = is_row ? cta_m0 + i : g0 + (i - mcount);
+        Derived d;
+        d.tkey[0] = d.tkey[1] = 0ull;
+        d.skey[0] = d.skey[1] = d.skey[2] = ~0ull;
+        if (id < n) {
+            d = derive_node(t, id, strat_mask);
+            if (!is_row && crank == 0) {
+#pragma unroll
+                for (int s = 0; s < kMaxStrategies; ++s)
+                    if (strat_mask & (1 << s)) o.score[(size_t)s * n + id] = d.score[s];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kKeyArrays; ++j) {
+            const unsigned long long k = j < kMaxStrategies ? d.skey[j] : d.tkey[j - kMaxStrategies];
+            if (is_row) s_mkeys[j][i] = k; else s_nkeys[j][i - mcount] = k;
+        }
+    }
+    __syncthreads();
     cluster.sync();                                            // every CTA's accumulators are initialised
 
     for (int j = kKeyArrays - 1; j >= 0; --j) {                // thresholds (3, 4), then strategies
         if (j < kMaxStrategies && !(strat_mask & (1 << j))) continue;
-        const unsigned long long *K = keys + (size_t)j * n;
-        const unsigned long long kn = node < n ? K[node] : 0ull;
+        const unsigned long long *K = s_mkeys[j] - cta_m0;     // indexable by the global row number
+        const unsigned long long kn = s_nkeys[j][lane];
         uint32_t c_pos = 0, c_less = 0;
         if (m1 <= g0) {                                        // every m is below the node group: ties count
 #pragma unroll 8
@@ -169,8 +215,10 @@ plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_
                 c_pos += lt | (uint32_t)((km == kn) & (m < node));
             }
         }
-        dsmem_add(cluster, &acc_pos[j][lane], c_pos);
-        if (j >= kMaxStrategies) dsmem_add(cluster, &acc_less[j - kMaxStrategies][lane], c_less);
+        if (node < n) {
+            dsmem_add(cluster, &acc_pos[j][lane], c_pos);
+            if (j >= kMaxStrategies) dsmem_add(cluster, &acc_less[j - kMaxStrategies][lane], c_less);
+        }
         if (j < kMaxStrategies && group == 0) {                // eligible nodes of this strategy table
             uint32_t live = 0;
             for (int m = m0 + lane; m < m1; m += 32) live += K[m] != ~0ull;
@@ -197,12 +245,11 @@ plan_count_kernel(const unsigned long long *__restrict__ keys, int n, int strat_
         const uint2 r = make_uint2(acc_less[0][lane], acc_less[1][lane]);
 #pragma unroll
         for (int jt = 0; jt < 2; ++jt)
-            o.uniq[(size_t)jt * o.npad + acc_pos[kMaxStrategies + jt][lane]] =
-                key_to_f64(keys[(size_t)(kMaxStrategies + jt) * n + node]);
+            o.uniq[(size_t)jt * o.npad + acc_pos[kMaxStrategies + jt][lane]] = key_to_f64(s_nkeys[kMaxStrategies + jt][lane]);
 #pragma unroll
         for (int s = 0; s < kMaxStrategies; ++s) {
             if (!(strat_mask & (1 << s))) continue;
-            if (keys[(size_t)s * n + node] == ~0ull) continue;            // ineligible: not in the table
+            if (s_nkeys[s][lane] == ~0ull) continue;                      // ineligible: not in the table
             const uint32_t p = acc_pos[s][lane];
             o.order[(size_t)s * o.npad + p] = (uint32_t)node;
             o.ab[(size_t)s * o.npad + p] = r;

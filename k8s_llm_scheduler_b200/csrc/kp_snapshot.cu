@@ -326,18 +326,39 @@ static int cfg_occupancy(int c)
     }
 }
 
+// Programmatic dependent launch: the kernel may start while its predecessor in the stream is
+// still draining; place_kernel does its plan-independent prologue first and then executes
+// griddepcontrol.wait before touching anything the plan wrote.
+template <int THREADS, int R, int NSPLIT>
+static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream_t stream)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(THREADS, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, place_kernel<THREADS, R, NSPLIT>, pp);
+}
+
 static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_t stream)
 {
+    cudaError_t e;
     switch (c) {
-        case 0: place_kernel<256, 8, 1><<<grid, 256, 0, stream>>>(pp); break;
-        case 1: place_kernel<128, 8, 1><<<grid, 128, 0, stream>>>(pp); break;
-        case 2: place_kernel<128, 4, 1><<<grid, 128, 0, stream>>>(pp); break;
-        case 3: place_kernel<256, 4, 4><<<grid, 256, 0, stream>>>(pp); break;
-        case 4: place_kernel<256, 4, 8><<<grid, 256, 0, stream>>>(pp); break;
-        case 5: place_kernel<256, 2, 8><<<grid, 256, 0, stream>>>(pp); break;
-        default: place_kernel<256, 8, 8><<<grid, 256, 0, stream>>>(pp); break;
+        case 0: e = launch_place_pdl<256, 8, 1>(pp, grid, stream); break;
+        case 1: e = launch_place_pdl<128, 8, 1>(pp, grid, stream); break;
+        case 2: e = launch_place_pdl<128, 4, 1>(pp, grid, stream); break;
+        case 3: e = launch_place_pdl<256, 4, 4>(pp, grid, stream); break;
+        case 4: e = launch_place_pdl<256, 4, 8>(pp, grid, stream); break;
+        case 5: e = launch_place_pdl<256, 2, 8>(pp, grid, stream); break;
+        default: e = launch_place_pdl<256, 8, 8>(pp, grid, stream); break;
     }
-    KP_LAUNCH_CHECK("place_kernel");
+    if (e != cudaSuccess) return cuda_fail(e, "place_kernel launch");
+    count_launch();
     return KP_OK;
 }
 
@@ -431,12 +452,9 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     ProfileEvents &pe = profile_events();
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e0, stream));
     if (!big) {
-        // no sort, no memset: derive, then every node counts its own sorted positions
-        const int nb = (int)((n + 255) / 256);
-        derive_kernel<false><<<nb, 256, 0, stream>>>(t, strat_mask, keys, po.score, hdr, nullptr);
-        KP_LAUNCH_CHECK("derive_kernel");
+        // no sort, no memset, one launch: every node counts its own sorted positions
         const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
-        plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(keys, (int)n, strat_mask, po);
+        plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(t, strat_mask, po);
         KP_LAUNCH_CHECK("plan_count_kernel");
     } else {
         KP_CUDA(cudaMemsetAsync(w, 0, L.zero_bytes, stream));
