@@ -48,12 +48,15 @@ struct PlaceParams {
     long long n_pods;
     int n_nodes, npad, uniform_strategy;
     int one;                           // always 1; run-time value so the IMAD update is not folded away
-    int tiles_per_seg_wide;            // tiles (of 1024 nodes) per node segment; the packed form uses half
+    int tiles_per_seg_wide;            // tiles (of 512 nodes) per node segment; the packed form uses half
+    int small_table_len;               // > 0: small-table plan -- packed form, thresholds sorted WITH duplicates
+                                       // (n_nodes of them), table length known on the host: no header reads
     const double *uniq;                // [2][npad] ascending distinct thresholds
     const uint2 *ab;                   // [3][npad] best-first {RA, RB}
     const uint32_t *packed;            // [3][npad] best-first packed ranks
     const uint32_t *order;             // [3][npad] rank position -> node index
     const double *score;               // [3][n]
+    const double *score_by_pos;        // [3][npad] score of the node at each rank position
     const SnapHeader *hdr;
     uint32_t *chunk_done;              // [chunks] finished node segments per pod chunk (zeroed; grid.y > 1)
     uint32_t *best_pos;                // [slots] merged best rank position (0xffffffff; grid.y > 1)
@@ -61,13 +64,13 @@ struct PlaceParams {
     double *out_score;
 };
 
-// #{i : arr[i] < x} in an ascending array
+// #{i : arr[i] < x} in an ascending array: branch-free, fixed depth (same trip count in every lane)
 __device__ __forceinline__ int lower_bound_lt(const double *arr, int n, double x)
 {
-    int lo = 0, hi = n;
-    while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (arr[mid] < x) lo = mid + 1; else hi = mid;
+    int lo = 0;
+    for (int step = 1 << (31 - __clz(n | 1)); step > 0; step >>= 1) {
+        const int nxt = lo + step;
+        if (nxt <= n && arr[nxt - 1] < x) lo = nxt;
     }
     return lo;
 }
@@ -170,9 +173,11 @@ place_kernel(const PlaceParams p)
     }
     if (slot0 - gbegin >= gcount) return;                    // CTA-uniform
 
-    const int nvalid4 = ((int)p.hdr->nvalid[s] + 3) & ~3;
-    const bool swar = p.hdr->use_swar != 0;
-    const int da = (int)p.hdr->distinct[0], db = (int)p.hdr->distinct[1];
+    const bool small = p.small_table_len > 0;
+    const int nvalid4 = small ? p.small_table_len : ((int)p.hdr->nvalid[s] + 3) & ~3;
+    const bool swar = small || p.hdr->use_swar != 0;
+    const int da = small ? p.n_nodes : (int)p.hdr->distinct[0];
+    const int db = small ? p.n_nodes : (int)p.hdr->distinct[1];
     const int tile_nodes = swar ? kTileNodesPacked : kTileNodesWide;
     const int elem = swar ? 4 : 8;
     const int tiles_per_seg = swar ? (p.tiles_per_seg_wide + 1) / 2 : p.tiles_per_seg_wide;
@@ -360,7 +365,7 @@ place_kernel(const PlaceParams p)
     // ---- epilogue: rank position -> node index and score ----
     if (split != 0) return;
     const uint32_t *order = p.order + (size_t)s * p.npad;
-    const double *score = p.score + (size_t)s * p.n_nodes;
+    const double *score = p.score_by_pos + (size_t)s * p.npad;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         if (!live[r]) continue;
@@ -370,7 +375,7 @@ place_kernel(const PlaceParams p)
         double sc = -1.0;
         if (best[r] >= 0) {
             idx = order[best[r]];
-            sc = score[idx];
+            sc = score[best[r]];
         }
         p.out_idx[pod] = idx;
         p.out_score[pod] = sc;

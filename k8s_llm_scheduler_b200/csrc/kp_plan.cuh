@@ -92,6 +92,7 @@ struct PlanOut {
     double *score;      // [3][n]
     double *uniq;       // [2][npad]
     uint32_t *order;    // [3][npad]
+    double *score_pos;  // [3][npad] score of the node at each rank position
     uint2 *ab;          // [3][npad]
     uint32_t *packed;   // [3][npad]
     int npad;
@@ -136,6 +137,7 @@ plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
     __shared__ uint32_t acc_pos[kKeyArrays][kCountNodes];               // accumulated in the leader CTA only
     __shared__ uint32_t acc_less[2][kCountNodes];
     __shared__ uint32_t acc_live[kMaxStrategies];
+    __shared__ double s_nscore[kMaxStrategies][kCountNodes];
 
     cg::cluster_group cluster = cg::this_cluster();
     const int crank = (int)cluster.block_rank();
@@ -179,7 +181,7 @@ plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
             if (!is_row && crank == 0) {
 #pragma unroll
                 for (int s = 0; s < kMaxStrategies; ++s)
-                    if (strat_mask & (1 << s)) o.score[(size_t)s * n + id] = d.score[s];
+                    if (strat_mask & (1 << s)) { o.score[(size_t)s * n + id] = d.score[s]; s_nscore[s][i - mcount] = d.score[s]; }
             }
         }
 #pragma unroll
@@ -252,6 +254,7 @@ plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
             if (s_nkeys[s][lane] == ~0ull) continue;                      // ineligible: not in the table
             const uint32_t p = acc_pos[s][lane];
             o.order[(size_t)s * o.npad + p] = (uint32_t)node;
+            o.score_pos[(size_t)s * o.npad + p] = s_nscore[s][lane];
             o.ab[(size_t)s * o.npad + p] = r;
             o.packed[(size_t)s * o.npad + p] = pack_ranks(r.x, r.y);
         }
@@ -363,6 +366,7 @@ scatter_tables_kernel(const unsigned long long *__restrict__ keys, const uint32_
         if (n >= n_nodes || keys[(size_t)s * n_nodes + n] == ~0ull) continue;   // ineligible: not in the table
         const uint32_t p = pos[(size_t)s * n_nodes + n];
         o.order[(size_t)s * o.npad + p] = (uint32_t)n;
+        o.score_pos[(size_t)s * o.npad + p] = o.score[(size_t)s * n_nodes + n];
         o.ab[(size_t)s * o.npad + p] = r;
         o.packed[(size_t)s * o.npad + p] = swar ? pack_ranks(r.x, r.y) : kSwarGuards;
     }

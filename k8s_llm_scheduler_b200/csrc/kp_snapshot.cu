@@ -48,7 +48,7 @@ struct SnapLayout {
     int64_t slots;       // pod slots incl. per-strategy chunk padding
     int64_t chunks;      // pod chunks at the smallest chunk size (32)
     size_t off_header, off_chunk_done, zero_bytes;            // zeroed together (large-table plan)
-    size_t off_keys, off_score, off_uniq, off_order, off_ab, off_packed, off_partial, off_perm;
+    size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_perm;
     size_t off_pos, off_kout, off_vout, off_iota, off_sorted, off_flag, off_incl, off_sort_tmp, off_best;   // large tables
     size_t sort_tmp_bytes, total;
 };
@@ -68,6 +68,7 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.zero_bytes = o;
     L.off_keys = o;    o = align_up(o + sizeof(uint64_t) * kKeyArrays * n);
     L.off_score = o;   o = align_up(o + sizeof(double) * kMaxStrategies * n);
+    L.off_score_pos = o; o = align_up(o + sizeof(double) * kMaxStrategies * L.npad);
     L.off_uniq = o;    o = align_up(o + sizeof(double) * 2 * L.npad);
     L.off_order = o;   o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
@@ -445,6 +446,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     po.score = reinterpret_cast<double *>(w + L.off_score);
     po.uniq = reinterpret_cast<double *>(w + L.off_uniq);
     po.order = reinterpret_cast<uint32_t *>(w + L.off_order);
+    po.score_pos = reinterpret_cast<double *>(w + L.off_score_pos);
     po.ab = reinterpret_cast<uint2 *>(w + L.off_ab);
     po.packed = reinterpret_cast<uint32_t *>(w + L.off_packed);
     po.npad = (int)L.npad;
@@ -513,6 +515,8 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.packed = po.packed;
     pp.order = po.order;
     pp.score = po.score;
+    pp.score_by_pos = po.score_pos;
+    pp.small_table_len = (!big && !per_pod) ? (int)((n + 3) / 4 * 4) : 0;
     pp.hdr = hdr;
     pp.chunk_done = reinterpret_cast<uint32_t *>(w + L.off_chunk_done);
     pp.best_pos = best_pos;
