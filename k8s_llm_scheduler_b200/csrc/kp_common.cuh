@@ -198,6 +198,11 @@ int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, in
                         int64_t *out_pod_count, double *out_cu, double *out_mu, void *ws,
                         size_t ws_bytes, cudaStream_t stream);
 size_t greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods);
+// kp_greedy_fast.cu: integer state-machine greedy; *done_flag (device) tells the fp64 kernel to skip
+size_t greedy_fast_workspace_bytes(int64_t n_nodes, int64_t n_pods);
+int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy, int filter_mode,
+                       int64_t *out_idx, double *out_score, int64_t *out_pc, double *out_cu, double *out_mu,
+                       void *ws, size_t ws_bytes, cudaStream_t stream, const uint32_t **done_flag);
 int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode,
                        double *out_score, double *out_free_cpu, double *out_free_mem,
                        uint8_t *out_eligible, cudaStream_t stream);

@@ -52,6 +52,7 @@ struct GreedyParams {
     double *out_score;
     long long *out_pc;
     double *out_cu, *out_mu;
+    const uint32_t *skip;        // device flag: non-zero = the fast path (kp_greedy_fast.cu) already did the work
 };
 
 struct Hot {
@@ -152,6 +153,7 @@ greedy_kernel(const GreedyParams g)
     __shared__ unsigned long long w_key[2][32];
     __shared__ uint32_t w_idx[2][32];
 
+    if (g.skip && *g.skip) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int KS = MULTI ? kMaxStrategies : 1;
     constexpr int NREG = NPT > 0 ? NPT : 1;
@@ -305,7 +307,7 @@ static GreedyLayout greedy_layout(int64_t n)
 size_t greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods)
 {
     if (n_nodes < 0 || n_pods < 0) return 0;
-    return greedy_layout(n_nodes).total;
+    return greedy_layout(n_nodes).total + greedy_fast_workspace_bytes(n_nodes, n_pods);
 }
 
 template <int NPT, bool MULTI>
@@ -334,8 +336,9 @@ int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, in
 {
     const int64_t n = nodes.n_nodes;
     const GreedyLayout L = greedy_layout(n);
-    if (!ws || ws_bytes < L.total || (reinterpret_cast<uintptr_t>(ws) & (kAlign - 1))) {
-        set_error("greedy workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", L.total,
+    const size_t need_bytes = greedy_workspace_bytes(n, pods.n_pods);
+    if (!ws || ws_bytes < need_bytes || (reinterpret_cast<uintptr_t>(ws) & (kAlign - 1))) {
+        set_error("greedy workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", need_bytes,
                   ws_bytes, ws);
         return KP_ERR_WORKSPACE;
     }
@@ -367,6 +370,11 @@ int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, in
     g.out_cu = out_cu;
     g.out_mu = out_mu;
     if (pods.n_pods == 0 && !out_pod_count && !out_cu && !out_mu) return KP_OK;
+
+    // fast path first (integer state machine); the fp64 kernel below runs only if its flag stays 0
+    const int fst = greedy_fast_device(nodes, pods, strategy, filter_mode, out_idx, out_score, out_pod_count, out_cu,
+                                       out_mu, w + L.total, ws_bytes - L.total, stream, &g.skip);
+    if (fst != KP_OK) return fst;
 
     const bool multi = pods.strategy_ids != nullptr;
     const int npt = (int)((n + kGreedyThreads - 1) / kGreedyThreads);

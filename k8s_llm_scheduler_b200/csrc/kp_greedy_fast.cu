@@ -1,0 +1,626 @@
+// Greedy placement, fast path: the sequential commit loop as an all-integer state machine.
+//
+// Same contract as kp_greedy.cu (reference loop scheduler.py:690-729 -> :598 -> :144-151,
+// capacity filter of SURVEY.md A13); bit-identical results, different mechanics:
+//
+//  * After its first commit a node's state depends only on its SHAPE (allocatable cpu,
+//    allocatable memory, max_pods) and its pod count.  Nodes of one shape share a TRAJECTORY
+//    of states indexed by pod count, so a commit is a shared-memory table lookup instead of a
+//    chain of fp64 divisions on the critical path.  (Clusters are built from instance types:
+//    a handful of shapes.  More than 128 shapes, or trajectories longer than 4096 states in
+//    total, fall back to kp_greedy.cu.)
+//  * Every state that can occur -- each node's initial state and every trajectory state --
+//    is computed ONCE with the exact fp64 routines, then rank-compressed (radix sort + scan of
+//    run starts): thresholds become dense ranks packed in one 32-bit word with guard bits (the
+//    snapshot kernel's SWAR test), scores become dense ranks, and a node's key is
+//    (score rank << idx bits) | (idx mask - node index): ONE unsigned compare orders nodes by
+//    (score desc, index asc) -- the reference's strict '>' with first-in-list-order ties.
+//  * A node's hot state is therefore two registers; the per-pod block arg-max is one REDUX.MAX
+//    per warp, one barrier, one more REDUX.MAX; the winner's index is read back out of the key.
+//  * Tables that exceed one CTA's registers run on a thread-block CLUSTER (2, 4 or 8 CTAs):
+//    per pod each CTA stores its best key into every peer's shared memory (DSMEM) and a
+//    cluster barrier completes the exchange.
+//
+// Whether the preconditions hold is decided on the device (ok flag); the fp64 kernel is always
+// launched behind this path and returns at once when the flag says the work is done.
+#include <algorithm>
+#include <cooperative_groups.h>
+
+#include "kp_common.cuh"
+
+namespace kp {
+
+namespace cg = cooperative_groups;
+
+constexpr int kFastThreads = 1024;
+constexpr int kFastMaxShapes = 128;
+constexpr int kFastMaxTraj = 4096;             // trajectory states kept in shared memory
+constexpr int kFastPodBatch = 1024;
+constexpr uint32_t kFastGuards = 0x80008000u;
+constexpr uint32_t kFastMaxDistinct = 32000;
+constexpr uint32_t kNoEntry = 0xffffffffu;
+
+struct FastHeader {
+    uint32_t ok;               // 1 = fast path valid (set by the prep kernels, read by both greedy kernels)
+    uint32_t n_shapes;
+    uint32_t traj_total;
+    uint32_t distinct[2];
+    uint32_t score_ranks[kMaxStrategies];
+    uint32_t traj_base[kFastMaxShapes + 1];
+    long long shape_cpu[kFastMaxShapes], shape_mem[kFastMaxShapes], shape_mp[kFastMaxShapes];
+};
+
+struct FastIn {
+    const long long *alloc_cpu, *alloc_mem, *pod_count0, *max_pods;
+    const uint8_t *ready;
+    const double *cu0, *mu0;
+    int n;
+    const long long *req_cpu, *req_mem, *sid;
+    long long n_pods;
+    int uniform_strategy, strat_mask;
+};
+
+// ---------------------------------------------------------------------------------------
+// 1. shapes: dedupe (alloc_cpu, alloc_mem, max_pods) over the nodes that can ever be chosen
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024, 1)
+fast_shapes_kernel(FastIn in, FastHeader *hdr, uint32_t *__restrict__ shape_id)
+{
+    __shared__ long long s_cpu[kFastMaxShapes], s_mem[kFastMaxShapes], s_mp[kFastMaxShapes];
+    __shared__ int s_count, s_pending, s_overflow;
+    const int tid = threadIdx.x;
+    if (tid == 0) { s_count = 0; s_pending = 0x7fffffff; s_overflow = 0; }
+    __syncthreads();
+    bool bad_value = false;
+    for (int base = 0; base < in.n; base += 1024) {
+        const int n = base + tid;
+        long long c = 0, m = 0, mp = 0;
+        bool want = false;
+        if (n < in.n) {
+            c = in.alloc_cpu[n]; m = in.alloc_mem[n]; mp = in.max_pods[n];
+            const long long pc = in.pod_count0[n];
+            want = in.ready[n] != 0 && mp > 0 && pc < mp;            // otherwise never chosen, never committed
+            if (want && (pc < 0 || mp >= (1ll << 24))) bad_value = true;
+        }
+        int found = -1;
+        for (;;) {
+            const int cnt = s_count;
+            if (want && found < 0)
+                for (int q = 0; q < cnt; ++q)
+                    if (s_cpu[q] == c && s_mem[q] == m && s_mp[q] == mp) { found = q; break; }
+            if (want && found < 0) atomicMin(&s_pending, n);
+            __syncthreads();
+            const int who = s_pending;
+            if (who == 0x7fffffff) break;                            // block-uniform
+            if (n == who) {
+                if (cnt < kFastMaxShapes) { s_cpu[cnt] = c; s_mem[cnt] = m; s_mp[cnt] = mp; s_count = cnt + 1; }
+                else { s_overflow = 1; }
+            }
+            __syncthreads();
+            if (tid == 0) s_pending = 0x7fffffff;
+            if (s_overflow) { want = false; }
+            __syncthreads();
+        }
+        __syncthreads();
+        if (n < in.n) shape_id[n] = found >= 0 ? (uint32_t)found : kNoEntry;
+    }
+    const int any_bad = __syncthreads_or(bad_value ? 1 : 0);
+    if (tid == 0) {
+        uint32_t total = 0;
+        const int cnt = s_count;
+        for (int q = 0; q < cnt; ++q) {
+            hdr->traj_base[q] = total;
+            hdr->shape_cpu[q] = s_cpu[q]; hdr->shape_mem[q] = s_mem[q]; hdr->shape_mp[q] = s_mp[q];
+            total += (uint32_t)s_mp[q] + 1u;                          // states pod_count = 0 .. max_pods
+            if (total > (1u << 30)) total = 1u << 30;
+        }
+        hdr->traj_base[cnt] = total;
+        hdr->n_shapes = (uint32_t)cnt;
+        hdr->traj_total = total;
+        hdr->ok = (!s_overflow && !any_bad && total <= (uint32_t)kFastMaxTraj) ? 1u : 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// 2. every state that can occur: entries [0, n) = the nodes' initial states,
+//    entries [n, n + kFastMaxTraj) = trajectory states (shape, pod_count)
+// ---------------------------------------------------------------------------------------
+struct FastEntries {
+    unsigned long long *key_t[2];                 // order keys of free cpu / free memory
+    unsigned long long *key_s[kMaxStrategies];    // order keys of the score (0 = state cannot be chosen)
+    double *score[kMaxStrategies];                // fp64 score of the state
+};
+
+__global__ void __launch_bounds__(256)
+fast_entries_kernel(FastIn in, const FastHeader *__restrict__ hdr, FastEntries e, uint32_t *__restrict__ iota)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = in.n + kFastMaxTraj;
+    if (i >= total) return;
+    iota[i] = (uint32_t)i;
+    double cu = 0, mu = 0, avail_cpu = 0, avail_mem = 0;
+    long long pc = 0, mp = 0;
+    bool exists = false, ready = true;
+    if (i < in.n) {
+        exists = true;
+        cu = in.cu0[i]; mu = in.mu0[i]; pc = in.pod_count0[i]; mp = in.max_pods[i];
+        ready = in.ready[i] != 0;
+        avail_cpu = __ddiv_rn((double)in.alloc_cpu[i], 1000.0);
+        avail_mem = bytes_to_gib(in.alloc_mem[i]);
+    } else if (hdr->ok) {
+        const uint32_t t = (uint32_t)(i - in.n);
+        if (t < hdr->traj_total) {
+            int s = 0;
+            const int ns = (int)hdr->n_shapes;
+            while (s + 1 < ns && hdr->traj_base[s + 1] <= t) ++s;
+            exists = true;
+            mp = hdr->shape_mp[s];
+            pc = (long long)(t - hdr->traj_base[s]);
+            cu = mu = usage_a3(pc, mp);                                // scheduler.py:150-151
+            avail_cpu = __ddiv_rn((double)hdr->shape_cpu[s], 1000.0);
+            avail_mem = bytes_to_gib(hdr->shape_mem[s]);
+        }
+    }
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
+    double ta = inf, tb = inf;
+    bool ok = false;
+    if (exists) {
+        ta = __ddiv_rn(__dmul_rn(avail_cpu, __dsub_rn(100.0, cu)), 100.0);   // scheduler.py:232
+        tb = __ddiv_rn(__dmul_rn(avail_mem, __dsub_rn(100.0, mu)), 100.0);   // scheduler.py:233
+        ok = ready && pc < mp && ta == ta && tb == tb;
+        if (ta != ta) ta = inf;
+        if (tb != tb) tb = inf;
+    }
+    e.key_t[0][i] = f64_order_key(ta);
+    e.key_t[1][i] = f64_order_key(tb);
+#pragma unroll
+    for (int s = 0; s < kMaxStrategies; ++s) {
+        if (!(in.strat_mask & (1 << s))) continue;
+        NodeScore ns;
+        ns.key = 0ull; ns.score = -1.0;
+        if (exists) ns = node_score(s, cu, mu, pc, mp);
+        e.key_s[s][i] = ok ? ns.key : 0ull;
+        e.score[s][i] = ns.score;
+    }
+}
+
+// after a sort of one key array: run starts of the sorted keys
+__global__ void __launch_bounds__(256)
+fast_flags_kernel(const unsigned long long *__restrict__ kout, int total, uint32_t *__restrict__ flag)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < total) flag[i] = (i == 0 || kout[i] != kout[i - 1]) ? 1u : 0u;
+}
+
+// dense rank back to the entries; unique values (thresholds only); number of distinct values
+__global__ void __launch_bounds__(256)
+fast_rank_kernel(const unsigned long long *__restrict__ kout, const uint32_t *__restrict__ vout,
+                 const uint32_t *__restrict__ flag, const uint32_t *__restrict__ incl, int total,
+                 uint32_t *__restrict__ rank, double *__restrict__ uniq, uint32_t *__restrict__ n_distinct)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const uint32_t d = incl[i] - 1;
+    rank[vout[i]] = d;
+    if (uniq && flag[i]) {
+        const unsigned long long k = kout[i];
+        const unsigned long long b = (k >> 63) ? (k ^ 0x8000000000000000ull) : ~k;
+        uniq[d] = __longlong_as_double((long long)b);
+    }
+    if (i == total - 1) *n_distinct = d + 1;
+}
+
+// packed threshold word and per-strategy score rank of every entry; final validity check
+__global__ void __launch_bounds__(256)
+fast_pack_kernel(FastIn in, FastHeader *hdr, const uint32_t *__restrict__ rank_t0, const uint32_t *__restrict__ rank_t1,
+                 const uint32_t *__restrict__ rank_s, const unsigned long long *__restrict__ key_s0, int total,
+                 int idx_bits, uint32_t *__restrict__ entry_w, uint32_t *__restrict__ entry_key)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        bool ok = hdr->ok != 0 && hdr->distinct[0] <= kFastMaxDistinct && hdr->distinct[1] <= kFastMaxDistinct;
+#pragma unroll
+        for (int s = 0; s < kMaxStrategies; ++s)
+            if ((in.strat_mask & (1 << s)) && (hdr->score_ranks[s] + 1u) >= (1u << (32 - idx_bits))) ok = false;
+        hdr->ok = ok ? 1u : 0u;
+    }
+    if (i >= total) return;
+    entry_w[i] = (((rank_t1[i] + 1u) | 0x8000u) << 16) | ((rank_t0[i] + 1u) | 0x8000u);
+#pragma unroll
+    for (int s = 0; s < kMaxStrategies; ++s) {
+        if (!(in.strat_mask & (1 << s))) continue;
+        const bool can = key_s0[(size_t)s * total + i] != 0ull;
+        entry_key[(size_t)s * total + i] = can ? rank_s[(size_t)s * total + i] + 1u : 0u;     // 0 = cannot be chosen
+    }
+}
+
+__device__ __forceinline__ int lower_bound_lt_g(const double *arr, int n, double x)
+{
+    int lo = 0;
+    for (int step = 1 << (31 - __clz(n | 1)); step > 0; step >>= 1) {
+        const int nxt = lo + step;
+        if (nxt <= n && arr[nxt - 1] < x) lo = nxt;
+    }
+    return lo;
+}
+
+// pods -> packed request ranks
+__global__ void __launch_bounds__(256)
+fast_pods_kernel(FastIn in, const FastHeader *__restrict__ hdr, const double *__restrict__ uniq0,
+                 const double *__restrict__ uniq1, uint32_t *__restrict__ xs)
+{
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= in.n_pods || !hdr->ok) return;
+    const uint32_t ra = (uint32_t)lower_bound_lt_g(uniq0, (int)hdr->distinct[0], req_cores(in.req_cpu[j]));
+    const uint32_t rb = (uint32_t)lower_bound_lt_g(uniq1, (int)hdr->distinct[1], req_gib(in.req_mem[j]));
+    xs[j] = ((rb + 1u) << 16) | (ra + 1u);
+}
+
+// ---------------------------------------------------------------------------------------
+// 3. the greedy loop
+// ---------------------------------------------------------------------------------------
+struct FastRun {
+    const FastHeader *hdr;
+    const uint32_t *shape_id;      // [n]
+    const uint32_t *entry_w;       // [total]
+    const uint32_t *entry_key;     // [3][total]
+    const uint32_t *xs;            // [P]
+    uint32_t *out_entry;           // [P] entry index of the chosen node's state at decision time
+    long long *out_idx;
+    long long *out_pc;             // final pod counts (may be NULL)
+    double *out_cu, *out_mu;
+    int total, idx_bits, nodes_per_cta;
+};
+
+// dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | pc[nodes_per_cta] | shape[nodes_per_cta]
+template <int NPT, bool MULTI>
+__global__ void __launch_bounds__(kFastThreads, 1)
+fast_greedy_kernel(FastIn in, FastRun r)
+{
+    extern __shared__ __align__(16) unsigned char fsm[];
+    __shared__ uint32_t s_x[kFastPodBatch];
+    __shared__ uint8_t s_sid[kFastPodBatch];
+    __shared__ uint32_t w_res[2][32];
+    __shared__ uint32_t c_res[2][8];
+
+    if (!r.hdr->ok) return;                                           // the fp64 kernel does the work instead
+    constexpr int KS = MULTI ? kMaxStrategies : 1;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int csize = (int)cluster.num_blocks();
+    const int crank = (int)cluster.block_rank();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int total = r.total;
+    uint32_t *traj_w = reinterpret_cast<uint32_t *>(fsm);
+    uint32_t *traj_key = traj_w + kFastMaxTraj;
+    uint32_t *c_pc = traj_key + KS * kFastMaxTraj;
+    uint32_t *c_shape = c_pc + r.nodes_per_cta;                        // bit 31: the node has been committed to
+    const int us = in.uniform_strategy;
+    const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
+    const int cta_base = crank * r.nodes_per_cta;
+
+    for (int i = tid; i < kFastMaxTraj; i += kFastThreads) {
+        traj_w[i] = r.entry_w[in.n + i];
+#pragma unroll
+        for (int q = 0; q < KS; ++q) traj_key[q * kFastMaxTraj + i] = r.entry_key[(size_t)(MULTI ? q : us) * total + in.n + i];
+    }
+    uint32_t w[NPT], key[KS][NPT];
+#pragma unroll
+    for (int k = 0; k < NPT; ++k) {
+        const int local = k * kFastThreads + tid;
+        const int n = cta_base + local;
+        w[k] = kFastGuards;                                            // fields 0: nothing fits
+#pragma unroll
+        for (int q = 0; q < KS; ++q) key[q][k] = 0u;
+        if (local < r.nodes_per_cta && n < in.n) {
+            w[k] = r.entry_w[n];
+#pragma unroll
+            for (int q = 0; q < KS; ++q) {
+                const uint32_t kr = r.entry_key[(size_t)(MULTI ? q : us) * total + n];
+                key[q][k] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
+            }
+            c_pc[local] = (uint32_t)in.pod_count0[n];
+            c_shape[local] = r.shape_id[n] & 0x7fffffffu;
+        }
+    }
+    __syncthreads();
+
+    for (long long base = 0; base < in.n_pods; base += kFastPodBatch) {
+        const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
+        __syncthreads();
+        if (tid < cnt) {
+            s_x[tid] = r.xs[base + tid];
+            s_sid[tid] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + tid]) : us);
+        }
+        __syncthreads();
+        for (int j = 0; j < cnt; ++j) {
+            const uint32_t x = s_x[j];
+            const int s = s_sid[j];
+            uint32_t best = 0u;
+#pragma unroll
+            for (int k = 0; k < NPT; ++k) {
+                const uint32_t t = w[k] - x;                           // both guard bits survive iff the pod fits
+                uint32_t kk;
+                if (MULTI) kk = s == 0 ? key[0][k] : (s == 1 ? key[KS > 1 ? 1 : 0][k] : key[KS > 2 ? 2 : 0][k]);
+                else kk = key[0][k];
+                const uint32_t cand = ((~t) & kFastGuards) ? 0u : kk;
+                best = max(best, cand);
+            }
+            const int par = j & 1;
+            best = __reduce_max_sync(0xffffffffu, best);
+            if (lane == 0) w_res[par][warp] = best;
+            __syncthreads();
+            best = __reduce_max_sync(0xffffffffu, w_res[par][lane]);
+            if (csize > 1) {
+                if (tid < csize) *cluster.map_shared_rank(&c_res[par][crank], tid) = best;    // to every CTA of the cluster
+                cluster.sync();
+                uint32_t g = 0u;
+                for (int c = 0; c < csize; ++c) g = max(g, c_res[par][c]);
+                best = g;
+            }
+            if (best == 0u) {
+                if (crank == 0 && tid == 0) { r.out_idx[base + j] = -1; r.out_entry[base + j] = kNoEntry; }
+                continue;
+            }
+            const int n = (int)(idx_mask - (best & idx_mask));
+            const int local = n - cta_base;
+            if (local >= 0 && local < r.nodes_per_cta && (local & (kFastThreads - 1)) == tid) {
+                // commit (scheduler.py:598 -> :144-151): one more pod, next state of the shape's trajectory
+                const uint32_t sh = c_shape[local];
+                const uint32_t pc = c_pc[local];
+                const uint32_t tbase = r.hdr->traj_base[sh & 0x7fffffffu];
+                r.out_idx[base + j] = n;
+                r.out_entry[base + j] = (sh >> 31) ? (uint32_t)in.n + tbase + pc : (uint32_t)n;
+                const uint32_t t2 = tbase + pc + 1u;
+                c_pc[local] = pc + 1u;
+                c_shape[local] = sh | 0x80000000u;
+                const uint32_t nw = traj_w[t2];
+                uint32_t nk[KS];
+#pragma unroll
+                for (int q = 0; q < KS; ++q) {
+                    const uint32_t kr = traj_key[q * kFastMaxTraj + t2];
+                    nk[q] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
+                }
+                const int kidx = local / kFastThreads;
+#pragma unroll
+                for (int k = 0; k < NPT; ++k) {
+                    if (k == kidx) {
+                        w[k] = nw;
+#pragma unroll
+                        for (int q = 0; q < KS; ++q) key[q][k] = nk[q];
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // final state: usage follows scheduler.py:150-151 for every node that received a pod
+    for (int local = tid; local < r.nodes_per_cta; local += kFastThreads) {
+        const int n = cta_base + local;
+        if (n >= in.n) break;
+        const bool touched = (c_shape[local] >> 31) != 0;
+        const long long pc = touched ? (long long)c_pc[local] : in.pod_count0[n];
+        const double u = usage_a3(pc, in.max_pods[n]);
+        if (r.out_pc) r.out_pc[n] = pc;
+        if (r.out_cu) r.out_cu[n] = touched ? u : in.cu0[n];
+        if (r.out_mu) r.out_mu[n] = touched ? u : in.mu0[n];
+    }
+}
+
+// scores of the chosen states, in parallel over the pods
+__global__ void __launch_bounds__(256)
+fast_scores_kernel(FastIn in, const FastHeader *__restrict__ hdr, const uint32_t *__restrict__ out_entry,
+                   const double *__restrict__ score, int total, double *__restrict__ out_score)
+{
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= in.n_pods || !hdr->ok) return;
+    const uint32_t e = out_entry[j];
+    const int s = in.sid ? canon_strategy(in.sid[j]) : in.uniform_strategy;
+    out_score[j] = e == kNoEntry ? -1.0 : score[(size_t)s * total + e];
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+struct FastLayout {
+    int64_t total;
+    size_t off_hdr, off_shape, off_iota, off_keys, off_score, off_kout, off_vout, off_flag, off_incl, off_rank,
+        off_uniq, off_w, off_key32, off_xs, off_entry, off_tmp, tmp_bytes, bytes;
+};
+
+static FastLayout fast_layout(int64_t n, int64_t p)
+{
+    FastLayout L{};
+    L.total = n + kFastMaxTraj;
+    const size_t T = (size_t)L.total;
+    size_t o = 0;
+    L.off_hdr = o;   o = align_up(o + sizeof(FastHeader));
+    L.off_shape = o; o = align_up(o + sizeof(uint32_t) * n);
+    L.off_iota = o;  o = align_up(o + sizeof(uint32_t) * T);
+    L.off_keys = o;  o = align_up(o + sizeof(uint64_t) * 5 * T);
+    L.off_score = o; o = align_up(o + sizeof(double) * kMaxStrategies * T);
+    L.off_kout = o;  o = align_up(o + sizeof(uint64_t) * T);
+    L.off_vout = o;  o = align_up(o + sizeof(uint32_t) * T);
+    L.off_flag = o;  o = align_up(o + sizeof(uint32_t) * T);
+    L.off_incl = o;  o = align_up(o + sizeof(uint32_t) * T);
+    L.off_rank = o;  o = align_up(o + sizeof(uint32_t) * 5 * T);
+    L.off_uniq = o;  o = align_up(o + sizeof(double) * 2 * T);
+    L.off_w = o;     o = align_up(o + sizeof(uint32_t) * T);
+    L.off_key32 = o; o = align_up(o + sizeof(uint32_t) * kMaxStrategies * T);
+    L.off_xs = o;    o = align_up(o + sizeof(uint32_t) * p);
+    L.off_entry = o; o = align_up(o + sizeof(uint32_t) * p);
+    L.tmp_bytes = sort_temp_bytes(L.total);
+    L.off_tmp = o;   o = align_up(o + L.tmp_bytes);
+    L.bytes = o;
+    return L;
+}
+
+constexpr int64_t kFastMinPods = 2048;         // below this the set-up costs more than it saves
+constexpr int kFastMaxNpt = 20;
+
+static int ceil_log2(int64_t v) { int b = 0; while ((1ll << b) < v) ++b; return b; }
+
+// Can the fast path be attempted for this call?  (Host-side, sizes only.)
+static bool fast_eligible(int64_t n, int64_t p, int filter_mode, bool multi, int *cluster, int *npt, int *idx_bits)
+{
+    if (filter_mode != KP_FILTER_CAPACITY || p < kFastMinPods || n < 1) return false;
+    if (const char *off = getenv("KP_GREEDY_NO_FAST")) if (off[0] == '1') return false;
+    const int ib = std::max(1, ceil_log2(n));
+    if (ib + ceil_log2(n + kFastMaxTraj + 2) > 32) return false;      // key = score rank | inverted index
+    const int max_npt = multi ? 10 : kFastMaxNpt;                     // registers: (1 + KS) words per node
+    int c = 1;
+    if (const char *force = getenv("KP_GREEDY_CLUSTER")) c = std::max(1, std::min(8, atoi(force)));
+    for (;; c *= 2) {
+        if (c > 8) return false;
+        const int64_t per_cta = (n + c - 1) / c;
+        const int need = (int)((per_cta + kFastThreads - 1) / kFastThreads);
+        const size_t smem = sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)need * kFastThreads;
+        if (need <= max_npt && smem <= 200 * 1024) { *cluster = c; *npt = need; break; }
+    }
+    *idx_bits = ib;
+    return true;
+}
+
+size_t greedy_fast_workspace_bytes(int64_t n, int64_t p)
+{
+    return fast_layout(n, p).bytes;
+}
+
+template <int NPT, bool MULTI>
+static int launch_fast(const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<NPT, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cluster, 1, 1);
+    cfg.blockDim = dim3(kFastThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    KP_CUDA(cudaLaunchKernelEx(&cfg, fast_greedy_kernel<NPT, MULTI>, in, r));
+    count_launch();
+    return KP_OK;
+}
+
+template <bool MULTI>
+static int dispatch_fast(int npt, const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
+{
+    if (npt <= 1) return launch_fast<1, MULTI>(in, r, cluster, smem, stream);
+    if (npt <= 2) return launch_fast<2, MULTI>(in, r, cluster, smem, stream);
+    if (npt <= 3) return launch_fast<3, MULTI>(in, r, cluster, smem, stream);
+    if (npt <= 5) return launch_fast<5, MULTI>(in, r, cluster, smem, stream);
+    if (npt <= 10) return launch_fast<10, MULTI>(in, r, cluster, smem, stream);
+    if (MULTI) return KP_ERR_INVALID_ARG;
+    return launch_fast<kFastMaxNpt, false>(in, r, cluster, smem, stream);
+}
+
+// Runs the fast path when the sizes allow it.  *done_flag (device) is 1 afterwards iff the
+// results are complete; the caller launches the fp64 kernel with that flag as its skip switch.
+int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy, int filter_mode,
+                       int64_t *out_idx, double *out_score, int64_t *out_pc, double *out_cu, double *out_mu,
+                       void *ws, size_t ws_bytes, cudaStream_t stream, const uint32_t **done_flag)
+{
+    *done_flag = nullptr;
+    const int64_t n = nodes.n_nodes, p = pods.n_pods;
+    const bool multi = pods.strategy_ids != nullptr;
+    int cluster = 1, npt = 1, idx_bits = 1;
+    if (!fast_eligible(n, p, filter_mode, multi, &cluster, &npt, &idx_bits)) return KP_OK;
+    const FastLayout L = fast_layout(n, p);
+    if (!ws || ws_bytes < L.bytes) return KP_OK;                     // not enough scratch: fp64 kernel only
+    unsigned char *w = static_cast<unsigned char *>(ws);
+    FastHeader *hdr = reinterpret_cast<FastHeader *>(w + L.off_hdr);
+    const int total = (int)L.total;
+
+    FastIn in{};
+    in.alloc_cpu = (const long long *)nodes.alloc_cpu_milli;
+    in.alloc_mem = (const long long *)nodes.alloc_mem_bytes;
+    in.pod_count0 = (const long long *)nodes.pod_count;
+    in.max_pods = (const long long *)nodes.max_pods;
+    in.ready = nodes.ready;
+    in.cu0 = nodes.cpu_usage_pct;
+    in.mu0 = nodes.mem_usage_pct;
+    in.n = (int)n;
+    in.req_cpu = (const long long *)pods.req_cpu_milli;
+    in.req_mem = (const long long *)pods.req_mem_bytes;
+    in.sid = (const long long *)pods.strategy_ids;
+    in.n_pods = p;
+    in.uniform_strategy = canon_strategy(strategy);
+    in.strat_mask = multi ? 7 : (1 << in.uniform_strategy);
+
+    uint32_t *shape_id = reinterpret_cast<uint32_t *>(w + L.off_shape);
+    uint32_t *iota = reinterpret_cast<uint32_t *>(w + L.off_iota);
+    unsigned long long *keys = reinterpret_cast<unsigned long long *>(w + L.off_keys);
+    double *score = reinterpret_cast<double *>(w + L.off_score);
+    unsigned long long *kout = reinterpret_cast<unsigned long long *>(w + L.off_kout);
+    uint32_t *vout = reinterpret_cast<uint32_t *>(w + L.off_vout);
+    uint32_t *flag = reinterpret_cast<uint32_t *>(w + L.off_flag);
+    uint32_t *incl = reinterpret_cast<uint32_t *>(w + L.off_incl);
+    uint32_t *rank = reinterpret_cast<uint32_t *>(w + L.off_rank);
+    double *uniq = reinterpret_cast<double *>(w + L.off_uniq);
+    uint32_t *entry_w = reinterpret_cast<uint32_t *>(w + L.off_w);
+    uint32_t *key32 = reinterpret_cast<uint32_t *>(w + L.off_key32);
+    uint32_t *xs = reinterpret_cast<uint32_t *>(w + L.off_xs);
+    uint32_t *out_entry = reinterpret_cast<uint32_t *>(w + L.off_entry);
+    void *tmp = w + L.off_tmp;
+
+    fast_shapes_kernel<<<1, 1024, 0, stream>>>(in, hdr, shape_id);
+    KP_LAUNCH_CHECK("fast_shapes_kernel");
+    FastEntries e{};
+    e.key_t[0] = keys + (size_t)3 * total;
+    e.key_t[1] = keys + (size_t)4 * total;
+    for (int s = 0; s < kMaxStrategies; ++s) { e.key_s[s] = keys + (size_t)s * total; e.score[s] = score + (size_t)s * total; }
+    const int gb = (total + 255) / 256;
+    fast_entries_kernel<<<gb, 256, 0, stream>>>(in, hdr, e, iota);
+    KP_LAUNCH_CHECK("fast_entries_kernel");
+    for (int a = 0; a < 5; ++a) {                                     // 0..2 score orders, 3..4 thresholds
+        if (a < kMaxStrategies && !(in.strat_mask & (1 << a))) continue;
+        int st = sort_pairs_u64(tmp, L.tmp_bytes, keys + (size_t)a * total, kout, iota, vout, total, stream);
+        if (st != KP_OK) return st;
+        fast_flags_kernel<<<gb, 256, 0, stream>>>(kout, total, flag);
+        KP_LAUNCH_CHECK("fast_flags_kernel");
+        st = inclusive_sum_u32(tmp, L.tmp_bytes, flag, incl, total, stream);
+        if (st != KP_OK) return st;
+        fast_rank_kernel<<<gb, 256, 0, stream>>>(kout, vout, flag, incl, total, rank + (size_t)a * total,
+                                                 a >= kMaxStrategies ? uniq + (size_t)(a - kMaxStrategies) * total : nullptr,
+                                                 a >= kMaxStrategies ? &hdr->distinct[a - kMaxStrategies] : &hdr->score_ranks[a]);
+        KP_LAUNCH_CHECK("fast_rank_kernel");
+    }
+    fast_pack_kernel<<<gb, 256, 0, stream>>>(in, hdr, rank + (size_t)3 * total, rank + (size_t)4 * total, rank, keys, total,
+                                             idx_bits, entry_w, key32);
+    KP_LAUNCH_CHECK("fast_pack_kernel");
+    fast_pods_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, uniq, uniq + total, xs);
+    KP_LAUNCH_CHECK("fast_pods_kernel");
+
+    FastRun r{};
+    r.hdr = hdr;
+    r.shape_id = shape_id;
+    r.entry_w = entry_w;
+    r.entry_key = key32;
+    r.xs = xs;
+    r.out_entry = out_entry;
+    r.out_idx = (long long *)out_idx;
+    r.out_pc = (long long *)out_pc;
+    r.out_cu = out_cu;
+    r.out_mu = out_mu;
+    r.total = total;
+    r.idx_bits = idx_bits;
+    r.nodes_per_cta = npt * kFastThreads;
+    const size_t smem = sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)r.nodes_per_cta;
+    const int st = multi ? dispatch_fast<true>(npt, in, r, cluster, smem, stream)
+                         : dispatch_fast<false>(npt, in, r, cluster, smem, stream);
+    if (st != KP_OK) return st;
+    fast_scores_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, out_entry, score, total, out_score);
+    KP_LAUNCH_CHECK("fast_scores_kernel");
+    *done_flag = &hdr->ok;
+    return KP_OK;
+}
+
+}  // namespace kp

@@ -118,3 +118,69 @@ def test_session_greedy_matches_device_api():
         assert_same_idx(h[0], d[0])
         assert_same_f64(h[1], d[1])
         assert np.array_equal(h[2], d[2])
+
+
+# ---- fast path (kp_greedy_fast.cu): integer state machine, clusters, fallbacks --------------
+def _check_greedy(nodes, pods, sid, mode, per_pod=False, what=""):
+    g = device_greedy(nodes, pods, sid, mode, per_pod=per_pod)
+    o = oracle_greedy(nodes, pods, sid, mode, per_pod=per_pod)
+    assert_same_idx(g[0], o[0], what)
+    assert_same_f64(g[1], o[1], what + " score")
+    assert np.array_equal(g[2], o[2]), what + " final pod counts"
+    assert_same_f64(g[3], o[3], what + " cpu usage")
+    assert_same_f64(g[4], o[4], what + " mem usage")
+
+
+@pytest.mark.parametrize("cluster", ["1", "2", "4", "8"])
+def test_fast_path_on_clusters(cluster, monkeypatch):
+    """Force the thread-block-cluster variants (DSMEM exchange) on a table one CTA could hold."""
+    monkeypatch.setenv("KP_GREEDY_CLUSTER", cluster)
+    nodes, pods = synth.config5(3000, 6000, seed=31)
+    for sid in (0, 1, 2):
+        _check_greedy(nodes, pods, sid, 1, what=f"cluster={cluster} strategy={sid}")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what=f"cluster={cluster} per-pod")
+
+
+def test_fast_path_large_tables_and_depletion():
+    nodes, pods = synth.config5(20_000, 30_000, seed=32)          # one CTA, 20 nodes per thread
+    _check_greedy(nodes, pods, 0, 1, what="20k uniform")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="20k per-pod (cluster of 2)")
+    nodes, pods = synth.config3(400, 50_000)                       # fills up: trajectories run to max_pods
+    _check_greedy(nodes, pods, 0, 1, what="depletion")
+    g = device_greedy(nodes, pods, 0, 1)
+    assert (g[0] < 0).any() and (g[2] <= 110).all()
+
+
+def test_fast_path_matches_fp64_kernel(monkeypatch):
+    nodes, pods = synth.config5(2500, 5000, seed=33)
+    fast = device_greedy(nodes, pods, 0, 1, per_pod=True)
+    monkeypatch.setenv("KP_GREEDY_NO_FAST", "1")
+    slow = device_greedy(nodes, pods, 0, 1, per_pod=True)
+    for a, b in zip(fast, slow):
+        assert np.array_equal(np.asarray(a).view(np.uint64) if a.dtype == np.float64 else a,
+                              np.asarray(b).view(np.uint64) if b.dtype == np.float64 else b)
+
+
+def test_fast_path_falls_back_when_preconditions_fail():
+    rng = np.random.Generator(np.random.PCG64(34))
+    n, p = 1500, 4000
+    mp = rng.integers(20, 200, n)
+    pc = (rng.random(n) * mp).astype(np.int64)
+    u = synth.usage_a3(pc, mp)
+    # every node its own shape (> 128 shapes): the device-side check sends the work to the fp64 kernel
+    nodes = NodeTable.from_columns(alloc_cpu_milli=rng.integers(2000, 64000, n), alloc_mem_bytes=rng.integers(4, 512, n) << 30,
+                                   pod_count=pc, max_pods=mp, ready=(rng.random(n) > 0.05).astype(np.uint8),
+                                   cpu_usage_pct=u, mem_usage_pct=u.copy())
+    pods = PodTable.from_columns(rng.integers(50, 8000, p), rng.integers(64, 32 * 1024, p) << 20, rng.integers(0, 3, p))
+    _check_greedy(nodes, pods, 0, 1, what="many shapes")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="many shapes per-pod")
+    # few shapes but usage that does not follow scheduler.py:150-151: initial states are their own entries
+    nodes, pods = synth.config5(800, 5000, seed=35)
+    nodes.cpu_usage_pct[:] = np.round(rng.random(800) * 60, 2)
+    nodes.mem_usage_pct[:] = np.round(rng.random(800) * 60, 2)
+    for sid in (0, 1):
+        _check_greedy(nodes, pods, sid, 1, what=f"custom usage strategy={sid}")
+    # max_pods too large for a trajectory table
+    nodes, pods = synth.config2(50, 3000)
+    nodes.max_pods[:] = 1 << 25
+    _check_greedy(nodes, pods, 0, 1, what="huge max_pods")
