@@ -32,7 +32,7 @@ namespace kp {
 
 namespace cg = cooperative_groups;
 
-constexpr int kFastThreads = 1024;
+constexpr int kFastThreadsMax = 1024;       // greedy loop: 256 threads when the table fits, else 1024
 constexpr int kFastMaxShapes = 128;
 constexpr int kFastMaxTraj = 4096;             // trajectory states kept in shared memory
 constexpr int kFastPodBatch = 1024;
@@ -273,8 +273,10 @@ struct FastRun {
 };
 
 // dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | pc[nodes_per_cta] | shape[nodes_per_cta]
-template <int NPT, bool MULTI>
-__global__ void __launch_bounds__(kFastThreads, 1)
+// THREADS x NPT nodes per CTA.  Few fat warps beat many thin ones here: the per-pod cost that does
+// not scale with the table (reductions, barrier, winner decode) is paid per warp.
+template <int THREADS, int NPT, bool MULTI, bool CLUSTER>
+__global__ void __launch_bounds__(THREADS, 1)
 fast_greedy_kernel(FastIn in, FastRun r)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
@@ -282,12 +284,15 @@ fast_greedy_kernel(FastIn in, FastRun r)
     __shared__ uint8_t s_sid[kFastPodBatch];
     __shared__ uint32_t w_res[2][32];
     __shared__ uint32_t c_res[2][8];
+    __shared__ uint32_t s_tbase[kFastMaxShapes + 1];
 
     if (!r.hdr->ok) return;                                           // the fp64 kernel does the work instead
     constexpr int KS = MULTI ? kMaxStrategies : 1;
+    constexpr int kFastThreads = THREADS;
+    constexpr int NW = THREADS / 32;
     cg::cluster_group cluster = cg::this_cluster();
-    const int csize = (int)cluster.num_blocks();
-    const int crank = (int)cluster.block_rank();
+    const int csize = CLUSTER ? (int)cluster.num_blocks() : 1;
+    const int crank = CLUSTER ? (int)cluster.block_rank() : 0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = r.total;
     uint32_t *traj_w = reinterpret_cast<uint32_t *>(fsm);
@@ -298,6 +303,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
     const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
     const int cta_base = crank * r.nodes_per_cta;
 
+    if (tid <= kFastMaxShapes) s_tbase[tid] = r.hdr->traj_base[tid];
     for (int i = tid; i < kFastMaxTraj; i += kFastThreads) {
         traj_w[i] = r.entry_w[in.n + i];
 #pragma unroll
@@ -327,9 +333,9 @@ fast_greedy_kernel(FastIn in, FastRun r)
     for (long long base = 0; base < in.n_pods; base += kFastPodBatch) {
         const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
         __syncthreads();
-        if (tid < cnt) {
-            s_x[tid] = r.xs[base + tid];
-            s_sid[tid] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + tid]) : us);
+        for (int i = tid; i < cnt; i += kFastThreads) {
+            s_x[i] = r.xs[base + i];
+            s_sid[i] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + i]) : us);
         }
         __syncthreads();
         for (int j = 0; j < cnt; ++j) {
@@ -349,8 +355,8 @@ fast_greedy_kernel(FastIn in, FastRun r)
             best = __reduce_max_sync(0xffffffffu, best);
             if (lane == 0) w_res[par][warp] = best;
             __syncthreads();
-            best = __reduce_max_sync(0xffffffffu, w_res[par][lane]);
-            if (csize > 1) {
+            best = __reduce_max_sync(0xffffffffu, lane < NW ? w_res[par][lane] : 0u);
+            if (CLUSTER) {
                 if (tid < csize) *cluster.map_shared_rank(&c_res[par][crank], tid) = best;    // to every CTA of the cluster
                 cluster.sync();
                 uint32_t g = 0u;
@@ -363,11 +369,11 @@ fast_greedy_kernel(FastIn in, FastRun r)
             }
             const int n = (int)(idx_mask - (best & idx_mask));
             const int local = n - cta_base;
-            if (local >= 0 && local < r.nodes_per_cta && (local & (kFastThreads - 1)) == tid) {
+            if (local >= 0 && local < r.nodes_per_cta && (local % kFastThreads) == tid) {
                 // commit (scheduler.py:598 -> :144-151): one more pod, next state of the shape's trajectory
                 const uint32_t sh = c_shape[local];
                 const uint32_t pc = c_pc[local];
-                const uint32_t tbase = r.hdr->traj_base[sh & 0x7fffffffu];
+                const uint32_t tbase = s_tbase[sh & 0x7fu];
                 r.out_idx[base + j] = n;
                 r.out_entry[base + j] = (sh >> 31) ? (uint32_t)in.n + tbase + pc : (uint32_t)n;
                 const uint32_t t2 = tbase + pc + 1u;
@@ -459,25 +465,37 @@ constexpr int kFastMaxNpt = 20;
 
 static int ceil_log2(int64_t v) { int b = 0; while ((1ll << b) < v) ++b; return b; }
 
+struct FastShape { int threads, npt, cluster; };
+
+static size_t fast_smem_bytes(bool multi, int nodes_per_cta)
+{
+    return sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)nodes_per_cta;
+}
+
 // Can the fast path be attempted for this call?  (Host-side, sizes only.)
-static bool fast_eligible(int64_t n, int64_t p, int filter_mode, bool multi, int *cluster, int *npt, int *idx_bits)
+static bool fast_eligible(int64_t n, int64_t p, int filter_mode, bool multi, FastShape *shape, int *idx_bits)
 {
     if (filter_mode != KP_FILTER_CAPACITY || p < kFastMinPods || n < 1) return false;
     if (const char *off = getenv("KP_GREEDY_NO_FAST")) if (off[0] == '1') return false;
     const int ib = std::max(1, ceil_log2(n));
     if (ib + ceil_log2(n + kFastMaxTraj + 2) > 32) return false;      // key = score rank | inverted index
     const int max_npt = multi ? 10 : kFastMaxNpt;                     // registers: (1 + KS) words per node
+    *idx_bits = ib;
     int c = 1;
     if (const char *force = getenv("KP_GREEDY_CLUSTER")) c = std::max(1, std::min(8, atoi(force)));
+    if (c == 1 && n <= 256 * max_npt) {                               // one small CTA
+        *shape = FastShape{256, (int)((n + 255) / 256), 1};
+        return true;
+    }
     for (;; c *= 2) {
         if (c > 8) return false;
         const int64_t per_cta = (n + c - 1) / c;
-        const int need = (int)((per_cta + kFastThreads - 1) / kFastThreads);
-        const size_t smem = sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)need * kFastThreads;
-        if (need <= max_npt && smem <= 200 * 1024) { *cluster = c; *npt = need; break; }
+        const int need = (int)((per_cta + kFastThreadsMax - 1) / kFastThreadsMax);
+        if (need <= max_npt && fast_smem_bytes(multi, need * kFastThreadsMax) <= 200 * 1024) {
+            *shape = FastShape{kFastThreadsMax, need, c};
+            return true;
+        }
     }
-    *idx_bits = ib;
-    return true;
 }
 
 size_t greedy_fast_workspace_bytes(int64_t n, int64_t p)
@@ -485,17 +503,18 @@ size_t greedy_fast_workspace_bytes(int64_t n, int64_t p)
     return fast_layout(n, p).bytes;
 }
 
-template <int NPT, bool MULTI>
+template <int THREADS, int NPT, bool MULTI, bool CLUSTER>
 static int launch_fast(const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<NPT, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<THREADS, NPT, MULTI, CLUSTER>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(cluster, 1, 1);
-    cfg.blockDim = dim3(kFastThreads, 1, 1);
+    cfg.blockDim = dim3(THREADS, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -505,21 +524,28 @@ static int launch_fast(const FastIn &in, const FastRun &r, int cluster, size_t s
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KP_CUDA(cudaLaunchKernelEx(&cfg, fast_greedy_kernel<NPT, MULTI>, in, r));
+    KP_CUDA(cudaLaunchKernelEx(&cfg, fast_greedy_kernel<THREADS, NPT, MULTI, CLUSTER>, in, r));
     count_launch();
     return KP_OK;
 }
 
-template <bool MULTI>
-static int dispatch_fast(int npt, const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
+// node slots per thread are compiled in: 3, 5, 10 or 20 (10 at most with per-pod strategies)
+template <int THREADS, bool MULTI, bool CLUSTER>
+static int dispatch_npt(int npt, const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
 {
-    if (npt <= 1) return launch_fast<1, MULTI>(in, r, cluster, smem, stream);
-    if (npt <= 2) return launch_fast<2, MULTI>(in, r, cluster, smem, stream);
-    if (npt <= 3) return launch_fast<3, MULTI>(in, r, cluster, smem, stream);
-    if (npt <= 5) return launch_fast<5, MULTI>(in, r, cluster, smem, stream);
-    if (npt <= 10) return launch_fast<10, MULTI>(in, r, cluster, smem, stream);
+    if (npt <= 3) return launch_fast<THREADS, 3, MULTI, CLUSTER>(in, r, cluster, smem, stream);
+    if (npt <= 5) return launch_fast<THREADS, 5, MULTI, CLUSTER>(in, r, cluster, smem, stream);
+    if (npt <= 10) return launch_fast<THREADS, 10, MULTI, CLUSTER>(in, r, cluster, smem, stream);
     if (MULTI) return KP_ERR_INVALID_ARG;
-    return launch_fast<kFastMaxNpt, false>(in, r, cluster, smem, stream);
+    return launch_fast<THREADS, kFastMaxNpt, false, CLUSTER>(in, r, cluster, smem, stream);
+}
+
+template <bool MULTI>
+static int dispatch_fast(const FastShape &sh, const FastIn &in, const FastRun &r, size_t smem, cudaStream_t stream)
+{
+    if (sh.threads == 256) return dispatch_npt<256, MULTI, false>(sh.npt, in, r, 1, smem, stream);
+    if (sh.cluster == 1) return dispatch_npt<kFastThreadsMax, MULTI, false>(sh.npt, in, r, 1, smem, stream);
+    return dispatch_npt<kFastThreadsMax, MULTI, true>(sh.npt, in, r, sh.cluster, smem, stream);
 }
 
 // Runs the fast path when the sizes allow it.  *done_flag (device) is 1 afterwards iff the
@@ -531,8 +557,9 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
     *done_flag = nullptr;
     const int64_t n = nodes.n_nodes, p = pods.n_pods;
     const bool multi = pods.strategy_ids != nullptr;
-    int cluster = 1, npt = 1, idx_bits = 1;
-    if (!fast_eligible(n, p, filter_mode, multi, &cluster, &npt, &idx_bits)) return KP_OK;
+    FastShape shape{};
+    int idx_bits = 1;
+    if (!fast_eligible(n, p, filter_mode, multi, &shape, &idx_bits)) return KP_OK;
     const FastLayout L = fast_layout(n, p);
     if (!ws || ws_bytes < L.bytes) return KP_OK;                     // not enough scratch: fp64 kernel only
     unsigned char *w = static_cast<unsigned char *>(ws);
@@ -612,10 +639,10 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
     r.out_mu = out_mu;
     r.total = total;
     r.idx_bits = idx_bits;
-    r.nodes_per_cta = npt * kFastThreads;
-    const size_t smem = sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)r.nodes_per_cta;
-    const int st = multi ? dispatch_fast<true>(npt, in, r, cluster, smem, stream)
-                         : dispatch_fast<false>(npt, in, r, cluster, smem, stream);
+    r.nodes_per_cta = shape.npt * shape.threads;
+    const size_t smem = fast_smem_bytes(multi, r.nodes_per_cta);
+    const int st = multi ? dispatch_fast<true>(shape, in, r, smem, stream)
+                         : dispatch_fast<false>(shape, in, r, smem, stream);
     if (st != KP_OK) return st;
     fast_scores_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, out_entry, score, total, out_score);
     KP_LAUNCH_CHECK("fast_scores_kernel");
