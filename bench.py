@@ -77,6 +77,12 @@ def make_workload(name: str, rank: int):
         return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=False,
                                  desc="c3: resource_balanced greedy commit, 5000 nodes x 1000000 pods per GPU, "
                                       "capacity filter (replicas at N > 1)")
+    if name == "c5greedy":
+        nodes, _ = synth.config5(20_000, 1)
+        _, pods = synth.config5(20_000, 2_000_000, seed=5 + seed_shift)
+        return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=True,
+                                 desc="c5 (greedy form): mixed strategies, 20000 heterogeneous nodes x 2000000 pods "
+                                      "per GPU, 30% infeasible, sequential commit (replicas at N > 1)")
     raise SystemExit(f"unknown workload {name}")
 
 
@@ -439,7 +445,7 @@ def run_extras(args, torch, placement, lib, dev):
     """Secondary single-GPU numbers for the other BASELINE configs (not the headline)."""
     import ctypes
     extras = {}
-    for name, steps in (("c4shard", 3), ("c5", 2), ("c3", 1)):
+    for name, steps in (("c4shard", 3), ("c4", 2), ("c5", 2), ("c3", 1), ("c5greedy", 1)):
         try:
             nodes, pods, meta = make_workload(name, 0)
             n, p = len(nodes), len(pods)
@@ -485,7 +491,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c4shard", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c4shard", "c5", "c5greedy"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--extra", action=argparse.BooleanOptionalAction, default=True)
