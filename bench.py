@@ -2,7 +2,7 @@
 """Benchmark of the fallback placement path (BASELINE.json metric: pod x node scores/sec
 and pods placed/sec), own arm and reference arm.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c4shard|c5]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c4shard|c5|c5greedy]
   python bench.py --impl reference ...        # the reference's CPU algorithm on host cores
   torchrun --nproc-per-node N bench.py --gpus N ...   # one rank per GPU, NCCL
 
