@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -97,9 +98,15 @@ struct kp_session {
     size_t ws_bytes = 0;
     int64_t resident_nodes = -1;        // >= 0: a node table is resident
     int64_t h2d = 0, d2h = 0;
+    // pinned staging for small node tables: the seven columns travel as ONE copy
+    unsigned char *h_stage = nullptr;
+    size_t stage_bytes = 0;
+    int direct = 3;                     // bit 0: pinned pod columns read in place, bit 1: pinned results written in place
 };
 
 namespace {
+
+constexpr size_t kStageMaxBytes = 1u << 20;   // node tables up to ~18 k rows travel as one copy
 
 struct DeviceGuard {
     int prev = -1;
@@ -112,9 +119,11 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// Columns are packed for the RESIDENT table size (not max_nodes) so that a small table is one
+// contiguous range: 6 x 8-byte columns, then the ready bytes.
 kp_node_table session_node_view(const kp_session *s, int64_t n)
 {
-    const size_t col = align_up(sizeof(int64_t) * (size_t)s->max_nodes);
+    const size_t col = align_up(sizeof(int64_t) * (size_t)(n > 0 ? n : 0));
     kp_node_table t{};
     t.n_nodes = n;
     t.alloc_cpu_milli = reinterpret_cast<const int64_t *>(s->d_nodes + 0 * col);
@@ -127,6 +136,18 @@ kp_node_table session_node_view(const kp_session *s, int64_t n)
     return t;
 }
 
+// Device-side alias of p when p lies in pinned host memory the GPU can address, else nullptr.
+void *device_alias(const void *p)
+{
+    cudaPointerAttributes a{};
+    if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return (reinterpret_cast<uintptr_t>(a.devicePointer) & 7u) ? nullptr : a.devicePointer;
+}
+
 int upload_nodes(kp_session *s, const kp_node_table *nodes)
 {
     const int64_t n = nodes->n_nodes;
@@ -136,7 +157,16 @@ int upload_nodes(kp_session *s, const kp_node_table *nodes)
     }
     const kp_node_table d = session_node_view(s, n);
     const size_t b8 = sizeof(int64_t) * (size_t)n;
-    if (n > 0) {
+    const size_t col = align_up(b8);
+    const size_t packed = 6 * col + (size_t)n;
+    if (n > 0 && s->h_stage && packed <= s->stage_bytes) {
+        // gather the columns on the host (tens of KB) and send one copy instead of seven
+        const void *src[6] = {nodes->alloc_cpu_milli, nodes->alloc_mem_bytes, nodes->pod_count,
+                              nodes->max_pods, nodes->cpu_usage_pct, nodes->mem_usage_pct};
+        for (int c = 0; c < 6; ++c) memcpy(s->h_stage + c * col, src[c], b8);
+        memcpy(s->h_stage + 6 * col, nodes->ready, (size_t)n);
+        KP_CUDA(cudaMemcpyAsync(s->d_nodes, s->h_stage, packed, cudaMemcpyHostToDevice, s->stream));
+    } else if (n > 0) {
         KP_CUDA(cudaMemcpyAsync((void *)d.alloc_cpu_milli, nodes->alloc_cpu_milli, b8, cudaMemcpyHostToDevice, s->stream));
         KP_CUDA(cudaMemcpyAsync((void *)d.alloc_mem_bytes, nodes->alloc_mem_bytes, b8, cudaMemcpyHostToDevice, s->stream));
         KP_CUDA(cudaMemcpyAsync((void *)d.pod_count, nodes->pod_count, b8, cudaMemcpyHostToDevice, s->stream));
@@ -337,6 +367,12 @@ int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_sessio
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_out, 2 * pcol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_state, 3 * ncol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc(&s->d_ws, s->ws_bytes + kAlign);
+    if (e == cudaSuccess) {
+        const size_t want = 6 * ncol + (size_t)max_nodes;
+        s->stage_bytes = want < kStageMaxBytes ? want : kStageMaxBytes;
+        if (s->stage_bytes) e = cudaHostAlloc((void **)&s->h_stage, s->stage_bytes, cudaHostAllocDefault);
+    }
+    if (const char *v = getenv("KP_SESSION_DIRECT")) s->direct = atoi(v) & 3;   // experiments only
     if (e != cudaSuccess) {
         kp_session_destroy(s);
         return cuda_fail(e, "kp_session_create allocation");
@@ -355,6 +391,7 @@ void kp_session_destroy(kp_session *s)
     cudaFree(s->d_out);
     cudaFree(s->d_state);
     cudaFree(s->d_ws);
+    if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -390,17 +427,40 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     const kp_node_table dn = session_node_view(s, s->resident_nodes);
     if ((st = check_tables(&dn, pods)) != KP_OK) return st;
     if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return KP_ERR_INVALID_ARG; }
-    kp_pod_table dp{};
-    if ((st = upload_pods(s, pods, &dp)) != KP_OK) return st;
     const size_t pcol = align_up(sizeof(int64_t) * (size_t)s->max_pods);
+    const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
     int64_t *d_idx = reinterpret_cast<int64_t *>(s->d_out);
     double *d_score = reinterpret_cast<double *>(s->d_out + pcol);
+    kp_pod_table dp{};
+    // Pinned (device-addressable) host buffers are used in place when the kernels touch every
+    // pod row once: the requests are read across the host link by the placement kernel itself
+    // and the results are written straight into the caller's arrays -- no staging copies, and
+    // the transfers overlap the scoring CTA by CTA.
+    bool in_place = false, out_in_place = false;
+    if (s->direct && b8 && snapshot_single_pass(s->resident_nodes, pods->strategy_ids != nullptr)) {
+        const void *rc = device_alias(pods->req_cpu_milli), *rm = device_alias(pods->req_mem_bytes);
+        if ((s->direct & 1) && rc && rm && pods->n_pods <= s->max_pods) {
+            dp.n_pods = pods->n_pods;
+            dp.req_cpu_milli = static_cast<const int64_t *>(rc);
+            dp.req_mem_bytes = static_cast<const int64_t *>(rm);
+            s->h2d += 2 * (int64_t)b8;
+            in_place = true;
+        }
+        void *oi = device_alias(out_node_idx), *os = device_alias(out_score);
+        if ((s->direct & 2) && oi && os) {
+            d_idx = static_cast<int64_t *>(oi);
+            d_score = static_cast<double *>(os);
+            out_in_place = true;
+        }
+    }
+    if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return st;
     st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream);
     if (st != KP_OK) return st;
-    const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
     if (b8) {
-        KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
-        KP_CUDA(cudaMemcpyAsync(out_score, d_score, b8, cudaMemcpyDeviceToHost, s->stream));
+        if (!out_in_place) {
+            KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
+            KP_CUDA(cudaMemcpyAsync(out_score, d_score, b8, cudaMemcpyDeviceToHost, s->stream));
+        }
         s->d2h += 2 * (int64_t)b8;
     }
     KP_CUDA(cudaStreamSynchronize(s->stream));

@@ -191,6 +191,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
                           int filter_mode, int64_t *out_idx, double *out_score, void *ws,
                           size_t ws_bytes, cudaStream_t stream);
 size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod);
+bool snapshot_single_pass(int64_t n_nodes, bool per_pod);
 int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                            int filter_mode, int64_t *out_idx, double *out_score, cudaStream_t stream);
 int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,

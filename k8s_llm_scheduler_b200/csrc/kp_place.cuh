@@ -131,7 +131,8 @@ place_kernel(const PlaceParams p)
     __shared__ uint64_t bars[2];
     __shared__ int comb[NSPLIT > 1 ? NSPLIT : 1][NSPLIT > 1 ? CHUNK : 1];
     __shared__ int s_last;
-    __shared__ double s_uniq[2][kUniqStage];
+    __shared__ __align__(16) double s_uniq[2][kUniqStage];
+    __shared__ uint64_t ubar;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int podw = warp / NSPLIT, split = warp % NSPLIT;
@@ -142,6 +143,7 @@ place_kernel(const PlaceParams p)
     if (tid == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
+        mbar_init(&ubar, 1);
         mbar_fence_init();
     }
     constexpr int ITEMS = NSPLIT > 1 ? (2 * CHUNK + THREADS - 1) / THREADS : 1;
@@ -187,24 +189,32 @@ place_kernel(const PlaceParams p)
     const unsigned char *table = swar ? reinterpret_cast<const unsigned char *>(p.packed + (size_t)s * p.npad)
                                       : reinterpret_cast<const unsigned char *>(p.ab + (size_t)s * p.npad);
 
-    // first tile on its way while the pods are ranked
+    // sorted thresholds (when both arrays fit shared memory) and the first tile on their way
+    // as bulk copies while the threads get to the ranking step
     auto tile_count = [&](int t) { return min(tile_nodes, nvalid4 - t * tile_nodes); };
+    const double *ua = p.uniq, *ub = p.uniq + p.npad;
+    const uint32_t ua_bytes = (uint32_t)((da + 1) & ~1) * 8u, ub_bytes = (uint32_t)((db + 1) & ~1) * 8u;
+    const bool stage_uniq = da <= kUniqStage && db <= kUniqStage && ua_bytes + ub_bytes > 0;
     __syncthreads();                                         // barrier objects initialised
-    if (tid == 0 && t_hi > t_lo) {
-        const int t = t_hi - 1;
-        const uint32_t bytes = (uint32_t)(tile_count(t) * elem);
-        mbar_expect_tx(&bars[0], bytes);
-        bulk_load(tiles[0], table + (size_t)t * tile_nodes * elem, bytes, &bars[0]);
+    if (tid == 0) {
+        if (stage_uniq) {
+            mbar_expect_tx(&ubar, ua_bytes + ub_bytes);
+            if (ua_bytes) bulk_load(s_uniq[0], ua, ua_bytes, &ubar);
+            if (ub_bytes) bulk_load(s_uniq[1], ub, ub_bytes, &ubar);
+        }
+        if (t_hi > t_lo) {
+            const int t = t_hi - 1;
+            const uint32_t bytes = (uint32_t)(tile_count(t) * elem);
+            mbar_expect_tx(&bars[0], bytes);
+            bulk_load(tiles[0], table + (size_t)t * tile_nodes * elem, bytes, &bars[0]);
+        }
     }
 
     // ---- pod prologue: requests -> threshold ranks (exact, see kp_plan.cuh) ----
-    const double *ua = p.uniq, *ub = p.uniq + p.npad;
-    if (da <= kUniqStage && db <= kUniqStage) {              // both sorted threshold arrays fit shared memory
-        for (int i = tid; i < da; i += THREADS) s_uniq[0][i] = ua[i];
-        for (int i = tid; i < db; i += THREADS) s_uniq[1][i] = ub[i];
+    if (stage_uniq) {
+        mbar_wait(&ubar, 0);
         ua = s_uniq[0];
         ub = s_uniq[1];
-        __syncthreads();
     }
     uint32_t ra[R], rb[R];
     bool live[R];

@@ -96,6 +96,14 @@ size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod)
     return make_layout(n_nodes, n_pods, per_pod).total;
 }
 
+// True when the snapshot reads every pod row exactly once and writes every result row exactly
+// once, in pod order (one node segment, no strategy grouping): the host session may then hand
+// the kernels pinned host memory directly instead of staging copies.
+bool snapshot_single_pass(int64_t n_nodes, bool per_pod)
+{
+    return n_nodes <= kSmallMaxNodes && !per_pod;
+}
+
 static NodePtrs node_ptrs(const kp_node_table &t)
 {
     return NodePtrs{(const long long *)t.alloc_cpu_milli, (const long long *)t.alloc_mem_bytes,

@@ -260,6 +260,40 @@ def test_session_host_api_matches_device_api():
             s.snapshot(nodes, PodTable.from_columns(np.zeros(40_000), np.zeros(40_000)), 0, 1)
 
 
+@pytest.mark.parametrize("n,p", [(1000, 30_000), (8192, 5_000), (9000, 5_000), (3, 1), (700, 257)])
+def test_session_pinned_buffers_are_used_in_place(n, p):
+    """Pinned host tables: small tables with one strategy are read / written by the kernels
+    directly (no staging copies); everything else takes the copy path.  Same answers either way."""
+    import torch
+    from k8s_llm_scheduler_b200.placement import Session
+    nodes, pods = synth.config5(n, p, seed=77)
+    uniform = PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes)
+    hn = {k: torch.as_tensor(getattr(nodes, k)).pin_memory() for k in nodes.columns()}
+    hp = (torch.as_tensor(pods.req_cpu_milli).pin_memory(), torch.as_tensor(pods.req_mem_bytes).pin_memory(), None)
+    hp_sid = hp[:2] + (torch.as_tensor(pods.strategy_ids).pin_memory(),)
+    out = (torch.full((p,), -7, dtype=torch.int64).pin_memory(), torch.full((p,), -7.0, dtype=torch.float64).pin_memory())
+    with Session(0, max_nodes=n, max_pods=p) as s:
+        for strat in (0, 1, 2):
+            for mode in (0, 1):
+                out[0].fill_(-7)
+                s.snapshot(hn, hp, strat, mode, out=out)
+                oi, os_ = oracle_snapshot(nodes, uniform, strat, mode)
+                assert_same_idx(out[0].numpy(), oi)
+                assert_same_f64(out[1].numpy(), os_)
+                assert s.last_copy_bytes() == (6 * 8 * n + n + 16 * p, 16 * p)
+        s.snapshot(hn, hp_sid, 0, 1, out=out)                       # per-pod ids: copy path
+        oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
+        assert_same_idx(out[0].numpy(), oi)
+        assert_same_f64(out[1].numpy(), os_)
+        # pinned inputs, pageable outputs and the other way round
+        gi, gs = s.snapshot(hn, hp, 0, 1)
+        oi, os_ = oracle_snapshot(nodes, uniform, 0, 1)
+        assert_same_idx(gi, oi)
+        s.snapshot(nodes, uniform, 0, 1, out=out)
+        assert_same_idx(out[0].numpy(), oi)
+        assert_same_f64(out[1].numpy(), os_)
+
+
 def test_workspace_errors_are_reported():
     import torch
     from k8s_llm_scheduler_b200 import PlacementError, placement
