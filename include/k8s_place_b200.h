@@ -164,10 +164,18 @@ int kp_node_scores(const kp_node_table *nodes, int strategy, int filter_mode,
                    uint8_t *out_eligible, void *stream);
 
 /* ---- session: host pointers, owns device memory ------------------------------------
- * The reference-facing form: `nodes`, `pods` and the outputs are HOST memory (pinned
- * host memory makes the copies asynchronous and faster, pageable memory works).  Each
- * call copies the tables in, runs the device path above on the session's stream, copies
- * the results out and waits for them.
+ * The reference-facing form: `nodes`, `pods` and the outputs are HOST memory.  Each
+ * call brings the tables to the GPU, runs the device path above on the session's stream,
+ * returns the results to the host arrays and waits for them.  Pageable memory works
+ * (staged copies).  PINNED host memory (cudaHostAlloc / cudaHostRegister, e.g. torch's
+ * pin_memory()) is faster: a node table of up to ~18 k rows travels as one packed copy,
+ * and in kp_session_snapshot with a single strategy and at most 8192 nodes the pod
+ * columns and the result arrays are not copied at all: the placement kernel reads the
+ * requests across the host link itself (paced so that the rows arrive in pod order and
+ * scoring overlaps the transfer) and writes idx/score straight into the caller's arrays.
+ * Either way the caller's arrays are complete when the call returns.
+ * kp_session_last_copy_bytes counts the bytes that crossed the host link in the last
+ * call, whichever way they travelled.
  */
 typedef struct kp_session kp_session;
 int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_session **out);

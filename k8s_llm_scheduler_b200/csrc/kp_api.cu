@@ -99,6 +99,7 @@ struct kp_session {
     int64_t resident_nodes = -1;        // >= 0: a node table is resident
     int64_t h2d = 0, d2h = 0;
     // pinned staging for small node tables: the seven columns travel as ONE copy
+    unsigned *d_flow = nullptr;         // flow-control words of the in-place snapshot (kept zero between calls)
     unsigned char *h_stage = nullptr;
     size_t stage_bytes = 0;
     int direct = 3;                     // bit 0: pinned pod columns read in place, bit 1: pinned results written in place
@@ -106,6 +107,7 @@ struct kp_session {
 
 namespace {
 
+constexpr unsigned kFlowWindowCtas = 64;      // request rows of this many CTAs in flight on the host link
 constexpr size_t kStageMaxBytes = 1u << 20;   // node tables up to ~18 k rows travel as one copy
 
 struct DeviceGuard {
@@ -367,6 +369,8 @@ int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_sessio
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_out, 2 * pcol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_state, 3 * ncol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc(&s->d_ws, s->ws_bytes + kAlign);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_flow, kAlign);
+    if (e == cudaSuccess) e = cudaMemset(s->d_flow, 0, kAlign);
     if (e == cudaSuccess) {
         const size_t want = 6 * ncol + (size_t)max_nodes;
         s->stage_bytes = want < kStageMaxBytes ? want : kStageMaxBytes;
@@ -391,6 +395,7 @@ void kp_session_destroy(kp_session *s)
     cudaFree(s->d_out);
     cudaFree(s->d_state);
     cudaFree(s->d_ws);
+    cudaFree(s->d_flow);
     if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
@@ -454,7 +459,12 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
         }
     }
     if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return st;
-    st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream);
+    PlaceTuning tuning;
+    if (in_place) {
+        tuning.flow = s->d_flow;
+        tuning.flow_window = kFlowWindowCtas;
+    }
+    st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream, tuning);
     if (st != KP_OK) return st;
     if (b8) {
         if (!out_in_place) {

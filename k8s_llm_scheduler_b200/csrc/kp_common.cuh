@@ -187,9 +187,15 @@ void count_launch(int n = 1);
     } while (0)
 
 // internal entry points (one per .cu file)
+// Launch options of the placement kernel that only the host-buffer session uses.
+struct PlaceTuning {
+    int resident_cap = 0;          // > 0: at most this many CTAs resident per SM
+    unsigned *flow = nullptr;      // two zeroed device words: pace the in-place reads of pinned pod rows
+    unsigned flow_window = 0;      // CTAs whose rows may be in flight at once
+};
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                           int filter_mode, int64_t *out_idx, double *out_score, void *ws,
-                          size_t ws_bytes, cudaStream_t stream);
+                          size_t ws_bytes, cudaStream_t stream, const PlaceTuning &tuning = PlaceTuning());
 size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod);
 bool snapshot_single_pass(int64_t n_nodes, bool per_pod);
 int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,

@@ -40,6 +40,7 @@ constexpr int kTileNodesWide = kTileBytes / 8;         // 512
 constexpr uint32_t kSwarGuards = 0x80008000u;
 constexpr uint32_t kSwarDeadPod = 0x7fff7fffu;         // larger than any node field: never fits
 constexpr uint32_t kNoPos = 0xffffffffu;
+constexpr long long kFlowNever = (long long)0x8000000000000001ull;   // sentinel for the arrival vote
 constexpr int kUniqStage = 1024;                       // sorted thresholds staged in shared memory up to this many
 
 struct PlaceParams {
@@ -62,6 +63,12 @@ struct PlaceParams {
     uint32_t *best_pos;                // [slots] merged best rank position (0xffffffff; grid.y > 1)
     long long *out_idx;
     double *out_score;
+    // Host-link flow control (pods read in place from pinned host memory, see kp_api.cu): CTA c
+    // asks for its rows only once the rows of CTA c - flow_window have arrived, so the requests
+    // reach the link in pod order and early CTAs score while later rows are still in flight.
+    // flow[0] = CTAs whose rows have arrived, flow[1] = CTAs finished (the last one resets both).
+    unsigned *flow;                    // NULL = off
+    unsigned flow_window;
 };
 
 // #{i : arr[i] < x} in an ascending array: branch-free, fixed depth (same trip count in every lane)
@@ -150,14 +157,33 @@ place_kernel(const PlaceParams p)
     double pre_req[ITEMS];
     const bool prefetched = NSPLIT > 1 && p.uniform_strategy >= 0;       // slot == pod: requests need no plan data
     if (prefetched) {
+        const bool paced = p.flow != nullptr;
+        if (paced) {
+            if (tid == 0) {
+                const unsigned need = blockIdx.x > p.flow_window ? blockIdx.x - p.flow_window : 0u;
+                // pacing is only a hint: give up after ~1 ms rather than depend on CTA dispatch order
+                for (int spin = 0; spin < 16384 && *reinterpret_cast<volatile unsigned *>(p.flow) < need; ++spin)
+                    __nanosleep(64);
+            }
+            __syncthreads();
+        }
+        bool arrived = true;
 #pragma unroll
         for (int e = 0; e < ITEMS; ++e) {
             const int item = tid + e * THREADS;
             const int q = item % CHUNK, dim = item / CHUNK;
             const long long pod = slot0 + q;
             pre_req[e] = 0.0;
-            if (item < 2 * CHUNK && pod < p.n_pods)
-                pre_req[e] = dim == 0 ? req_cores(p.req_cpu[pod]) : req_gib(p.req_mem[pod]);
+            if (item < 2 * CHUNK && pod < p.n_pods) {
+                const long long raw = dim == 0 ? p.req_cpu[pod] : p.req_mem[pod];
+                pre_req[e] = dim == 0 ? req_cores(raw) : req_gib(raw);
+                arrived = arrived && raw != kFlowNever;
+            }
+        }
+        if (paced) {
+            // the vote consumes every loaded value, so passing the barrier means the rows are here
+            if (!__syncthreads_and(arrived)) p.flow[2] = 1u;      // never true for int64 requests that mean anything
+            if (tid == 0) atomicAdd(p.flow, 1u);
         }
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");                   // the plan kernels have completed
@@ -389,6 +415,13 @@ place_kernel(const PlaceParams p)
         }
         p.out_idx[pod] = idx;
         p.out_score[pod] = sc;
+    }
+    if (p.flow && tid == 0) {                                // flow control off again for the next launch
+        __threadfence();
+        if (atomicAdd(p.flow + 1, 1u) == gridDim.x - 1) {
+            p.flow[0] = 0u;
+            p.flow[1] = 0u;
+        }
     }
 }
 

@@ -307,6 +307,7 @@ constexpr PlaceCfg kPlaceCfgs[] = {
     {256, 8, 8, 256},     // not in the size ladder: few pods, one wave of 8-warp CTAs with 8 pods per lane
 };
 constexpr int kNumPlaceCfgs = sizeof(kPlaceCfgs) / sizeof(kPlaceCfgs[0]);
+constexpr int kFirstSplitCfg = 3;        // configurations from here on split the nodes over the warps (NSPLIT > 1)
 constexpr int kFallbackCfg = 4;          // few pods: 128 pods per CTA, 8 warps splitting the nodes
 
 template <int THREADS, int R, int NSPLIT>
@@ -338,13 +339,37 @@ static int cfg_occupancy(int c)
 // Programmatic dependent launch: the kernel may start while its predecessor in the stream is
 // still draining; place_kernel does its plan-independent prologue first and then executes
 // griddepcontrol.wait before touching anything the plan wrote.
+// resident_cap > 0 limits the CTAs resident per SM (by reserving unused dynamic shared memory):
+// used when the pods arrive over the host link, where several short waves pipeline the
+// transfers with the scoring instead of every CTA waiting for its rows at the same time.
 template <int THREADS, int R, int NSPLIT>
-static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream_t stream)
+static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream_t stream, int resident_cap)
 {
+    static size_t static_smem = 0;
+    static size_t max_dyn_set = 0;
+    size_t dyn = 0;
+    if (resident_cap > 0) {
+        if (static_smem == 0) {
+            cudaFuncAttributes fa{};
+            cudaError_t e = cudaFuncGetAttributes(&fa, place_kernel<THREADS, R, NSPLIT>);
+            if (e != cudaSuccess) return e;
+            static_smem = fa.sharedSizeBytes ? fa.sharedSizeBytes : 1;
+        }
+        const size_t per_sm = 228u * 1024u, reserve = 1024u, max_cta = 227u * 1024u;
+        size_t want = per_sm / (size_t)resident_cap - reserve;         // static + dynamic per CTA
+        if (want > max_cta) want = max_cta;
+        if (want > static_smem) dyn = (want - static_smem) & ~(size_t)127;
+        if (dyn > max_dyn_set) {
+            cudaError_t e = cudaFuncSetAttribute(place_kernel<THREADS, R, NSPLIT>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (e != cudaSuccess) return e;
+            max_dyn_set = dyn;
+        }
+    }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(THREADS, 1, 1);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = dyn;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -354,17 +379,17 @@ static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream
     return cudaLaunchKernelEx(&cfg, place_kernel<THREADS, R, NSPLIT>, pp);
 }
 
-static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_t stream)
+static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_t stream, int resident_cap)
 {
     cudaError_t e;
     switch (c) {
-        case 0: e = launch_place_pdl<256, 8, 1>(pp, grid, stream); break;
-        case 1: e = launch_place_pdl<128, 8, 1>(pp, grid, stream); break;
-        case 2: e = launch_place_pdl<128, 4, 1>(pp, grid, stream); break;
-        case 3: e = launch_place_pdl<256, 4, 4>(pp, grid, stream); break;
-        case 4: e = launch_place_pdl<256, 4, 8>(pp, grid, stream); break;
-        case 5: e = launch_place_pdl<256, 2, 8>(pp, grid, stream); break;
-        default: e = launch_place_pdl<256, 8, 8>(pp, grid, stream); break;
+        case 0: e = launch_place_pdl<256, 8, 1>(pp, grid, stream, resident_cap); break;
+        case 1: e = launch_place_pdl<128, 8, 1>(pp, grid, stream, resident_cap); break;
+        case 2: e = launch_place_pdl<128, 4, 1>(pp, grid, stream, resident_cap); break;
+        case 3: e = launch_place_pdl<256, 4, 4>(pp, grid, stream, resident_cap); break;
+        case 4: e = launch_place_pdl<256, 4, 8>(pp, grid, stream, resident_cap); break;
+        case 5: e = launch_place_pdl<256, 2, 8>(pp, grid, stream, resident_cap); break;
+        default: e = launch_place_pdl<256, 8, 8>(pp, grid, stream, resident_cap); break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "place_kernel launch");
     count_launch();
@@ -373,10 +398,14 @@ static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_
 
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                           int filter_mode, int64_t *out_idx, double *out_score, void *ws,
-                          size_t ws_bytes, cudaStream_t stream)
+                          size_t ws_bytes, cudaStream_t stream, const PlaceTuning &tuning)
 {
     const int64_t n = nodes.n_nodes, P = pods.n_pods;
     if (P == 0) return KP_OK;
+    int resident_cap = tuning.resident_cap;
+    unsigned flow_window = tuning.flow_window;
+    if (const char *v = getenv("KP_PLACE_RESIDENT")) resident_cap = atoi(v);        // experiments only
+    if (const char *v = getenv("KP_FLOW_WINDOW")) flow_window = (unsigned)atoi(v);  // experiments only
     const bool per_pod = pods.strategy_ids != nullptr;
     const SnapLayout L = make_layout(n, P, per_pod);
     if (!ws || ws_bytes < L.total || (reinterpret_cast<uintptr_t>(ws) & (kAlign - 1))) {
@@ -530,8 +559,12 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.best_pos = best_pos;
     pp.out_idx = (long long *)out_idx;
     pp.out_score = out_score;
+    // pacing applies to the kernels that fetch a CTA's requests up front (node splits, one strategy)
+    const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && cfg >= kFirstSplitCfg;
+    pp.flow = paced ? tuning.flow : nullptr;
+    pp.flow_window = flow_window;
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e1, stream));
-    const int st = launch_place_cfg(cfg, pp, dim3((unsigned)n_chunks, (unsigned)nseg, 1), stream);
+    const int st = launch_place_cfg(cfg, pp, dim3((unsigned)n_chunks, (unsigned)nseg, 1), stream, resident_cap);
     if (st == KP_OK && pe.enabled) {
         KP_CUDA(cudaEventRecord(pe.e2, stream));
         pe.valid = true;

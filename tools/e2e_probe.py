@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--strategy", type=int, default=1)
     ap.add_argument("--iters", type=int, default=300)
     ap.add_argument("--direct", default="0,1,2,3", help="KP_SESSION_DIRECT masks to time")
+    ap.add_argument("--windows", default="", help="flow-control windows (CTAs in flight) to time, e.g. 0,32,96@5")
     ap.add_argument("--cfgs", default="", help="place configurations to force, e.g. 3,4,5")
     a = ap.parse_args()
     nodes, pods = synth.config2(a.nodes, a.pods)
@@ -62,14 +63,36 @@ def main():
         print(f"link only: one {name} copy of {16 * a.pods} B + sync : median {med:8.1f} us  min {mn:8.1f} us")
     ref = None
     ap_cfgs = [c for c in a.cfgs.split(",") if c]
-    for cfg in ap_cfgs:
+    for item in ap_cfgs:                       # "cfg" or "cfg:resident"
+        cfg, _, res = item.partition(":")
         os.environ["KP_SESSION_DIRECT"] = "3"
         os.environ["KP_FORCE_PLACE_CFG"] = cfg
+        if res:
+            os.environ["KP_PLACE_RESIDENT"] = res
         sess = placement.Session(0, max_nodes=a.nodes, max_pods=a.pods)
         med, mn = timeit(lambda: sess.snapshot(hn, hp, a.strategy, 1, out=ho), a.iters)
-        print(f"direct=3 cfg={cfg} python wrapper, nodes every call : median {med:8.1f} us  min {mn:8.1f} us")
+        print(f"direct=3 cfg={cfg} resident={res or '-'} python wrapper, nodes every call : median {med:8.1f} us  min {mn:8.1f} us")
         sess.close()
+        os.environ.pop("KP_PLACE_RESIDENT", None)
     os.environ.pop("KP_FORCE_PLACE_CFG", None)
+    for item in [w for w in a.windows.split(",") if w]:     # "window" or "window@cfg"
+        win, _, cfg = item.partition("@")
+        os.environ["KP_SESSION_DIRECT"] = "3"
+        os.environ["KP_FLOW_WINDOW"] = win
+        if cfg:
+            os.environ["KP_FORCE_PLACE_CFG"] = cfg
+        sess = placement.Session(0, max_nodes=a.nodes, max_pods=a.pods)
+        med, mn = timeit(lambda: sess.snapshot(hn, hp, a.strategy, 1, out=ho), a.iters)
+        print(f"direct=3 flow window={win} cfg={cfg or '-'} python wrapper, nodes every call : median {med:8.1f} us  min {mn:8.1f} us")
+        if ref is None:
+            os.environ["KP_SESSION_DIRECT"] = "0"
+            s0 = placement.Session(0, max_nodes=a.nodes, max_pods=a.pods)
+            ref = s0.snapshot(hn, hp, a.strategy, 1)[0].copy()
+            s0.close()
+        assert np.array_equal(ref, ho[0].numpy()), "paced variant disagrees"
+        sess.close()
+        os.environ.pop("KP_FORCE_PLACE_CFG", None)
+    os.environ.pop("KP_FLOW_WINDOW", None)
     for direct in a.direct.split(","):
         os.environ["KP_SESSION_DIRECT"] = direct
         sess = placement.Session(0, max_nodes=a.nodes, max_pods=a.pods)
