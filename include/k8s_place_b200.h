@@ -193,6 +193,62 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
 /* Bytes moved host->device and device->host by the last session call. */
 int kp_session_last_copy_bytes(const kp_session *s, int64_t *h2d, int64_t *d2h);
 
+/* ---- table ingest: Kubernetes quantity strings -> table columns, device pointers ------
+ * The step in front of the placement kernels.  String columns are
+ * Arrow-style: one byte buffer plus int64 offsets (row i is text[offsets[i] .. offsets[i+1])).
+ * The fp64 outputs are the reference's own values bit for bit; the int64 outputs are the wire
+ * values of kp_node_table / kp_pod_table that reproduce them.  Per-row status flags:
+ */
+#define KP_ROW_OK 0
+#define KP_ROW_CPU_INEXACT 1 /* the fp64 cpu value is right but no integer milli-core count equals it */
+#define KP_ROW_MEM_INEXACT 2 /* the fp64 memory value is right but no integer byte count equals it */
+#define KP_ROW_HOST 4        /* a string outside the device grammar ([+-]digits[.digits], < 2^53):
+                                the host must redo this row with float()/int() (it may raise, as the
+                                reference would); the row's outputs are not meaningful */
+
+/* Pod requests, CustomScheduler._convert_pod_to_spec (scheduler.py:731-764): fp64 sums over a
+ * pod's containers in container order; cpu "…m" -> /1000 else float(x or 0) (:742-745); memory
+ * only "…Ki" / "…Mi" / "…Gi", anything else contributes 0 (:747-753).  Containers without
+ * resources.requests are left out by the caller (:738); a missing key is the string "0" (:739-740).
+ */
+typedef struct {
+    int64_t n_pods;
+    const int64_t *container_begin; /* [n_pods + 1] rows of pod p: container_begin[p] .. container_begin[p+1]-1 */
+    const uint8_t *cpu_text;        /* requests['cpu'] of every container row */
+    const int64_t *cpu_offsets;     /* [n_containers + 1] */
+    const uint8_t *mem_text;        /* requests['memory'] */
+    const int64_t *mem_offsets;     /* [n_containers + 1] */
+} kp_pod_request_strings;
+
+/* out_cpu_request / out_memory_request: PodSpec.cpu_request / memory_request (cores, GiB);
+ * out_req_cpu_milli / out_req_mem_bytes: the kp_pod_table columns.  Any output but
+ * out_status may be NULL. */
+int kp_ingest_pod_requests(const kp_pod_request_strings *in, int64_t *out_req_cpu_milli,
+                           int64_t *out_req_mem_bytes, double *out_cpu_request,
+                           double *out_memory_request, uint8_t *out_status, void *stream);
+
+/* Node rows, ContextManager.get_node_metrics (scheduler.py:139-151) with _parse_cpu (:172-176)
+ * and _parse_memory (:178-187): allocatable cpu / memory / pods strings and the number of pods
+ * on the node -> the kp_node_table columns (ready comes from the node conditions and is not a
+ * quantity: the caller fills it).  cpu_usage_pct == mem_usage_pct == (pod_count/max_pods)*50,
+ * 0 when max_pods <= 0 (:150-151). */
+typedef struct {
+    int64_t n_nodes;
+    const uint8_t *cpu_text;   /* allocatable['cpu'] */
+    const int64_t *cpu_offsets;
+    const uint8_t *mem_text;   /* allocatable['memory'] */
+    const int64_t *mem_offsets;
+    const uint8_t *pods_text;  /* allocatable['pods'], int() */
+    const int64_t *pods_offsets;
+    const int64_t *pod_count;  /* len(pods on the node), scheduler.py:144-147 */
+} kp_node_strings;
+
+/* out_available_cpu / out_available_memory: NodeMetrics.available_cpu / available_memory. */
+int kp_ingest_nodes(const kp_node_strings *in, int64_t *out_alloc_cpu_milli,
+                    int64_t *out_alloc_mem_bytes, int64_t *out_max_pods, double *out_cpu_usage_pct,
+                    double *out_mem_usage_pct, double *out_available_cpu,
+                    double *out_available_memory, uint8_t *out_status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,20 @@ class KpPodTable(ctypes.Structure):
                 ("strategy_ids", c_void_p)]
 
 
+class KpPodRequestStrings(ctypes.Structure):
+    _fields_ = [("n_pods", c_int64), ("container_begin", c_void_p), ("cpu_text", c_void_p),
+                ("cpu_offsets", c_void_p), ("mem_text", c_void_p), ("mem_offsets", c_void_p)]
+
+
+class KpNodeStrings(ctypes.Structure):
+    _fields_ = [("n_nodes", c_int64), ("cpu_text", c_void_p), ("cpu_offsets", c_void_p),
+                ("mem_text", c_void_p), ("mem_offsets", c_void_p), ("pods_text", c_void_p),
+                ("pods_offsets", c_void_p), ("pod_count", c_void_p)]
+
+
+ROW_OK, ROW_CPU_INEXACT, ROW_MEM_INEXACT, ROW_HOST = 0, 1, 2, 4
+
+
 class PlacementError(RuntimeError):
     def __init__(self, status: int, where: str, detail: str):
         super().__init__(f"{where}: status {status} ({detail})")
@@ -60,6 +74,10 @@ SYMBOLS = {
     "kp_session_greedy": (c_int, [c_void_p, POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "kp_session_last_copy_bytes": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),
+    "kp_ingest_pod_requests": (c_int, [POINTER(KpPodRequestStrings), c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_void_p]),
+    "kp_ingest_nodes": (c_int, [POINTER(KpNodeStrings), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -345,6 +345,34 @@ int kp_node_scores(const kp_node_table *nodes, int strategy, int filter_mode, do
                               out_eligible, (cudaStream_t)stream);
 }
 
+int kp_ingest_pod_requests(const kp_pod_request_strings *in, int64_t *out_req_cpu_milli,
+                           int64_t *out_req_mem_bytes, double *out_cpu_request,
+                           double *out_memory_request, uint8_t *out_status, void *stream)
+{
+    if (!in || in->n_pods < 0) { set_error("pod request strings: NULL or negative size"); return KP_ERR_INVALID_ARG; }
+    if (in->n_pods > 0 && (!in->container_begin || !in->cpu_offsets || !in->mem_offsets || !out_status)) {
+        set_error("pod request strings: container_begin / offsets / out_status is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    return ingest_pods_device(*in, out_req_cpu_milli, out_req_mem_bytes, out_cpu_request,
+                              out_memory_request, out_status, (cudaStream_t)stream);
+}
+
+int kp_ingest_nodes(const kp_node_strings *in, int64_t *out_alloc_cpu_milli, int64_t *out_alloc_mem_bytes,
+                    int64_t *out_max_pods, double *out_cpu_usage_pct, double *out_mem_usage_pct,
+                    double *out_available_cpu, double *out_available_memory, uint8_t *out_status,
+                    void *stream)
+{
+    if (!in || in->n_nodes < 0) { set_error("node strings: NULL or negative size"); return KP_ERR_INVALID_ARG; }
+    if (in->n_nodes > 0 && (!in->cpu_offsets || !in->mem_offsets || !in->pods_offsets || !in->pod_count || !out_status)) {
+        set_error("node strings: offsets, pod_count or out_status is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    return ingest_nodes_device(*in, out_alloc_cpu_milli, out_alloc_mem_bytes, out_max_pods,
+                               out_cpu_usage_pct, out_mem_usage_pct, out_available_cpu,
+                               out_available_memory, out_status, (cudaStream_t)stream);
+}
+
 int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_session **out)
 {
     if (!out || max_nodes < 0 || max_pods < 0) { set_error("bad session arguments"); return KP_ERR_INVALID_ARG; }

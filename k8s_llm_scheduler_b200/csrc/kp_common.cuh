@@ -60,6 +60,11 @@ __device__ __forceinline__ double bytes_to_gib(long long bytes)
 {
     return __dmul_rn((double)bytes, 9.31322574615478515625e-10);   // 2^-30
 }
+// float(text) / 1024 / 1024 / 1024 for a byte count that is already a double (scheduler.py:187)
+__device__ __forceinline__ double bytes_to_gib_f64(double bytes)
+{
+    return __dmul_rn(bytes, 9.31322574615478515625e-10);           // 2^-30, exact scaling
+}
 __device__ __forceinline__ double free_mem_gib(long long alloc_bytes, double mu)
 {
     const double avail = bytes_to_gib(alloc_bytes);
@@ -213,6 +218,12 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
 int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode,
                        double *out_score, double *out_free_cpu, double *out_free_mem,
                        uint8_t *out_eligible, cudaStream_t stream);
+// kp_ingest.cu: quantity strings -> table columns
+int ingest_pods_device(const kp_pod_request_strings &in, int64_t *out_milli, int64_t *out_bytes,
+                       double *out_cpu, double *out_mem, uint8_t *out_status, cudaStream_t stream);
+int ingest_nodes_device(const kp_node_strings &in, int64_t *out_milli, int64_t *out_bytes,
+                        int64_t *out_max_pods, double *out_cu, double *out_mu, double *out_avail_cpu,
+                        double *out_avail_mem, uint8_t *out_status, cudaStream_t stream);
 int sm_count_cached();
 // kp_sort.cu: library radix sort / scan for the large-table plan (temp storage from the workspace)
 size_t sort_temp_bytes(int64_t n);

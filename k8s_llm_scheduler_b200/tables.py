@@ -106,7 +106,16 @@ def is_ready(conditions: Sequence[Dict[str, str]]) -> bool:
     return any(c.get("type") == "Ready" and c.get("status") == "True" for c in conditions)
 
 
+WIRE_LIMIT = 2 ** 53          # |milli-cores|, |bytes| below this are exact in fp64 (kernel contract)
+
+
+def _in_wire_range(x: float, what: str) -> None:
+    if not abs(x) < WIRE_LIMIT:          # also catches nan / inf
+        raise ValueError(f"{what} is outside the wire format's range (|value| < 2^53)")
+
+
 def cores_to_milli(cores: float, exact: bool = True) -> int:
+    _in_wire_range(cores * 1000, f"{cores!r} cores")
     m = int(round(cores * 1000))
     if exact and m / 1000.0 != cores:
         raise ValueError(f"{cores!r} cores is not an integer number of milli-cores in fp64")
@@ -114,6 +123,7 @@ def cores_to_milli(cores: float, exact: bool = True) -> int:
 
 
 def gib_to_bytes(gib: float, exact: bool = True) -> int:
+    _in_wire_range(gib * 2 ** 30, f"{gib!r} GiB")
     b = int(round(gib * 2 ** 30))
     if exact and b / 1024 / 1024 / 1024 != gib:
         raise ValueError(f"{gib!r} GiB is not an integer number of bytes in fp64")

@@ -22,6 +22,9 @@ and records, as JSON, what the reference computes for the fallback placement pat
                        fake CoreV1Api, real ``_fallback_decision``, fake bind.
   parsers.json         ``_parse_cpu`` / ``_parse_memory`` (scheduler.py:172-187) and
                        ``_convert_pod_to_spec`` (scheduler.py:731-764) outputs.
+  ingest.json          a few hundred pods / node rows with randomly spelled quantity strings
+                       (incl. spellings float() accepts or rejects in surprising ways) through
+                       ``_convert_pod_to_spec`` and ``get_node_metrics`` (scheduler.py:121-170).
   config1_trace.json   BASELINE config 1: 3-node cluster x ai-test-pods.yaml through
                        ``CustomScheduler._schedule_pod`` with the LLM call failing.
 
@@ -391,6 +394,87 @@ def gen_parsers(sched):
     return out
 
 
+# --------------------------------------------------------------------------------------
+# ingest vectors: quantity strings through the reference's own parsers, in bulk, including
+# every spelling class the device grammar accepts, defers to the host, or must reject
+# --------------------------------------------------------------------------------------
+ODD_NUMBERS = ["", "+5", "-5", "-0", "1e3", "1E-2", " 5", "5 ", "1_0", "\u0663", "inf", "nan", "Infinity",
+               "0.1234567890123456789", "12345678901234567890", "9007199254740993", ".5", "5.", ".",
+               "1.5.2", "0x10", "--1", "1,5", "00012", "0.000", "3.14159", "007.500", "1e", "e5"]
+
+
+def _rand_number(rng):
+    k = int(rng.integers(0, 10))
+    if k == 0 and rng.random() < 0.4:
+        return ODD_NUMBERS[int(rng.integers(0, len(ODD_NUMBERS)))]
+    if k <= 4:
+        return str(int(rng.integers(0, 200000)))
+    if k <= 6:
+        return f"{int(rng.integers(0, 64))}.{int(rng.integers(0, 1000)):0{int(rng.integers(1, 4))}d}"
+    if k == 7:
+        return f"{rng.random() * 100:.{int(rng.integers(4, 12))}f}"
+    if k == 8:
+        return str(int(rng.integers(0, 2 ** 40)))
+    return f"0.{int(rng.integers(0, 10))}"
+
+
+def gen_ingest(sched):
+    rng = np.random.Generator(np.random.PCG64(29))
+    cs = sched.CustomScheduler.__new__(sched.CustomScheduler)
+    def sfx(good, bad):
+        return bad[int(rng.integers(0, len(bad)))] if rng.random() < 0.05 else good[int(rng.integers(0, len(good)))]
+
+    cpu_good, cpu_bad = ["m", "m", "m", "", ""], ["M", "mm", " m"]
+    mem_good, mem_bad = ["Ki", "Mi", "Gi", "Mi", "Gi", "", ""], ["G", "K", "Ti", "ki", "i", "Gi "]
+    pods = []
+    for i in range(420):
+        containers = []
+        for _ in range(int(rng.integers(0, 5)) if i % 7 else 1):
+            r = rng.random()
+            if r < 0.06:
+                containers.append(None)                      # container without resources.requests
+                continue
+            req = {}
+            if rng.random() > 0.05:
+                req["cpu"] = _rand_number(rng) + sfx(cpu_good, cpu_bad)
+            if rng.random() > 0.05:
+                req["memory"] = _rand_number(rng) + sfx(mem_good, mem_bad)
+            if rng.random() < 0.02:
+                req["cpu"] = int(rng.integers(0, 8))         # YAML integer instead of a string
+            containers.append(req)
+        cl = [_NS(resources=_NS(requests=req) if req is not None else None) for req in containers]
+        pod = _NS(metadata=_NS(name=f"p{i}", namespace="default"),
+                  spec=_NS(containers=cl, node_selector=None, tolerations=None, priority=None))
+        rec = {"containers": containers}
+        try:
+            ps = cs._convert_pod_to_spec(pod)
+            rec.update(cpu_bits=f64_bits(ps.cpu_request), mem_bits=f64_bits(ps.memory_request), error=None)
+        except Exception as e:  # noqa: BLE001
+            rec.update(cpu_bits=None, mem_bits=None, error=type(e).__name__)
+        pods.append(rec)
+
+    nodes = []
+    for i in range(260):
+        cpu = _rand_number(rng) + sfx(cpu_good, cpu_bad)
+        mem = _rand_number(rng) + sfx(mem_good, mem_bad)
+        pods_s = str(int(rng.integers(0, 300))) if rng.random() > 0.08 else ODD_NUMBERS[int(rng.integers(0, len(ODD_NUMBERS)))]
+        spec = dict(name=f"n{i}", cpu=cpu, memory=mem, pods=pods_s, n_running=int(rng.integers(0, 260)))
+        cm = sched.ContextManager.__new__(sched.ContextManager)
+        cm.v1 = FakeCoreV1([dict(spec)])
+        table = cm.get_node_metrics()                        # [] on any exception (scheduler.py:168-170)
+        rec = dict(spec)
+        if table:
+            t = table[0]
+            rec.update(ok=True, available_cpu_bits=f64_bits(t.available_cpu),
+                       available_memory_bits=f64_bits(t.available_memory), max_pods=t.max_pods,
+                       pod_count=t.pod_count, cu_bits=f64_bits(t.cpu_usage_percent),
+                       mu_bits=f64_bits(t.memory_usage_percent))
+        else:
+            rec.update(ok=False)
+        nodes.append(rec)
+    return {"pods": pods, "nodes": nodes}
+
+
 def gen_config1_trace(sched):
     """BASELINE config 1 through the reference's own _schedule_pod."""
     import yaml
@@ -450,6 +534,7 @@ def main():
         "greedy.json": gen_greedy(sched, tap),
         "parsers.json": gen_parsers(sched),
         "config1_trace.json": gen_config1_trace(sched),
+        "ingest.json": gen_ingest(sched),
     }
     for name, obj in outputs.items():
         (OUT_DIR / name).write_text(json.dumps(obj, indent=1, sort_keys=True) + "\n")

@@ -1,0 +1,79 @@
+"""CPU tests of the ingest host logic: string packing, CSR flattening, and the literal mirrors of
+the reference's parsers (tables.py, oracle/py_oracle.py) against tests/golden/ingest.json, which
+the unmodified reference produced (tests/golden/make_golden.py: _convert_pod_to_spec
+scheduler.py:731-764, get_node_metrics :121-170)."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from k8s_llm_scheduler_b200 import tables
+from oracle import py_oracle
+from tests.helpers import bits
+
+GOLD = json.loads((Path(__file__).parent / "golden" / "ingest.json").read_text())
+
+
+def _pack():
+    # the packer needs torch only for the device hand-over; import lazily so that a missing
+    # CUDA library cannot break the pure-host checks
+    from k8s_llm_scheduler_b200.ingest import flatten_pod_requests, pack_strings
+    return flatten_pod_requests, pack_strings
+
+
+def test_pack_strings_round_trip():
+    _, pack_strings = _pack()
+    strs = ["250m", "", "1.5Gi", "٣", "x" * 70, "0"]
+    data, off = pack_strings(strs)
+    assert off.dtype == np.int64 and off[0] == 0 and len(off) == len(strs) + 1
+    got = [bytes(data[off[i]:off[i + 1]]).decode("utf-8") for i in range(len(strs))]
+    assert got == strs
+    data, off = pack_strings([])
+    assert data.size == 0 and off.tolist() == [0]
+    data, off = pack_strings(["", ""])
+    assert data.size == 0 and off.tolist() == [0, 0, 0]
+
+
+def test_flatten_follows_the_reference_loop():
+    flatten, _ = _pack()
+    pods = [[{"cpu": "250m", "memory": "256Mi"}], [], [None, {}, {"cpu": "1"}], [{"memory": "1Gi"}, {"cpu": 2}]]
+    begin, cpu, mem, odd = flatten(pods)
+    assert begin.tolist() == [0, 1, 1, 2, 4]
+    assert cpu == ["250m", "1", "0", "0"] and mem == ["256Mi", "0", "1Gi", "0"]
+    assert odd == [3]
+
+
+@pytest.mark.parametrize("mirror", [tables.pod_requests, py_oracle.pod_requests])
+def test_pod_mirrors_match_the_reference(mirror):
+    assert len(GOLD["pods"]) >= 400
+    for rec in GOLD["pods"]:
+        if rec["error"]:
+            with pytest.raises(ValueError):
+                mirror(rec["containers"])
+        else:
+            c, m = mirror(rec["containers"])
+            assert (bits(c), bits(m)) == (rec["cpu_bits"], rec["mem_bits"]), rec["containers"]
+
+
+def test_node_mirrors_match_the_reference():
+    seen_ok = 0
+    for rec in GOLD["nodes"]:
+        def row():
+            mp = int(rec["pods"])
+            return (tables.parse_cpu(rec["cpu"]), tables.parse_memory(rec["memory"]), mp,
+                    tables.usage_percent(rec["n_running"], mp))
+        if not rec["ok"]:
+            with pytest.raises(ValueError):
+                row()
+            continue
+        seen_ok += 1
+        cpu, mem, mp, u = row()
+        assert bits(cpu) == rec["available_cpu_bits"] and bits(mem) == rec["available_memory_bits"]
+        assert mp == rec["max_pods"] and rec["pod_count"] == rec["n_running"]
+        assert bits(u) == rec["cu_bits"] == rec["mu_bits"]
+        o = py_oracle.node_row(rec["name"], rec["cpu"], rec["memory"], rec["pods"], rec["n_running"])
+        assert bits(o.available_cpu) == rec["available_cpu_bits"]
+        assert bits(o.available_memory) == rec["available_memory_bits"]
+        assert bits(o.cpu_usage_percent) == rec["cu_bits"]
+    assert seen_ok >= 150
