@@ -151,11 +151,11 @@ ingest_pods_kernel(long long n_pods, const long long *container_begin, StrCol cp
         for (long long c = c0; c < c1; ++c) {
             double v;
             const long long a0 = cpu.off[c], a1 = cpu.off[c + 1];
-            if (a1 - a0 > 64 || !cpu_value(cpu.text + a0, (int)(a1 - a0), true, &v)) status |= KP_ROW_HOST;
+            if (a1 < a0 || a1 - a0 > 64 || !cpu_value(cpu.text + a0, (int)(a1 - a0), true, &v)) status |= KP_ROW_HOST;
             else cpu_sum = __dadd_rn(cpu_sum, v);
             const long long b0 = mem.off[c], b1 = mem.off[c + 1];
             bool counted;
-            if (b1 - b0 > 64 || !mem_value(mem.text + b0, (int)(b1 - b0), true, &v, &counted)) status |= KP_ROW_HOST;
+            if (b1 < b0 || b1 - b0 > 64 || !mem_value(mem.text + b0, (int)(b1 - b0), true, &v, &counted)) status |= KP_ROW_HOST;
             else if (counted) mem_sum = __dadd_rn(mem_sum, v);
         }
         long long milli = 0, bytes = 0;
@@ -203,11 +203,11 @@ ingest_nodes_kernel(long long n_nodes, StrCol cpu, StrCol mem, StrCol pods, cons
         long long mp = 0, milli = 0, bytes = 0;
         bool counted;
         const long long a0 = cpu.off[i], a1 = cpu.off[i + 1];
-        if (a1 - a0 > 64 || !cpu_value(cpu.text + a0, (int)(a1 - a0), false, &cores)) status |= KP_ROW_HOST;
+        if (a1 < a0 || a1 - a0 > 64 || !cpu_value(cpu.text + a0, (int)(a1 - a0), false, &cores)) status |= KP_ROW_HOST;
         const long long b0 = mem.off[i], b1 = mem.off[i + 1];
-        if (b1 - b0 > 64 || !mem_value(mem.text + b0, (int)(b1 - b0), false, &gib, &counted)) status |= KP_ROW_HOST;
+        if (b1 < b0 || b1 - b0 > 64 || !mem_value(mem.text + b0, (int)(b1 - b0), false, &gib, &counted)) status |= KP_ROW_HOST;
         const long long p0 = pods.off[i], p1 = pods.off[i + 1];
-        if (p1 - p0 > 32 || !parse_int(pods.text + p0, (int)(p1 - p0), &mp)) status |= KP_ROW_HOST;
+        if (p1 < p0 || p1 - p0 > 32 || !parse_int(pods.text + p0, (int)(p1 - p0), &mp)) status |= KP_ROW_HOST;
         if (!(status & KP_ROW_HOST)) {
             if (!milli_of(cores, &milli)) status |= KP_ROW_CPU_INEXACT;
             if (!bytes_of(gib, &bytes)) status |= KP_ROW_MEM_INEXACT;

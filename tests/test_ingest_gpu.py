@@ -162,6 +162,47 @@ def test_ingest_feeds_the_placement_kernels():
         assert_same_f64(gs, os_)
 
 
+def test_ragged_batches_and_unaligned_text():
+    """Pods with very many containers, long (zero-padded) spellings and text buffers that start at
+    an odd address: same answers as the host mirror."""
+    import ctypes
+    import torch
+    from k8s_llm_scheduler_b200 import _lib
+    from k8s_llm_scheduler_b200.ingest import flatten_pod_requests, ingest_pod_requests, pack_strings
+    rng = np.random.Generator(np.random.PCG64(3))
+    pods = []
+    for j in range(3000):
+        k = 1500 if j in (7, 1300) else int(rng.integers(0, 4))
+        pad = "0" * int(rng.integers(0, 50)) if 600 <= j < 1200 else ""
+        pods.append([{"cpu": f"{pad}{int(rng.integers(0, 4000))}m", "memory": f"{pad}{int(rng.integers(0, 4096))}Mi"}
+                     for _ in range(k)])
+    raw = ingest_pod_requests(pods, redo=False)
+    assert not (raw.status & HOST).any()
+    want = np.array([tables.pod_requests(p) for p in pods])
+    assert_same_f64(raw.cpu_request, want[:, 0], "cpu_request")
+    assert_same_f64(raw.memory_request, want[:, 1], "memory_request")
+    # the same batch with both text buffers shifted by one byte
+    lib = _lib.load()
+    begin, cpu, mem, _ = flatten_pod_requests(pods)
+    cols = [pack_strings(cpu), pack_strings(mem)]
+    dev = []
+    for text, off in cols:
+        shifted = torch.zeros(text.size + 17, dtype=torch.uint8, device="cuda")
+        shifted[1:1 + text.size] = torch.from_numpy(text).cuda()
+        dev += [shifted, torch.from_numpy(off).cuda()]
+    dbegin = torch.from_numpy(begin).cuda()
+    n = len(pods)
+    o_cpu, o_mem = (torch.empty(n, dtype=torch.float64, device="cuda") for _ in range(2))
+    o_st = torch.empty(n, dtype=torch.uint8, device="cuda")
+    st = _lib.KpPodRequestStrings(n, dbegin.data_ptr(), dev[0].data_ptr() + 1, dev[1].data_ptr(),
+                                  dev[2].data_ptr() + 1, dev[3].data_ptr())
+    rc = lib.kp_ingest_pod_requests(ctypes.byref(st), None, None, o_cpu.data_ptr(), o_mem.data_ptr(), o_st.data_ptr(), None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert_same_f64(o_cpu.cpu().numpy(), want[:, 0], "cpu_request (unaligned text)")
+    assert_same_f64(o_mem.cpu().numpy(), want[:, 1], "memory_request (unaligned text)")
+
+
 def test_empty_and_degenerate_batches():
     from k8s_llm_scheduler_b200.ingest import ingest_nodes, ingest_pod_requests
     out = ingest_pod_requests([])
