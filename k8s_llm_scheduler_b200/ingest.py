@@ -19,7 +19,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import ROW_HOST, KpNodeStrings, KpPodRequestStrings, check
+from ._lib import ROW_CPU_INEXACT, ROW_HOST, ROW_MEM_INEXACT, KpNodeStrings, KpPodRequestStrings, check
 from .tables import (WIRE_LIMIT, NodeTable, PodTable, cores_to_milli, gib_to_bytes, is_ready, parse_cpu,
                      parse_memory, pod_requests, usage_percent)
 
@@ -89,6 +89,24 @@ def flatten_pod_requests(pods: Sequence[Sequence[Optional[Dict[str, Any]]]]):
     return begin, cpu, mem, odd
 
 
+def _round_inexact(status, flag, values, scale, wire, scalar_fn, exact) -> None:
+    """Rows the device parsed (fp64 value right) but flagged as having no exact wire value:
+    ``exact`` -> the scalar converter raises for the first one, as ``tables`` does; otherwise
+    round half-to-even like ``int(round(x))`` there, vectorised."""
+    rows = np.nonzero(((status & flag) != 0) & ((status & ROW_HOST) == 0))[0]
+    if rows.size == 0:
+        return
+    if exact:                           # raises at the first truly inexact row (a -0.0 sum passes as 0)
+        for j in rows.tolist():
+            wire[j] = scalar_fn(float(values[j]), True)
+        return
+    scaled = values[rows] * scale
+    off_range = ~(np.abs(scaled) < WIRE_LIMIT)
+    if off_range.any():
+        scalar_fn(float(values[rows[np.argmax(off_range)]]), False)      # raises ValueError
+    wire[rows] = np.rint(scaled).astype(np.int64)
+
+
 def ingest_pod_requests(pods: Sequence[Sequence[Optional[Dict[str, Any]]]], device="cuda:0",
                         exact: bool = True, strategy_ids=None, redo: bool = True) -> PodIngest:
     """GPU form of ``PodTable.from_container_requests`` (same inputs, same table, same errors).
@@ -117,11 +135,15 @@ def ingest_pod_requests(pods: Sequence[Sequence[Optional[Dict[str, Any]]]], devi
     if odd:
         status = status.copy()
         status[np.asarray(odd, dtype=np.int64)] |= ROW_HOST
-    redo = set(np.nonzero(status)[0].tolist()) if redo else set()
-    for j in sorted(redo):                   # literal mirror: real float(), the reference's exceptions
+    host = np.nonzero(status & ROW_HOST)[0] if redo else np.empty(0, np.int64)
+    for j in host.tolist():                  # literal mirror: real float(), the reference's exceptions
         c, m = pod_requests(pods[j])
         cpu_req[j], mem_req[j] = c, m
         milli[j], nbytes[j] = cores_to_milli(c, exact), gib_to_bytes(m, exact)
+    if redo:                                 # values parsed on the device that have no exact wire form
+        _round_inexact(status, ROW_CPU_INEXACT, cpu_req, 1000.0, milli, cores_to_milli, exact)
+        _round_inexact(status, ROW_MEM_INEXACT, mem_req, float(2 ** 30), nbytes, gib_to_bytes, exact)
+    redo = host
     sid = None if strategy_ids is None else np.ascontiguousarray(strategy_ids, dtype=np.int64)
     table = PodTable(milli, nbytes, sid, [f"pod-{j}" for j in range(n)])
     return PodIngest(table, cpu_req, mem_req, status, len(redo))
