@@ -57,7 +57,9 @@ class BatchScheduler:
             greedy_fn = self._gpu_greedy
         if pod_table_fn is None:
             from .ingest import ingest_pod_requests
-            pod_table_fn = lambda reqs: ingest_pod_requests(reqs, device=f"cuda:{device}").table  # noqa: E731
+            # multi-container fp64 sums such as 0.1 + 0.2 cores are rounded to the nearest milli-core /
+            # byte for the capacity filter (which is an extension; the Ready filter ignores requests)
+            pod_table_fn = lambda reqs: ingest_pod_requests(reqs, device=f"cuda:{device}", exact=False).table  # noqa: E731
         self._greedy = greedy_fn
         self._pod_table = pod_table_fn
 
