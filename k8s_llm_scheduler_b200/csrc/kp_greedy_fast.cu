@@ -272,7 +272,7 @@ struct FastRun {
     int total, idx_bits, nodes_per_cta;
 };
 
-// dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | pc[nodes_per_cta] | shape[nodes_per_cta]
+// dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | c_t[nodes_per_cta]
 // THREADS x NPT nodes per CTA.  Few fat warps beat many thin ones here: the per-pod cost that does
 // not scale with the table (reductions, barrier, winner decode) is paid per warp.
 template <int THREADS, int NPT, bool MULTI, bool CLUSTER>
@@ -280,8 +280,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 fast_greedy_kernel(FastIn in, FastRun r)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ uint32_t s_x[kFastPodBatch];
-    __shared__ uint8_t s_sid[kFastPodBatch];
+    __shared__ uint32_t s_x[kFastPodBatch + 1];
+    __shared__ uint8_t s_sid[kFastPodBatch + 4];
     __shared__ uint32_t w_res[2][32];
     __shared__ uint32_t c_res[2][8];
     __shared__ uint32_t s_tbase[kFastMaxShapes + 1];
@@ -297,8 +297,8 @@ fast_greedy_kernel(FastIn in, FastRun r)
     const int total = r.total;
     uint32_t *traj_w = reinterpret_cast<uint32_t *>(fsm);
     uint32_t *traj_key = traj_w + kFastMaxTraj;
-    uint32_t *c_pc = traj_key + KS * kFastMaxTraj;
-    uint32_t *c_shape = c_pc + r.nodes_per_cta;                        // bit 31: the node has been committed to
+    uint32_t *c_t = traj_key + KS * kFastMaxTraj;                      // per node: trajectory index of its state;
+                                                                       // bit 31: the node has been committed to
     const int us = in.uniform_strategy;
     const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
     const int cta_base = crank * r.nodes_per_cta;
@@ -324,8 +324,10 @@ fast_greedy_kernel(FastIn in, FastRun r)
                 const uint32_t kr = r.entry_key[(size_t)(MULTI ? q : us) * total + n];
                 key[q][k] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
             }
-            c_pc[local] = (uint32_t)in.pod_count0[n];
-            c_shape[local] = r.shape_id[n] & 0x7fffffffu;
+            // trajectory index of the state with this node's pod count (its NEXT state is one further);
+            // nodes that can never be chosen have no shape and are never committed to
+            const uint32_t sh = r.shape_id[n];
+            c_t[local] = sh == kNoEntry ? 0u : (r.hdr->traj_base[sh & 0x7fu] + (uint32_t)in.pod_count0[n]) & 0x7fffffffu;
         }
     }
     __syncthreads();
@@ -338,19 +340,23 @@ fast_greedy_kernel(FastIn in, FastRun r)
             s_sid[i] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + i]) : us);
         }
         __syncthreads();
+        uint32_t x = s_x[0];
+        int s = s_sid[0];
         for (int j = 0; j < cnt; ++j) {
-            const uint32_t x = s_x[j];
-            const int s = s_sid[j];
             uint32_t best = 0u;
+            // both guard bits of w - x survive iff the pod fits the node in both dimensions
+            auto scan = [&](const uint32_t (&kq)[NPT]) {
 #pragma unroll
-            for (int k = 0; k < NPT; ++k) {
-                const uint32_t t = w[k] - x;                           // both guard bits survive iff the pod fits
-                uint32_t kk;
-                if (MULTI) kk = s == 0 ? key[0][k] : (s == 1 ? key[KS > 1 ? 1 : 0][k] : key[KS > 2 ? 2 : 0][k]);
-                else kk = key[0][k];
-                const uint32_t cand = ((~t) & kFastGuards) ? 0u : kk;
-                best = max(best, cand);
-            }
+                for (int k = 0; k < NPT; ++k) {
+                    const uint32_t t = w[k] - x;
+                    if (((~t) & kFastGuards) == 0u) best = max(best, kq[k]);
+                }
+            };
+            if (!MULTI || s == 0) scan(key[0]);                        // block-uniform branch per pod
+            else if (s == 1) scan(key[KS > 1 ? 1 : 0]);
+            else scan(key[KS > 2 ? 2 : 0]);
+            const uint32_t x_next = s_x[j + 1];                        // next pod's request, off the critical path
+            const int s_next = s_sid[j + 1];                           // (one spare element past the batch)
             const int par = j & 1;
             best = __reduce_max_sync(0xffffffffu, best);
             if (lane == 0) w_res[par][warp] = best;
@@ -363,6 +369,8 @@ fast_greedy_kernel(FastIn in, FastRun r)
                 for (int c = 0; c < csize; ++c) g = max(g, c_res[par][c]);
                 best = g;
             }
+            x = x_next;
+            s = s_next;
             if (best == 0u) {
                 if (crank == 0 && tid == 0) { r.out_idx[base + j] = -1; r.out_entry[base + j] = kNoEntry; }
                 continue;
@@ -371,15 +379,12 @@ fast_greedy_kernel(FastIn in, FastRun r)
             const int local = n - cta_base;
             if (local >= 0 && local < r.nodes_per_cta && (local % kFastThreads) == tid) {
                 // commit (scheduler.py:598 -> :144-151): one more pod, next state of the shape's trajectory
-                const uint32_t sh = c_shape[local];
-                const uint32_t pc = c_pc[local];
-                const uint32_t tbase = s_tbase[sh & 0x7fu];
-                r.out_idx[base + j] = n;
-                r.out_entry[base + j] = (sh >> 31) ? (uint32_t)in.n + tbase + pc : (uint32_t)n;
-                const uint32_t t2 = tbase + pc + 1u;
-                c_pc[local] = pc + 1u;
-                c_shape[local] = sh | 0x80000000u;
+                const uint32_t ct = c_t[local];
+                const uint32_t t2 = (ct & 0x7fffffffu) + 1u;
+                c_t[local] = t2 | 0x80000000u;
                 const uint32_t nw = traj_w[t2];
+                r.out_idx[base + j] = n;
+                r.out_entry[base + j] = (ct >> 31) ? (uint32_t)in.n + (ct & 0x7fffffffu) : (uint32_t)n;
                 uint32_t nk[KS];
 #pragma unroll
                 for (int q = 0; q < KS; ++q) {
@@ -403,8 +408,10 @@ fast_greedy_kernel(FastIn in, FastRun r)
     for (int local = tid; local < r.nodes_per_cta; local += kFastThreads) {
         const int n = cta_base + local;
         if (n >= in.n) break;
-        const bool touched = (c_shape[local] >> 31) != 0;
-        const long long pc = touched ? (long long)c_pc[local] : in.pod_count0[n];
+        const uint32_t ct = c_t[local];
+        const bool touched = (ct >> 31) != 0;
+        long long pc = in.pod_count0[n];
+        if (touched) pc = (long long)((ct & 0x7fffffffu) - s_tbase[r.shape_id[n] & 0x7fu]);
         const double u = usage_a3(pc, in.max_pods[n]);
         if (r.out_pc) r.out_pc[n] = pc;
         if (r.out_cu) r.out_cu[n] = touched ? u : in.cu0[n];
@@ -469,7 +476,7 @@ struct FastShape { int threads, npt, cluster; };
 
 static size_t fast_smem_bytes(bool multi, int nodes_per_cta)
 {
-    return sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 8 * (size_t)nodes_per_cta;
+    return sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 4 * (size_t)nodes_per_cta;
 }
 
 // Can the fast path be attempted for this call?  (Host-side, sizes only.)
