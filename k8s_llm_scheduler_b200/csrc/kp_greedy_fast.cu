@@ -32,7 +32,6 @@ namespace kp {
 
 namespace cg = cooperative_groups;
 
-constexpr int kFastThreadsMax = 1024;       // greedy loop: 256 threads when the table fits, else 1024
 constexpr int kFastMaxShapes = 128;
 constexpr int kFastMaxTraj = 4096;             // trajectory states kept in shared memory
 constexpr int kFastPodBatch = 1024;
@@ -273,25 +272,57 @@ struct FastRun {
 };
 
 // dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | c_t[nodes_per_cta]
-// THREADS x NPT nodes per CTA.  Few fat warps beat many thin ones here: the per-pod cost that does
-// not scale with the table (reductions, barrier, winner decode) is paid per warp.
-template <int THREADS, int NPT, bool MULTI, bool CLUSTER>
-__global__ void __launch_bounds__(THREADS, 1)
+// 256 threads x NPT nodes per CTA.  Few fat warps beat many thin ones here: the per-pod cost that
+// does not scale with the table (reductions, barrier, winner decode -- ~100 instructions) is paid
+// per warp, so a CTA is 8 warps holding up to 80 nodes per thread (two registers per node, four
+// with per-pod strategies) and larger tables add CTAs through a cluster (CSIZE), not warps.
+#ifndef KP_FAST_THREADS
+#define KP_FAST_THREADS 256
+#endif
+constexpr int kFastThreads = KP_FAST_THREADS;
+
+// best key among this thread's nodes that the pod fits: w - x keeps both guard bits iff it fits in
+// both dimensions.  Four independent maxima so the dependent-max chain does not bound the scan.
+template <int NPT, int KS, int Q>
+__device__ __forceinline__ uint32_t fast_scan(const uint32_t (&w)[NPT], const uint32_t (&key)[KS][NPT], uint32_t x)
+{
+    uint32_t b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u;
+#pragma unroll
+    for (int k = 0; k < NPT; ++k) {
+        const uint32_t t = w[k] - x;
+        const bool fits = ((~t) & kFastGuards) == 0u;
+        const uint32_t kk = key[Q][k];
+        if ((k & 3) == 0) { if (fits) b0 = max(b0, kk); }
+        else if ((k & 3) == 1) { if (fits) b1 = max(b1, kk); }
+        else if ((k & 3) == 2) { if (fits) b2 = max(b2, kk); }
+        else { if (fits) b3 = max(b3, kk); }
+    }
+    return max(max(b0, b1), max(b2, b3));
+}
+
+__device__ __forceinline__ void cluster_barrier()
+{
+    // release/acquire at cluster scope orders the DSMEM stores before it; no device-wide fence
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int NPT, bool MULTI, int CSIZE>
+__global__ void __launch_bounds__(kFastThreads, 1)
 fast_greedy_kernel(FastIn in, FastRun r)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
     __shared__ uint32_t s_x[kFastPodBatch + 1];
     __shared__ uint8_t s_sid[kFastPodBatch + 4];
     __shared__ uint32_t w_res[2][32];
-    __shared__ uint32_t c_res[2][8];
+    __shared__ uint32_t c_res[2][8];                                   // best key of every CTA of the cluster
     __shared__ uint32_t s_tbase[kFastMaxShapes + 1];
 
-    if (!r.hdr->ok) return;                                           // the fp64 kernel does the work instead
+    if (!r.hdr->ok) return;                                          // the fp64 kernel does the work instead
     constexpr int KS = MULTI ? kMaxStrategies : 1;
-    constexpr int kFastThreads = THREADS;
-    constexpr int NW = THREADS / 32;
+    constexpr int NW = kFastThreads / 32;
+    constexpr bool CLUSTER = CSIZE > 1;
     cg::cluster_group cluster = cg::this_cluster();
-    const int csize = CLUSTER ? (int)cluster.num_blocks() : 1;
     const int crank = CLUSTER ? (int)cluster.block_rank() : 0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = r.total;
@@ -331,6 +362,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
         }
     }
     __syncthreads();
+    if (CLUSTER) cluster_barrier();                                    // every CTA of the cluster is running before any peer stores into it
 
     for (long long base = 0; base < in.n_pods; base += kFastPodBatch) {
         const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
@@ -343,18 +375,10 @@ fast_greedy_kernel(FastIn in, FastRun r)
         uint32_t x = s_x[0];
         int s = s_sid[0];
         for (int j = 0; j < cnt; ++j) {
-            uint32_t best = 0u;
-            // both guard bits of w - x survive iff the pod fits the node in both dimensions
-            auto scan = [&](const uint32_t (&kq)[NPT]) {
-#pragma unroll
-                for (int k = 0; k < NPT; ++k) {
-                    const uint32_t t = w[k] - x;
-                    if (((~t) & kFastGuards) == 0u) best = max(best, kq[k]);
-                }
-            };
-            if (!MULTI || s == 0) scan(key[0]);                        // block-uniform branch per pod
-            else if (s == 1) scan(key[KS > 1 ? 1 : 0]);
-            else scan(key[KS > 2 ? 2 : 0]);
+            uint32_t best;
+            if (!MULTI || s == 0) best = fast_scan<NPT, KS, 0>(w, key, x);      // block-uniform branch per pod
+            else if (s == 1) best = fast_scan<NPT, KS, (KS > 1 ? 1 : 0)>(w, key, x);
+            else best = fast_scan<NPT, KS, (KS > 2 ? 2 : 0)>(w, key, x);
             const uint32_t x_next = s_x[j + 1];                        // next pod's request, off the critical path
             const int s_next = s_sid[j + 1];                           // (one spare element past the batch)
             const int par = j & 1;
@@ -363,10 +387,15 @@ fast_greedy_kernel(FastIn in, FastRun r)
             __syncthreads();
             best = __reduce_max_sync(0xffffffffu, lane < NW ? w_res[par][lane] : 0u);
             if (CLUSTER) {
-                if (tid < csize) *cluster.map_shared_rank(&c_res[par][crank], tid) = best;    // to every CTA of the cluster
-                cluster.sync();
+                // every CTA stores its best key into slot [crank] of every CTA's shared memory (DSMEM); the
+                // cluster barrier (release / acquire at cluster scope, no device-wide fence) completes the
+                // exchange.  Measured alternative, dropped: tagging the stored word with the pod number and
+                // spinning on the local slots instead of the barrier was 1.6x slower.
+                if (tid < CSIZE) *cluster.map_shared_rank(&c_res[par][crank], tid) = best;
+                cluster_barrier();
                 uint32_t g = 0u;
-                for (int c = 0; c < csize; ++c) g = max(g, c_res[par][c]);
+#pragma unroll
+                for (int c = 0; c < CSIZE; ++c) g = max(g, c_res[par][c]);
                 best = g;
             }
             x = x_next;
@@ -404,6 +433,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
         }
     }
     __syncthreads();
+    if (CLUSTER) cluster_barrier();                                    // nobody leaves while a peer may still store into it
     // final state: usage follows scheduler.py:150-151 for every node that received a pod
     for (int local = tid; local < r.nodes_per_cta; local += kFastThreads) {
         const int n = cta_base + local;
@@ -468,40 +498,41 @@ static FastLayout fast_layout(int64_t n, int64_t p)
 }
 
 constexpr int64_t kFastMinPods = 2048;         // below this the set-up costs more than it saves
-constexpr int kFastMaxNpt = 20;
+constexpr int kFastMaxNptUniform = 80;         // node slots per thread: two registers per node ...
+constexpr int kFastMaxNptMulti = 40;           // ... four with per-pod strategies
 
 static int ceil_log2(int64_t v) { int b = 0; while ((1ll << b) < v) ++b; return b; }
 
-struct FastShape { int threads, npt, cluster; };
+struct FastShape { int npt, cluster; };
 
 static size_t fast_smem_bytes(bool multi, int nodes_per_cta)
 {
     return sizeof(uint32_t) * kFastMaxTraj * (multi ? 4 : 2) + 4 * (size_t)nodes_per_cta;
 }
 
-// Can the fast path be attempted for this call?  (Host-side, sizes only.)
+// Can the fast path be attempted for this call?  (Host-side, sizes only.)  One CTA while the table
+// fits its registers (20 480 nodes, 10 240 with per-pod strategies), then clusters of 2, 4, 8 CTAs
+// at the largest slot count; beyond that the fp64 kernel does the work.
 static bool fast_eligible(int64_t n, int64_t p, int filter_mode, bool multi, FastShape *shape, int *idx_bits)
 {
     if (filter_mode != KP_FILTER_CAPACITY || p < kFastMinPods || n < 1) return false;
     if (const char *off = getenv("KP_GREEDY_NO_FAST")) if (off[0] == '1') return false;
     const int ib = std::max(1, ceil_log2(n));
     if (ib + ceil_log2(n + kFastMaxTraj + 2) > 32) return false;      // key = score rank | inverted index
-    const int max_npt = multi ? 10 : kFastMaxNpt;                     // registers: (1 + KS) words per node
     *idx_bits = ib;
+    const int max_npt = multi ? kFastMaxNptMulti : kFastMaxNptUniform;
     int c = 1;
-    if (const char *force = getenv("KP_GREEDY_CLUSTER")) c = std::max(1, std::min(8, atoi(force)));
-    if (c == 1 && n <= 256 * max_npt) {                               // one small CTA
-        *shape = FastShape{256, (int)((n + 255) / 256), 1};
-        return true;
-    }
+    if (const char *force = getenv("KP_GREEDY_CLUSTER")) c = std::max(1, std::min(8, atoi(force)));   // experiments only
     for (;; c *= 2) {
         if (c > 8) return false;
         const int64_t per_cta = (n + c - 1) / c;
-        const int need = (int)((per_cta + kFastThreadsMax - 1) / kFastThreadsMax);
-        if (need <= max_npt && fast_smem_bytes(multi, need * kFastThreadsMax) <= 200 * 1024) {
-            *shape = FastShape{kFastThreadsMax, need, c};
-            return true;
-        }
+        const int need = (int)((per_cta + kFastThreads - 1) / kFastThreads);
+        if (need > max_npt) continue;
+        int npt = max_npt;                                             // clusters exist at the largest slot count only
+        if (c == 1) for (int cand : {5, 10, 20, 40, 80}) if (need <= cand) { npt = cand; break; }
+        if (fast_smem_bytes(multi, npt * kFastThreads) > 200 * 1024) return false;
+        *shape = FastShape{npt, c};
+        return true;
     }
 }
 
@@ -510,49 +541,47 @@ size_t greedy_fast_workspace_bytes(int64_t n, int64_t p)
     return fast_layout(n, p).bytes;
 }
 
-template <int THREADS, int NPT, bool MULTI, bool CLUSTER>
-static int launch_fast(const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
+template <int NPT, bool MULTI, int CSIZE>
+static int launch_fast(const FastIn &in, const FastRun &r, size_t smem, cudaStream_t stream)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<THREADS, NPT, MULTI, CLUSTER>,
+        KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<NPT, MULTI, CSIZE>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(cluster, 1, 1);
-    cfg.blockDim = dim3(THREADS, 1, 1);
+    cfg.gridDim = dim3(CSIZE, 1, 1);
+    cfg.blockDim = dim3(kFastThreads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = cluster;
+    attr[0].val.clusterDim.x = CSIZE;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KP_CUDA(cudaLaunchKernelEx(&cfg, fast_greedy_kernel<THREADS, NPT, MULTI, CLUSTER>, in, r));
+    KP_CUDA(cudaLaunchKernelEx(&cfg, fast_greedy_kernel<NPT, MULTI, CSIZE>, in, r));
     count_launch();
     return KP_OK;
-}
-
-// node slots per thread are compiled in: 3, 5, 10 or 20 (10 at most with per-pod strategies)
-template <int THREADS, bool MULTI, bool CLUSTER>
-static int dispatch_npt(int npt, const FastIn &in, const FastRun &r, int cluster, size_t smem, cudaStream_t stream)
-{
-    if (npt <= 3) return launch_fast<THREADS, 3, MULTI, CLUSTER>(in, r, cluster, smem, stream);
-    if (npt <= 5) return launch_fast<THREADS, 5, MULTI, CLUSTER>(in, r, cluster, smem, stream);
-    if (npt <= 10) return launch_fast<THREADS, 10, MULTI, CLUSTER>(in, r, cluster, smem, stream);
-    if (MULTI) return KP_ERR_INVALID_ARG;
-    return launch_fast<THREADS, kFastMaxNpt, false, CLUSTER>(in, r, cluster, smem, stream);
 }
 
 template <bool MULTI>
 static int dispatch_fast(const FastShape &sh, const FastIn &in, const FastRun &r, size_t smem, cudaStream_t stream)
 {
-    if (sh.threads == 256) return dispatch_npt<256, MULTI, false>(sh.npt, in, r, 1, smem, stream);
-    if (sh.cluster == 1) return dispatch_npt<kFastThreadsMax, MULTI, false>(sh.npt, in, r, 1, smem, stream);
-    return dispatch_npt<kFastThreadsMax, MULTI, true>(sh.npt, in, r, sh.cluster, smem, stream);
+    constexpr int MAXN = MULTI ? kFastMaxNptMulti : kFastMaxNptUniform;
+    switch (sh.cluster) {
+        case 2: return launch_fast<MAXN, MULTI, 2>(in, r, smem, stream);
+        case 4: return launch_fast<MAXN, MULTI, 4>(in, r, smem, stream);
+        case 8: return launch_fast<MAXN, MULTI, 8>(in, r, smem, stream);
+        default: break;
+    }
+    if (sh.npt <= 5) return launch_fast<5, MULTI, 1>(in, r, smem, stream);
+    if (sh.npt <= 10) return launch_fast<10, MULTI, 1>(in, r, smem, stream);
+    if (sh.npt <= 20) return launch_fast<20, MULTI, 1>(in, r, smem, stream);
+    if (sh.npt <= 40) return launch_fast<40, MULTI, 1>(in, r, smem, stream);
+    return launch_fast<MAXN, MULTI, 1>(in, r, smem, stream);
 }
 
 // Runs the fast path when the sizes allow it.  *done_flag (device) is 1 afterwards iff the
@@ -646,7 +675,7 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
     r.out_mu = out_mu;
     r.total = total;
     r.idx_bits = idx_bits;
-    r.nodes_per_cta = shape.npt * shape.threads;
+    r.nodes_per_cta = shape.npt * kFastThreads;
     const size_t smem = fast_smem_bytes(multi, r.nodes_per_cta);
     const int st = multi ? dispatch_fast<true>(shape, in, r, smem, stream)
                          : dispatch_fast<false>(shape, in, r, smem, stream);

@@ -142,9 +142,15 @@ def test_fast_path_on_clusters(cluster, monkeypatch):
 
 
 def test_fast_path_large_tables_and_depletion():
-    nodes, pods = synth.config5(20_000, 30_000, seed=32)          # one CTA, 20 nodes per thread
+    nodes, pods = synth.config5(20_000, 30_000, seed=32)          # one CTA, 80 nodes per thread
     _check_greedy(nodes, pods, 0, 1, what="20k uniform")
     _check_greedy(nodes, pods, 0, 1, per_pod=True, what="20k per-pod (cluster of 2)")
+    nodes, pods = synth.config5(8_000, 6_000, seed=36)             # one CTA, 40 nodes per thread
+    _check_greedy(nodes, pods, 1, 1, what="8k uniform")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="8k per-pod")
+    nodes, pods = synth.config5(30_000, 5_000, seed=37)            # past one CTA's registers: cluster of 2 / of 4
+    _check_greedy(nodes, pods, 0, 1, what="30k uniform (cluster of 2)")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="30k per-pod (cluster of 4)")
     nodes, pods = synth.config3(400, 50_000)                       # fills up: trajectories run to max_pods
     _check_greedy(nodes, pods, 0, 1, what="depletion")
     g = device_greedy(nodes, pods, 0, 1)
