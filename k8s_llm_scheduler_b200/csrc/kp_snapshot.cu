@@ -302,12 +302,17 @@ int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode
 // ---------------------------------------------------------------------------------------
 // place_kernel configurations, largest pods-per-CTA first
 struct PlaceCfg { int threads, r, nsplit, chunk; };
-constexpr PlaceCfg kPlaceCfgs[] = {
-    {256, 8, 1, 2048}, {128, 8, 1, 1024}, {128, 4, 1, 512}, {256, 4, 4, 256}, {256, 4, 8, 128}, {256, 2, 8, 64},
-    {256, 8, 8, 256},     // not in the size ladder: few pods, one wave of 8-warp CTAs with 8 pods per lane
-};
+// (index, threads, pods per lane, node splits); pods per CTA = 32 * R * warps / NSPLIT
+#define KP_PLACE_CFG_LIST(X) \
+    X(0, 256, 8, 1) X(1, 128, 8, 1) X(2, 128, 4, 1) X(3, 256, 4, 4) X(4, 256, 4, 8) X(5, 256, 2, 8) \
+    X(6, 256, 8, 8) /* not in the size ladder: few pods, one wave of 8-warp CTAs with 8 pods per lane */
+// Measured on c2 and not kept (profiles/r01_place_cfg_sweep.txt): 128-thread CTAs with one or two node
+// splits (fewer, longer warps: less prologue per pair) lose more to latency than they save.
+#define KP_CFG_ROW(i, t, r, ns) {t, r, ns, 32 * r * (t / 32 / ns)},
+constexpr PlaceCfg kPlaceCfgs[] = {KP_PLACE_CFG_LIST(KP_CFG_ROW)};
+#undef KP_CFG_ROW
 constexpr int kNumPlaceCfgs = sizeof(kPlaceCfgs) / sizeof(kPlaceCfgs[0]);
-constexpr int kFirstSplitCfg = 3;        // configurations from here on split the nodes over the warps (NSPLIT > 1)
+constexpr int kLadderCfgs = 6;           // configurations 0..5 form the size ladder, largest pods-per-CTA first
 constexpr int kFallbackCfg = 4;          // few pods: 128 pods per CTA, 8 warps splitting the nodes
 
 template <int THREADS, int R, int NSPLIT>
@@ -326,13 +331,10 @@ static int place_occupancy()
 static int cfg_occupancy(int c)
 {
     switch (c) {
-        case 0: return place_occupancy<256, 8, 1>();
-        case 1: return place_occupancy<128, 8, 1>();
-        case 2: return place_occupancy<128, 4, 1>();
-        case 3: return place_occupancy<256, 4, 4>();
-        case 4: return place_occupancy<256, 4, 8>();
-        case 5: return place_occupancy<256, 2, 8>();
-        default: return place_occupancy<256, 8, 8>();
+#define KP_CFG_CASE(i, t, r, ns) case i: return place_occupancy<t, r, ns>();
+        KP_PLACE_CFG_LIST(KP_CFG_CASE)
+#undef KP_CFG_CASE
+        default: return 1;
     }
 }
 
@@ -381,15 +383,12 @@ static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream
 
 static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_t stream, int resident_cap)
 {
-    cudaError_t e;
+    cudaError_t e = cudaErrorInvalidValue;
     switch (c) {
-        case 0: e = launch_place_pdl<256, 8, 1>(pp, grid, stream, resident_cap); break;
-        case 1: e = launch_place_pdl<128, 8, 1>(pp, grid, stream, resident_cap); break;
-        case 2: e = launch_place_pdl<128, 4, 1>(pp, grid, stream, resident_cap); break;
-        case 3: e = launch_place_pdl<256, 4, 4>(pp, grid, stream, resident_cap); break;
-        case 4: e = launch_place_pdl<256, 4, 8>(pp, grid, stream, resident_cap); break;
-        case 5: e = launch_place_pdl<256, 2, 8>(pp, grid, stream, resident_cap); break;
-        default: e = launch_place_pdl<256, 8, 8>(pp, grid, stream, resident_cap); break;
+#define KP_CFG_CASE(i, t, r, ns) case i: e = launch_place_pdl<t, r, ns>(pp, grid, stream, resident_cap); break;
+        KP_PLACE_CFG_LIST(KP_CFG_CASE)
+#undef KP_CFG_CASE
+        default: break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "place_kernel launch");
     count_launch();
@@ -448,7 +447,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     const int ntiles_wide = (int)((L.npad + kTileNodesWide - 1) / kTileNodesWide);
     const int max_nseg = big ? ntiles_wide : 1;
     int cfg = kFallbackCfg;
-    for (int c = 0; c < kNumPlaceCfgs - 1; ++c) {
+    for (int c = 0; c < kLadderCfgs; ++c) {
         const int64_t chunks = (P + kPlaceCfgs[c].chunk - 1) / kPlaceCfgs[c].chunk;
         if (chunks * max_nseg >= (int64_t)4 * sms * cfg_occupancy(c)) { cfg = c; break; }
     }
@@ -560,7 +559,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.out_idx = (long long *)out_idx;
     pp.out_score = out_score;
     // pacing applies to the kernels that fetch a CTA's requests up front (node splits, one strategy)
-    const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && cfg >= kFirstSplitCfg;
+    const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && kPlaceCfgs[cfg].nsplit > 1;
     pp.flow = paced ? tuning.flow : nullptr;
     pp.flow_window = flow_window;
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e1, stream));
