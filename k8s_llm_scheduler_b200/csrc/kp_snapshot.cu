@@ -304,7 +304,7 @@ int node_scores_device(const kp_node_table &nodes, int strategy, int filter_mode
 struct PlaceCfg { int threads, r, nsplit, chunk; };
 // (index, threads, pods per lane, node splits); pods per CTA = 32 * R * warps / NSPLIT
 #define KP_PLACE_CFG_LIST(X) \
-    X(0, 256, 8, 1) X(1, 128, 8, 1) X(2, 128, 4, 1) X(3, 256, 4, 4) X(4, 256, 4, 8) X(5, 256, 2, 8) \
+    X(0, 128, 16, 1) X(1, 128, 8, 1) X(2, 128, 4, 1) X(3, 256, 4, 4) X(4, 256, 4, 8) X(5, 256, 2, 8) \
     X(6, 256, 8, 8) /* not in the size ladder: few pods, one wave of 8-warp CTAs with 8 pods per lane */
 // Measured on c2 and not kept (profiles/r01_place_cfg_sweep.txt): 128-thread CTAs with one or two node
 // splits (fewer, longer warps: less prologue per pair) lose more to latency than they save.
@@ -447,9 +447,10 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     const int ntiles_wide = (int)((L.npad + kTileNodesWide - 1) / kTileNodesWide);
     const int max_nseg = big ? ntiles_wide : 1;
     int cfg = kFallbackCfg;
-    // configuration 0 (256 threads x 8 pods per lane) is not used: 128-thread CTAs with the same 8 pods per lane
-    // compile to a tighter inner loop and measure 3-9 % faster on the large shapes (profiles/r01_place_cfg_sweep.txt)
-    for (int c = 1; c < kLadderCfgs; ++c) {
+    // The top of the ladder carries 16 pods per lane: the per-iteration overhead of the inner loop (one LDS.128,
+    // four position adds, loop control: 11 instructions) is then spread over 64 pairs instead of 32, and 16
+    // independent compare chains per lane need only 3 warps per scheduler (profiles/r01_place_cfg_sweep.txt).
+    for (int c = 0; c < kLadderCfgs; ++c) {
         const int64_t chunks = (P + kPlaceCfgs[c].chunk - 1) / kPlaceCfgs[c].chunk;
         if (chunks * max_nseg >= (int64_t)4 * sms * cfg_occupancy(c)) { cfg = c; break; }
     }
