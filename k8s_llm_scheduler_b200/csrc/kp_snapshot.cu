@@ -76,7 +76,7 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_partial = o; o = align_up(o + (sizeof(uint64_t) + sizeof(uint32_t) * 2) * kMaxStrategies * kArgmaxMaxBlocks);
     L.off_perm = o;    o = align_up(o + sizeof(uint32_t) * (per_pod ? L.slots : 0));
     const int64_t nb = big ? n : 0, npb = big ? L.npad : 0;
-    L.sort_tmp_bytes = big ? sort_temp_bytes(n) : 0;
+    L.sort_tmp_bytes = big ? align_up(sort_temp_bytes(n)) : 0;            // per sorted array (they run concurrently)
     L.off_pos = o;      o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
     L.off_kout = o;     o = align_up(o + sizeof(uint64_t) * kKeyArrays * nb);
     L.off_vout = o;     o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
@@ -84,7 +84,7 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_sorted = o;   o = align_up(o + sizeof(double) * 2 * npb);
     L.off_flag = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
     L.off_incl = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
-    L.off_sort_tmp = o; o = align_up(o + L.sort_tmp_bytes);
+    L.off_sort_tmp = o; o = align_up(o + L.sort_tmp_bytes * (kMaxStrategies + 2));
     L.off_best = o;     o = align_up(o + sizeof(uint32_t) * (big ? L.slots : 0));
     L.total = o;
     return L;
@@ -114,39 +114,85 @@ static NodePtrs node_ptrs(const kp_node_table &t)
 // ---------------------------------------------------------------------------------------
 // per-pod strategy: group pods by strategy so that a CTA scans one best-first table
 // ---------------------------------------------------------------------------------------
+// Pods grouped by strategy.  A block owns kGroupItems consecutive pods, aggregates in shared memory
+// and touches the three global counters once: with one global atomic per warp the two kernels took
+// 120 us each for 2 M pods (serialised on three addresses); the data itself is 16 MB = 3 us of HBM.
+constexpr int kGroupPerThread = 8;
+constexpr int kGroupItems = 256 * kGroupPerThread;
+
 __global__ void __launch_bounds__(256)
 group_count_kernel(const long long *__restrict__ sid, long long n_pods, SnapHeader *hdr)
 {
-    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const int g = j < n_pods ? canon_strategy(sid[j]) : -1;
+    __shared__ unsigned s_cnt[kMaxStrategies];
+    if (threadIdx.x < kMaxStrategies) s_cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * kGroupItems;
+    unsigned c[kMaxStrategies] = {0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < kGroupPerThread; ++i) {
+        const long long j = base + i * 256 + threadIdx.x;
+        if (j < n_pods) {
+            const int g = canon_strategy(sid[j]);
+#pragma unroll
+            for (int s = 0; s < kMaxStrategies; ++s) c[s] += g == s;
+        }
+    }
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {
-        const unsigned b = __ballot_sync(0xffffffffu, g == s);
-        if ((threadIdx.x & 31) == 0 && b) atomicAdd(&hdr->group_count[s], __popc(b));
+        const unsigned w = __reduce_add_sync(0xffffffffu, c[s]);
+        if ((threadIdx.x & 31) == 0 && w) atomicAdd(&s_cnt[s], w);
     }
+    __syncthreads();
+    if (threadIdx.x < kMaxStrategies && s_cnt[threadIdx.x]) atomicAdd(&hdr->group_count[threadIdx.x], s_cnt[threadIdx.x]);
 }
-
 __global__ void __launch_bounds__(256)
 group_assign_kernel(const long long *__restrict__ sid, long long n_pods, int chunk_pods,
                     SnapHeader *hdr, uint32_t *__restrict__ perm)
 {
-    long long begin[kMaxStrategies];
-    group_begins(hdr, chunk_pods, begin);
-    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const int g = j < n_pods ? canon_strategy(sid[j]) : -1;
+    __shared__ unsigned s_cnt[kMaxStrategies], s_cur[kMaxStrategies];
+    __shared__ long long s_base[kMaxStrategies];
+    if (threadIdx.x < kMaxStrategies) { s_cnt[threadIdx.x] = 0u; s_cur[threadIdx.x] = 0u; }
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * kGroupItems;
     const int lane = threadIdx.x & 31;
+    int g[kGroupPerThread];
+    unsigned c[kMaxStrategies] = {0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < kGroupPerThread; ++i) {
+        const long long j = base + i * 256 + threadIdx.x;
+        g[i] = j < n_pods ? canon_strategy(sid[j]) : -1;
+#pragma unroll
+        for (int s = 0; s < kMaxStrategies; ++s) c[s] += g[i] == s;
+    }
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {
-        const unsigned b = __ballot_sync(0xffffffffu, g == s);
-        if (!b) continue;
-        uint32_t base = 0;
-        const int leader = __ffs(b) - 1;
-        if (lane == leader) base = atomicAdd(&hdr->group_cursor[s], __popc(b));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (g == s) perm[begin[s] + base + __popc(b & ((1u << lane) - 1))] = (uint32_t)j;
+        const unsigned w = __reduce_add_sync(0xffffffffu, c[s]);
+        if (lane == 0 && w) atomicAdd(&s_cnt[s], w);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                                   // this block's range inside every group
+        long long begin[kMaxStrategies];
+        group_begins(hdr, chunk_pods, begin);
+#pragma unroll
+        for (int s = 0; s < kMaxStrategies; ++s)
+            s_base[s] = begin[s] + (s_cnt[s] ? (long long)atomicAdd(&hdr->group_cursor[s], s_cnt[s]) : 0ll);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kGroupPerThread; ++i) {
+        const long long j = base + i * 256 + threadIdx.x;
+#pragma unroll
+        for (int s = 0; s < kMaxStrategies; ++s) {
+            const unsigned b = __ballot_sync(0xffffffffu, g[i] == s);
+            if (!b) continue;
+            unsigned off = 0;
+            const int leader = __ffs(b) - 1;
+            if (lane == leader) off = atomicAdd(&s_cur[s], (unsigned)__popc(b));
+            off = __shfl_sync(0xffffffffu, off, leader);
+            if (g[i] == s) perm[s_base[s] + off + __popc(b & ((1u << lane) - 1))] = (uint32_t)j;
+        }
     }
 }
-
 // ---------------------------------------------------------------------------------------
 // KP_FILTER_READY: argmax over nodes (+ fill).  The filter does not look at the pod
 // (scheduler.py:521: _fallback_decision takes no pod), so one argmax serves every pod.
@@ -395,6 +441,33 @@ static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_
     return KP_OK;
 }
 
+// Side streams for the independent radix sorts of the large-table plan (one pool per device, made on
+// first use and kept for the life of the process).  NULL = could not be created: the sorts then run one
+// after the other on the caller's stream.
+constexpr int kSideStreams = 4;                 // up to 5 sorted arrays: 3 strategies + 2 thresholds
+struct SideStreams {
+    cudaStream_t s[kSideStreams];
+    cudaEvent_t fork, join[kSideStreams];
+};
+static SideStreams *side_streams()
+{
+    static SideStreams pool[64];
+    static int state[64] = {0};                 // 0 = not tried, 1 = ready, -1 = unavailable
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (state[dev] == 0) {
+        bool ok = getenv("KP_NO_SIDE_STREAMS") == nullptr;
+        SideStreams &p = pool[dev];
+        if (ok) ok = cudaEventCreateWithFlags(&p.fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; ok && i < kSideStreams; ++i)
+            ok = cudaStreamCreateWithFlags(&p.s[i], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&p.join[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+        state[dev] = ok ? 1 : -1;
+    }
+    return state[dev] == 1 ? &pool[dev] : nullptr;
+}
+
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                           int filter_mode, int64_t *out_idx, double *out_score, void *ws,
                           size_t ws_bytes, cudaStream_t stream, const PlaceTuning &tuning)
@@ -512,11 +585,21 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         for (int s = 0; s < kMaxStrategies; ++s) if (strat_mask & (1 << s)) list.idx[list.count++] = s;
         list.idx[list.count++] = 3;
         list.idx[list.count++] = 4;
+        // the sorts are independent and latency-bound (tens of thousands of keys, ~9 launches each):
+        // all but the first run on side streams, forked from and joined back into the caller's stream
+        SideStreams *side = side_streams();
+        if (side) KP_CUDA(cudaEventRecord(side->fork, stream));
         for (int q = 0; q < list.count; ++q) {
             const int j = list.idx[q];
-            const int st = sort_pairs_u64(tmp, L.sort_tmp_bytes, keys + (size_t)j * n, kout + (size_t)j * n, iota,
-                                          vout + (size_t)j * n, (int)n, stream);
+            cudaStream_t sq = (side && q > 0) ? side->s[q - 1] : stream;
+            if (sq != stream) KP_CUDA(cudaStreamWaitEvent(sq, side->fork, 0));
+            const int st = sort_pairs_u64(static_cast<unsigned char *>(tmp) + (size_t)q * L.sort_tmp_bytes, L.sort_tmp_bytes,
+                                          keys + (size_t)j * n, kout + (size_t)j * n, iota, vout + (size_t)j * n, (int)n, sq);
             if (st != KP_OK) return st;
+            if (sq != stream) {
+                KP_CUDA(cudaEventRecord(side->join[q - 1], sq));
+                KP_CUDA(cudaStreamWaitEvent(stream, side->join[q - 1], 0));
+            }
         }
         post_sort_kernel<<<dim3(nb, list.count), 256, 0, stream>>>(kout, vout, (int)n, (int)L.npad, list, pos, sorted, flag);
         KP_LAUNCH_CHECK("post_sort_kernel");
@@ -532,7 +615,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
 
     // ---- pods ----
     if (per_pod) {
-        const int gb = (int)((P + 255) / 256);
+        const int gb = (int)((P + kGroupItems - 1) / kGroupItems);
         group_count_kernel<<<gb, 256, 0, stream>>>((const long long *)pods.strategy_ids, P, hdr);
         KP_LAUNCH_CHECK("group_count_kernel");
         group_assign_kernel<<<gb, 256, 0, stream>>>((const long long *)pods.strategy_ids, P, chunk_pods, hdr, perm);

@@ -1,0 +1,19 @@
+"""One snapshot placement of a BASELINE shape, for profiling: python tools/snap_one.py [c2|c4shard|c5] (GPU box)."""
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch  # noqa: E402
+import bench  # noqa: E402
+from k8s_llm_scheduler_b200 import placement  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "c5"
+nodes, pods, meta = bench.make_workload(name, 0)
+dn = placement.nodes_to_device(nodes, "cuda:0")
+rc = torch.as_tensor(pods.req_cpu_milli).cuda()
+rm = torch.as_tensor(pods.req_mem_bytes).cuda()
+strat = torch.as_tensor(pods.strategy_ids).cuda() if meta["per_pod"] else meta["strategy"]
+for _ in range(3):
+    placement.snapshot_place(dn, rc, rm, strat, meta["filter"])
+torch.cuda.synchronize()
+print("ok", name)
