@@ -154,6 +154,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         "r"(parity)
         : "memory");
 }
+// cluster-wide barrier with release / acquire at cluster scope: orders shared-memory and DSMEM
+// traffic of the cluster's CTAs without the device-wide fence that cooperative_groups'
+// cluster.sync() emits (MEMBAR.ALL.GPU + ERRBAR showed up as the top stall of the kernels using it)
+__device__ __forceinline__ void cluster_barrier()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 // global -> shared bulk copy; bytes must be a multiple of 16, both addresses 16-B aligned
 __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes,
                                           uint64_t *bar)

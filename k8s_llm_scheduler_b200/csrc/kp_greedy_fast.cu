@@ -300,13 +300,6 @@ __device__ __forceinline__ uint32_t fast_scan(const uint32_t (&w)[NPT], const ui
     return max(max(b0, b1), max(b2, b3));
 }
 
-__device__ __forceinline__ void cluster_barrier()
-{
-    // release/acquire at cluster scope orders the DSMEM stores before it; no device-wide fence
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
 template <int NPT, bool MULTI, int CSIZE>
 __global__ void __launch_bounds__(kFastThreads, 1)
 fast_greedy_kernel(FastIn in, FastRun r)

@@ -191,7 +191,7 @@ plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
         }
     }
     __syncthreads();
-    cluster.sync();                                            // every CTA's accumulators are initialised
+    cluster_barrier();                                         // every CTA's accumulators are initialised
 
     for (int j = kKeyArrays - 1; j >= 0; --j) {                // thresholds (3, 4), then strategies
         if (j < kMaxStrategies && !(strat_mask & (1 << j))) continue;
@@ -229,7 +229,7 @@ plan_count_kernel(NodePtrs t, int strat_mask, PlanOut o)
             if (lane == 0) dsmem_add(cluster, &acc_live[j], live);
         }
     }
-    cluster.sync();                                            // all partial counts have landed in the leader
+    cluster_barrier();                                         // all partial counts have landed in the leader
     if (crank != 0) return;
     if (group == 0) {
 #pragma unroll
