@@ -294,6 +294,45 @@ def test_session_pinned_buffers_are_used_in_place(n, p):
         assert_same_f64(out[1].numpy(), os_)
 
 
+@pytest.mark.parametrize("n,p,per_pod", [(1000, 20_000, False), (12_000, 30_000, False), (9_000, 20_000, True)])
+def test_snapshot_captures_into_a_cuda_graph(n, p, per_pod):
+    """kp_snapshot_place is stream-ordered with caller-owned memory (no allocation, no synchronisation,
+    side streams joined back): it can be captured once and replayed on new table contents."""
+    import torch
+    from k8s_llm_scheduler_b200 import placement
+    nodes, pods = synth.config5(n, p, seed=51)
+    dev = torch.device("cuda:0")
+    dn = placement.nodes_to_device(nodes, dev)
+    rc, rm = torch.as_tensor(pods.req_cpu_milli).to(dev), torch.as_tensor(pods.req_mem_bytes).to(dev)
+    strat = torch.as_tensor(pods.strategy_ids).to(dev) if per_pod else 0
+    ws = torch.empty(placement.snapshot_workspace_bytes(n, p, per_pod), dtype=torch.uint8, device=dev)
+    out = (torch.empty(p, dtype=torch.int64, device=dev), torch.empty(p, dtype=torch.float64, device=dev))
+
+    def step():
+        placement.snapshot_place(dn, rc, rm, strat, 1, workspace=ws, out=out)
+
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        step()                                           # first call outside the capture (one-time attribute set-up)
+        torch.cuda.synchronize()
+        with torch.cuda.graph(graph, stream=side):
+            step()
+    # new requests and a changed node table in the same buffers, then replay
+    _, pods2 = synth.config5(n, p, seed=52)
+    rc.copy_(torch.as_tensor(pods2.req_cpu_milli))
+    rm.copy_(torch.as_tensor(pods2.req_mem_bytes))
+    nodes.pod_count[::3] = np.minimum(nodes.pod_count[::3] + 1, np.maximum(nodes.max_pods[::3], 0))
+    dn["pod_count"].copy_(torch.as_tensor(nodes.pod_count))
+    out[0].fill_(-9)
+    graph.replay()
+    torch.cuda.synchronize()
+    pods2.strategy_ids = pods.strategy_ids
+    oi, os_ = oracle_snapshot(nodes, pods2, 0, 1, per_pod=per_pod)
+    assert_same_idx(out[0].cpu().numpy(), oi)
+    assert_same_f64(out[1].cpu().numpy(), os_)
+
+
 def test_workspace_errors_are_reported():
     import torch
     from k8s_llm_scheduler_b200 import PlacementError, placement

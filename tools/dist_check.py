@@ -54,6 +54,21 @@ def main():
     if rank == 0:
         ok = np.array_equal(ni.cpu().numpy(), o0i) and np.array_equal(ns.cpu().numpy().view(np.uint64), o0s.view(np.uint64))
         print(f"node-sharded world={world} 20000 nodes x 200000 pods resource_balanced: parity={'OK' if ok else 'FAIL'} ({dt*1e3:.2f} ms incl. 2 all-reduces)", flush=True)
+    # what ONE per-pod exchange would cost a node-sharded GREEDY placement: a 16-byte (score, idx)
+    # all-reduce per pod, back to back on the device (the lower bound NCCL offers for DESIGN.md §7)
+    tiny = torch.zeros(2, dtype=torch.float64, device=dev)
+    for _ in range(20):
+        dist.all_reduce(tiny, op=dist.ReduceOp.MAX)
+    torch.cuda.synchronize(); dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 2000
+    a.record()
+    for _ in range(iters):
+        dist.all_reduce(tiny, op=dist.ReduceOp.MAX)
+    b.record(); torch.cuda.synchronize()
+    if rank == 0:
+        print(f"16-byte all-reduce, world={world}: {a.elapsed_time(b) * 1e3 / iters:.2f} us each, back to back "
+              f"(single-GPU greedy: 0.26 us per pod on c3, 1.1 us on c5)", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
