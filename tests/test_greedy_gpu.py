@@ -190,3 +190,25 @@ def test_fast_path_falls_back_when_preconditions_fail():
     nodes, pods = synth.config2(50, 3000)
     nodes.max_pods[:] = 1 << 25
     _check_greedy(nodes, pods, 0, 1, what="huge max_pods")
+
+
+def test_full_size_config3_greedy():
+    """BASELINE config 3 at full size (5k nodes x 1M pods, resource_balanced, sequential commit):
+    conservation properties at full size; exact parity with the oracle on the first 30k pods (a
+    greedy prefix does not depend on the pods behind it)."""
+    nodes, pods = synth.config3(5000, 1_000_000)
+    idx, score, pc, cu, mu = device_greedy(nodes, pods, 0, 1)
+    placed = idx >= 0
+    per_node = np.bincount(idx[placed], minlength=len(nodes))
+    assert np.array_equal(pc - nodes.pod_count, per_node)                 # every commit is accounted for
+    assert (pc <= np.maximum(nodes.max_pods, nodes.pod_count)).all()      # nobody is filled past max_pods
+    assert (score[~placed] == -1.0).all()
+    touched = per_node > 0
+    assert_same_f64(cu[touched], synth.usage_a3(pc[touched], nodes.max_pods[touched]), "final cpu usage")
+    assert_same_f64(mu[~touched], nodes.mem_usage_pct[~touched], "untouched mem usage")
+    again = device_greedy(nodes, pods, 0, 1)
+    assert np.array_equal(again[0], idx)
+    head = PodTable.from_columns(pods.req_cpu_milli[:30_000], pods.req_mem_bytes[:30_000])
+    o = oracle_greedy(nodes, head, 0, 1)
+    assert_same_idx(idx[:30_000], o[0])
+    assert_same_f64(score[:30_000], o[1])

@@ -349,3 +349,28 @@ def test_workspace_errors_are_reported():
     st = lib.kp_snapshot_place(ctypes.byref(nst), ctypes.byref(pst), 0, 1, out_i.data_ptr(), out_s.data_ptr(),
                                ws.data_ptr(), 1024, None)
     assert st == 2 and b"workspace" in lib.kp_last_error()
+
+
+def test_full_size_config5_snapshot():
+    """BASELINE config 5 at full size (20k heterogeneous nodes x 2M pods, per-pod strategies, ~30 %
+    infeasible): properties at full size, exact parity with the oracle on a seeded subsample."""
+    from k8s_llm_scheduler_b200 import placement
+    nodes, pods = synth.config5(20_000, 2_000_000)
+    gi, gs = device_snapshot(nodes, pods, 0, 1, per_pod=True)
+    infeasible = (gi < 0).mean()
+    assert 0.2 < infeasible < 0.4
+    assert (gs[gi < 0] == -1.0).all()
+    dn = placement.nodes_to_device(nodes, "cuda:0")
+    for sid in (0, 1, 2):
+        score, fc, fm, el = (t.cpu().numpy() for t in placement.node_scores(dn, sid, 1))
+        mine = (pods.strategy_ids == sid) & (gi >= 0)
+        g = gi[mine]
+        assert el[g].all()
+        assert (pods.req_cpu_milli[mine] / 1000.0 <= fc[g]).all()
+        assert (pods.req_mem_bytes[mine] / 1024 / 1024 / 1024 <= fm[g]).all()
+        assert np.array_equal(score[g].view(np.uint64), gs[mine].view(np.uint64))
+    sub = np.random.Generator(np.random.PCG64(8)).choice(len(pods), 3000, replace=False)
+    sp = PodTable.from_columns(pods.req_cpu_milli[sub], pods.req_mem_bytes[sub], pods.strategy_ids[sub])
+    oi, os_ = oracle_snapshot(nodes, sp, 0, 1, per_pod=True)
+    assert_same_idx(gi[sub], oi)
+    assert_same_f64(gs[sub], os_)
