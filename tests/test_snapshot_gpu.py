@@ -374,3 +374,22 @@ def test_full_size_config5_snapshot():
     oi, os_ = oracle_snapshot(nodes, sp, 0, 1, per_pod=True)
     assert_same_idx(gi[sub], oi)
     assert_same_f64(gs[sub], os_)
+
+
+def test_full_size_config4_whole():
+    """BASELINE config 4 whole on one GPU: 50k nodes x 10M pods, resource_balanced."""
+    from k8s_llm_scheduler_b200 import placement
+    nodes, pods = synth.config4(50_000, 10_000_000)
+    gi, gs = device_snapshot(nodes, pods, 0, 1)
+    assert (gi >= 0).all()
+    dn = placement.nodes_to_device(nodes, "cuda:0")
+    score, fc, fm, el = (t.cpu().numpy() for t in placement.node_scores(dn, 0, 1))
+    assert el[gi].all()
+    assert (pods.req_cpu_milli / 1000.0 <= fc[gi]).all()
+    assert (pods.req_mem_bytes / 1024 / 1024 / 1024 <= fm[gi]).all()
+    assert np.array_equal(score[gi].view(np.uint64), gs.view(np.uint64))
+    sub = np.random.Generator(np.random.PCG64(9)).choice(len(pods), 1000, replace=False)
+    sp = PodTable.from_columns(pods.req_cpu_milli[sub], pods.req_mem_bytes[sub])
+    oi, os_ = oracle_snapshot(nodes, sp, 0, 1)
+    assert_same_idx(gi[sub], oi)
+    assert_same_f64(gs[sub], os_)
