@@ -182,6 +182,7 @@ class Session:
         self._h = c_void_p()
         self.device, self.max_nodes, self.max_pods = device, max_nodes, max_pods
         self._resident = -1
+        self._memo = {}
         check(self._lib.kp_session_create(device, max_nodes, max_pods, byref(self._h)),
               "kp_session_create")
 
@@ -236,18 +237,61 @@ class Session:
         check(self._lib.kp_session_set_nodes(self._h, byref(st)), "kp_session_set_nodes")
         self._resident = st.n_nodes
 
+    # Repeated calls with the very same torch buffers (a loop over pinned tables) skip rebuilding the
+    # ctypes structs: the memo holds the objects themselves and is honoured only while every tensor is
+    # the same object at the same address.
+    def _memo_get(self, slot, owner, tensors):
+        hit = self._memo.get(slot)
+        if hit is None or hit[0] is not owner or len(hit[1]) != len(tensors):
+            return None
+        for t, (ref, ptr, count) in zip(tensors, hit[1]):
+            if t is not ref or t.data_ptr() != ptr or t.numel() != count:
+                return None
+        return hit[2]
+
+    def _memo_put(self, slot, owner, tensors, keep, value):
+        if all(type(t) is torch.Tensor and t is k for t, k in zip(tensors, keep)):
+            self._memo[slot] = (owner, [(t, t.data_ptr(), t.numel()) for t in tensors], value)
+
+    def _node_struct_memo(self, nodes):
+        if type(nodes) is not dict:
+            return self._node_struct(nodes)[0]
+        tensors = [nodes[k] for k in NODE_COLUMNS]
+        st = self._memo_get("nodes", nodes, tensors)
+        if st is None:
+            st, keep = self._node_struct(nodes)
+            self._memo_put("nodes", nodes, tensors, keep, st)
+        return st
+
+    def _pod_struct_memo(self, pods):
+        if type(pods) is not tuple:
+            return self._pod_struct(pods)[0]
+        tensors = [t for t in pods if t is not None]
+        st = self._memo_get("pods", pods, tensors)
+        if st is None:
+            st, keep = self._pod_struct(pods)
+            self._memo_put("pods", pods, tensors, keep, st)
+        return st
+
     def snapshot(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY, out=None):
         """nodes=None reuses the table kept by set_nodes().  Returns (idx, score) numpy arrays,
         or fills ``out`` = (idx, score) host buffers (numpy or pinned torch)."""
-        nst, keep = self._node_struct(nodes) if nodes is not None else (None, [])
-        pst, keep2 = self._pod_struct(pods)
+        nst = self._node_struct_memo(nodes) if nodes is not None else None
+        pst = self._pod_struct_memo(pods)
         p = pst.n_pods
         if out is None:
             out = (np.empty(p, np.int64), np.empty(p, np.float64))
-        ip, iref = _host_ptr(out[0], np.int64)
-        sp, sref = _host_ptr(out[1], np.float64)
+        ptrs = self._memo_get("out", out, list(out)) if type(out) is tuple else None
+        if ptrs is None:
+            ip, iref = _host_ptr(out[0], np.int64)
+            sp, sref = _host_ptr(out[1], np.float64)
+            if iref is not out[0] or sref is not out[1]:
+                raise TypeError("out buffers must be contiguous int64 / float64 host arrays")
+            ptrs = (ip, sp)
+            if type(out) is tuple:
+                self._memo_put("out", out, list(out), [iref, sref], ptrs)
         check(self._lib.kp_session_snapshot(self._h, byref(nst) if nst is not None else None,
-                                            byref(pst), int(strategy), int(filter_mode), ip, sp),
+                                            byref(pst), int(strategy), int(filter_mode), ptrs[0], ptrs[1]),
               "kp_session_snapshot")
         if nst is not None:
             self._resident = nst.n_nodes
