@@ -260,7 +260,7 @@ def test_session_host_api_matches_device_api():
             s.snapshot(nodes, PodTable.from_columns(np.zeros(40_000), np.zeros(40_000)), 0, 1)
 
 
-@pytest.mark.parametrize("n,p", [(1000, 30_000), (8192, 5_000), (9000, 5_000), (3, 1), (700, 257)])
+@pytest.mark.parametrize("n,p", [(1000, 30_000), (8192, 5_000), (9000, 5_000), (3, 1), (700, 257), (500, 400_000)])
 def test_session_pinned_buffers_are_used_in_place(n, p):
     """Pinned host tables: small tables with one strategy are read / written by the kernels
     directly (no staging copies); everything else takes the copy path.  Same answers either way."""
