@@ -169,10 +169,11 @@ int kp_node_scores(const kp_node_table *nodes, int strategy, int filter_mode,
  * returns the results to the host arrays and waits for them.  Pageable memory works
  * (staged copies).  PINNED host memory (cudaHostAlloc / cudaHostRegister, e.g. torch's
  * pin_memory()) is faster: a node table of up to ~18 k rows travels as one packed copy,
- * and in kp_session_snapshot with a single strategy and at most 8192 nodes the pod
- * columns and the result arrays are not copied at all: the placement kernel reads the
- * requests across the host link itself (paced so that the rows arrive in pod order and
- * scoring overlaps the transfer) and writes idx/score straight into the caller's arrays.
+ * and in kp_session_snapshot with a single strategy the result arrays are not copied:
+ * the placement kernel writes idx/score straight into the caller's arrays; with at most
+ * 8192 nodes (every pod row is then read exactly once) the pod columns are not copied
+ * either: the kernel reads the requests across the host link itself, paced so that the
+ * rows arrive in pod order and scoring overlaps the transfer.
  * Either way the caller's arrays are complete when the call returns.
  * kp_session_last_copy_bytes counts the bytes that crossed the host link in the last
  * call, whichever way they travelled.

@@ -470,8 +470,13 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     // and the results are written straight into the caller's arrays -- no staging copies, and
     // the transfers overlap the scoring CTA by CTA.
     bool in_place = false, out_in_place = false;
-    if (s->direct && b8 && snapshot_single_pass(s->resident_nodes, pods->strategy_ids != nullptr)) {
-        const void *rc = device_alias(pods->req_cpu_milli), *rm = device_alias(pods->req_mem_bytes);
+    // (requests: only when every row is read once -- a large table is cut into node segments and
+    // each segment would fetch the rows again; results: whenever pods keep their order, every row is
+    // written exactly once, by the CTA that finishes the pod chunk)
+    if (s->direct && b8 && pods->strategy_ids == nullptr) {
+        const bool once = snapshot_single_pass(s->resident_nodes, false);
+        const void *rc = once ? device_alias(pods->req_cpu_milli) : nullptr;
+        const void *rm = once ? device_alias(pods->req_mem_bytes) : nullptr;
         if ((s->direct & 1) && rc && rm && pods->n_pods <= s->max_pods) {
             dp.n_pods = pods->n_pods;
             dp.req_cpu_milli = static_cast<const int64_t *>(rc);
