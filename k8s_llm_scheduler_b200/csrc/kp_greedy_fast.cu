@@ -300,6 +300,24 @@ __device__ __forceinline__ uint32_t fast_scan(const uint32_t (&w)[NPT], const ui
     return max(max(b0, b1), max(b2, b3));
 }
 
+// Per-thread summary of its choosable nodes: field-wise minimum of the threshold words and the best
+// key.  A pod that fits the minimum fits every one of them, so the thread's candidate is the best key
+// and the scan can be skipped -- the common case when the cluster has headroom (config 3: every pod
+// fits every node with room).  The owner of a committed node recomputes its summary.
+template <int NPT>
+__device__ __forceinline__ void fast_summary(const uint32_t (&w)[NPT], const uint32_t (&key)[NPT], uint32_t &wmin,
+                                             uint32_t &kbest)
+{
+    uint32_t m = 0xffffffffu, b = 0u;
+#pragma unroll
+    for (int k = 0; k < NPT; ++k) {
+        if (key[k] != 0u) m = __vminu2(m, w[k]);
+        b = max(b, key[k]);
+    }
+    wmin = m;
+    kbest = b;
+}
+
 template <int NPT, bool MULTI, int CSIZE>
 __global__ void __launch_bounds__(kFastThreads, 1)
 fast_greedy_kernel(FastIn in, FastRun r)
@@ -354,6 +372,8 @@ fast_greedy_kernel(FastIn in, FastRun r)
             c_t[local] = sh == kNoEntry ? 0u : (r.hdr->traj_base[sh & 0x7fu] + (uint32_t)in.pod_count0[n]) & 0x7fffffffu;
         }
     }
+    uint32_t wmin = 0u, kbest = 0u;                                    // uniform strategy only (one key per node)
+    if (!MULTI) fast_summary<NPT>(w, key[0], wmin, kbest);
     __syncthreads();
     if (CLUSTER) cluster_barrier();                                    // every CTA of the cluster is running before any peer stores into it
 
@@ -369,7 +389,11 @@ fast_greedy_kernel(FastIn in, FastRun r)
         int s = s_sid[0];
         for (int j = 0; j < cnt; ++j) {
             uint32_t best;
-            if (!MULTI || s == 0) best = fast_scan<NPT, KS, 0>(w, key, x);      // block-uniform branch per pod
+            if (!MULTI) {
+                const bool all_fit = ((~(wmin - x)) & kFastGuards) == 0u;
+                if (__all_sync(0xffffffffu, all_fit)) best = kbest;    // warp-uniform: nobody in the warp needs the scan
+                else best = fast_scan<NPT, KS, 0>(w, key, x);
+            } else if (s == 0) best = fast_scan<NPT, KS, 0>(w, key, x);         // block-uniform branch per pod
             else if (s == 1) best = fast_scan<NPT, KS, (KS > 1 ? 1 : 0)>(w, key, x);
             else best = fast_scan<NPT, KS, (KS > 2 ? 2 : 0)>(w, key, x);
             const uint32_t x_next = s_x[j + 1];                        // next pod's request, off the critical path
@@ -422,6 +446,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
                         for (int q = 0; q < KS; ++q) key[q][k] = nk[q];
                     }
                 }
+                if (!MULTI) fast_summary<NPT>(w, key[0], wmin, kbest);
             }
         }
     }
