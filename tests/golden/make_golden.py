@@ -475,6 +475,33 @@ def gen_ingest(sched):
     return {"pods": pods, "nodes": nodes}
 
 
+def gen_prompts(sched):
+    """The computed node block of PromptEngine.construct_scheduling_prompt (scheduler.py:226-243)."""
+    pe = sched.PromptEngine()
+    rng = np.random.Generator(np.random.PCG64(41))
+    out = []
+    for c in range(4):
+        nodes = []
+        for i in range(int(rng.integers(1, 9))):
+            mp = int(rng.choice([30, 58, 110, 250]))
+            pc = int(rng.integers(0, mp + 1))
+            u = usage_a3(pc, mp)
+            cpu = float(rng.choice([4.0, 7.91, 16.0, 32.0, 96.0]))
+            mem = float(rng.choice([16374576 / 1024 / 1024, 64.0, 128.0, 32780300 / 1024 / 1024]))
+            nodes.append(dict(name=f"node-{c}-{i}", pc=pc, mp=mp, cu_bits=f64_bits(u), cpu=cpu, mem=mem))
+        recs = [mk_node(sched, n["name"], n["pc"], n["mp"], cpu=n["cpu"], mem=n["mem"]) for n in nodes]
+        for r, n in zip(recs, nodes):
+            r.name = n["name"]
+        pod = sched.PodSpec(name="p", namespace="default", cpu_request=0.25, memory_request=0.25,
+                            node_selector={}, tolerations=[], affinity_rules={}, priority=0)
+        prompt = pe.construct_scheduling_prompt(pod, recs)
+        a = prompt.index("AVAILABLE NODES:")
+        b = prompt.index("VALID NODE NAMES:")
+        b = prompt.index("\n", b) + 1
+        out.append({"nodes": nodes, "cluster_info": prompt[a:b]})
+    return out
+
+
 def gen_config1_trace(sched):
     """BASELINE config 1 through the reference's own _schedule_pod."""
     import yaml
@@ -535,6 +562,7 @@ def main():
         "parsers.json": gen_parsers(sched),
         "config1_trace.json": gen_config1_trace(sched),
         "ingest.json": gen_ingest(sched),
+        "prompts.json": gen_prompts(sched),
     }
     for name, obj in outputs.items():
         (OUT_DIR / name).write_text(json.dumps(obj, indent=1, sort_keys=True) + "\n")
