@@ -1,6 +1,7 @@
 """Small end-to-end case touching every kernel family, for compute-sanitizer runs."""
 import sys
-sys.path.insert(0, '/root/repo')
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 import numpy as np
 import torch
 from k8s_llm_scheduler_b200 import placement, synth
@@ -34,5 +35,21 @@ greedy(n3, p3, 0, 0, False)                      # fp64 kernel (ready filter)
 import os
 os.environ["KP_GREEDY_CLUSTER"] = "2"
 greedy(n3, p3, 0, 1, True)                       # cluster + DSMEM exchange
+os.environ.pop("KP_GREEDY_CLUSTER", None)
+# ingest kernels (strings -> columns), incl. rows the device defers to the host
+from k8s_llm_scheduler_b200 import ingest, tables
+reqs = [[{"cpu": "250m", "memory": "256Mi"}], [{"cpu": "0.1", "memory": "1Gi"}, {"cpu": "200m", "memory": "12x"}], [], [{"cpu": "1e3m"}]]
+out = ingest.ingest_pod_requests(reqs[:1] + reqs[2:3] * 300, exact=False)
+assert out.table.req_cpu_milli[0] == 250
+rows = [dict(name=f"n{i}", cpu="7910m", memory="32780300Ki", pods="110", pod_count=i % 111) for i in range(500)]
+assert np.array_equal(ingest.ingest_nodes(rows).table.alloc_cpu_milli, tables.NodeTable.from_allocatable(rows).alloc_cpu_milli)
+# host session with pinned buffers (in-place reads / writes, paced)
+hn = {k: torch.as_tensor(getattr(n1, k)).pin_memory() for k in tables.NODE_COLUMNS}
+hp = (torch.as_tensor(p1.req_cpu_milli).pin_memory(), torch.as_tensor(p1.req_mem_bytes).pin_memory(), None)
+ho = (torch.empty(len(p1), dtype=torch.int64).pin_memory(), torch.empty(len(p1), dtype=torch.float64).pin_memory())
+with placement.Session(0, max_nodes=len(n1), max_pods=len(p1)) as sess:
+    sess.snapshot(hn, hp, 1, 1, out=ho)
+oi, _ = c_oracle.snapshot(n1.columns(), p1.req_cpu_milli, p1.req_mem_bytes, strategy=1, filter_mode=1, threads=4)
+assert np.array_equal(ho[0].numpy(), oi)
 torch.cuda.synchronize()
 print("sanitize case ok")
