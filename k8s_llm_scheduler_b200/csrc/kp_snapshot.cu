@@ -9,6 +9,7 @@
 // KP_FILTER_READY (the reference's own filter) is pod-independent: every pod of a strategy
 // gets the same node, so that mode is an argmax over nodes plus a fill (this file).
 #include <algorithm>
+#include <mutex>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -448,13 +449,16 @@ constexpr int kSideStreams = 4;                 // up to 5 sorted arrays: 3 stra
 struct SideStreams {
     cudaStream_t s[kSideStreams];
     cudaEvent_t fork, join[kSideStreams];
+    std::mutex mu;                              // the events are shared: one fork/join sequence is enqueued at a time
 };
 static SideStreams *side_streams()
 {
     static SideStreams pool[64];
     static int state[64] = {0};                 // 0 = not tried, 1 = ready, -1 = unavailable
+    static std::mutex once;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(once);                // first use may come from several host threads
     if (state[dev] == 0) {
         bool ok = getenv("KP_NO_SIDE_STREAMS") == nullptr;
         SideStreams &p = pool[dev];
@@ -588,7 +592,11 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         // the sorts are independent and latency-bound (tens of thousands of keys, ~9 launches each):
         // all but the first run on side streams, forked from and joined back into the caller's stream
         SideStreams *side = side_streams();
-        if (side) KP_CUDA(cudaEventRecord(side->fork, stream));
+        std::unique_lock<std::mutex> side_lock;
+        if (side) {
+            side_lock = std::unique_lock<std::mutex>(side->mu);
+            KP_CUDA(cudaEventRecord(side->fork, stream));
+        }
         for (int q = 0; q < list.count; ++q) {
             const int j = list.idx[q];
             cudaStream_t sq = (side && q > 0) ? side->s[q - 1] : stream;
@@ -601,6 +609,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
                 KP_CUDA(cudaStreamWaitEvent(stream, side->join[q - 1], 0));
             }
         }
+        if (side_lock.owns_lock()) side_lock.unlock();
         post_sort_kernel<<<dim3(nb, list.count), 256, 0, stream>>>(kout, vout, (int)n, (int)L.npad, list, pos, sorted, flag);
         KP_LAUNCH_CHECK("post_sort_kernel");
         for (int tq = 0; tq < 2; ++tq) {
