@@ -25,6 +25,12 @@
  *     selected_node == ""), fp64 score of the chosen node (-1.0 = none, the reference's
  *     best_score sentinel, scheduler.py:529).
  *   - values must satisfy |x| < 2^53 (exact in fp64); n_nodes < 2^31 - 4096.
+ *   - threads: the reference calls this path from one thread (scheduler.py:654-729).  The
+ *     library itself allows concurrent calls from several host threads as long as they do
+ *     not share a workspace, an output buffer or a session; the only shared state is a
+ *     per-device pool of helper streams (large node tables), whose use is serialised
+ *     inside the library.  Device entry points can be captured in CUDA graphs once the
+ *     first (uncaptured) call on that device has run.
  */
 #ifndef K8S_PLACE_B200_H
 #define K8S_PLACE_B200_H

@@ -77,3 +77,22 @@ def test_node_mirrors_match_the_reference():
         assert bits(o.available_memory) == rec["available_memory_bits"]
         assert bits(o.cpu_usage_percent) == rec["cu_bits"]
     assert seen_ok >= 150
+
+
+def test_inexact_rows_are_rounded_or_refused_like_the_host_tables():
+    """Rows the device parsed but flagged as having no exact wire value: same outcome as tables.py."""
+    from k8s_llm_scheduler_b200.ingest import ROW_HOST, _round_inexact
+    values = np.array([0.25, 0.1 + 0.2, 1e13, 0.30000000000000004, -0.0, 7.0])
+    status = np.array([0, 1, 1 | ROW_HOST, 1, 1, 0], dtype=np.uint8)
+    wire = np.array([250, -1, -1, -1, -1, 7000], dtype=np.int64)
+    _round_inexact(status, 1, values, 1000.0, wire, tables.cores_to_milli, exact=False)
+    assert wire.tolist() == [250, 300, -1, 300, 0, 7000]          # row 2 is the host's, untouched here
+    with pytest.raises(ValueError):
+        _round_inexact(status, 1, values, 1000.0, wire.copy(), tables.cores_to_milli, exact=True)
+    big = np.array([1e16])
+    with pytest.raises(ValueError):                                 # outside the int64 wire range even when rounding
+        _round_inexact(np.array([1], dtype=np.uint8), 1, big, 1000.0, np.zeros(1, np.int64), tables.cores_to_milli, False)
+    only_zero = np.array([-0.0])
+    w = np.array([-1], dtype=np.int64)
+    _round_inexact(np.array([1], dtype=np.uint8), 1, only_zero, 1000.0, w, tables.cores_to_milli, exact=True)
+    assert w.tolist() == [0]                                        # -0.0 == 0: fine for tables.py, fine here
