@@ -300,6 +300,23 @@ __device__ __forceinline__ uint32_t fast_scan(const uint32_t (&w)[NPT], const ui
     return max(max(b0, b1), max(b2, b3));
 }
 
+// Registers cannot be indexed at run time: the committed node's slot is reached through a binary tree
+// of branches (about log2(NPT) compares for the one lane that commits) instead of NPT predicated moves.
+template <int NPT, int KS, int LO, int HI>
+__device__ __forceinline__ void fast_set_slot(uint32_t (&w)[NPT], uint32_t (&key)[KS][NPT], int slot, uint32_t nw,
+                                              const uint32_t (&nk)[KS])
+{
+    if constexpr (LO == HI) {
+        w[LO] = nw;
+#pragma unroll
+        for (int q = 0; q < KS; ++q) key[q][LO] = nk[q];
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (slot <= MID) fast_set_slot<NPT, KS, LO, MID>(w, key, slot, nw, nk);
+        else fast_set_slot<NPT, KS, MID + 1, HI>(w, key, slot, nw, nk);
+    }
+}
+
 // Per-thread summary of its choosable nodes: field-wise minimum of the threshold words and the best
 // key.  A pod that fits the minimum fits every one of them, so the thread's candidate is the best key
 // and the scan can be skipped -- the common case when the cluster has headroom (config 3: every pod
@@ -437,16 +454,18 @@ fast_greedy_kernel(FastIn in, FastRun r)
                     const uint32_t kr = traj_key[q * kFastMaxTraj + t2];
                     nk[q] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
                 }
-                const int kidx = local / kFastThreads;
+                fast_set_slot<NPT, KS, 0, NPT - 1>(w, key, local / kFastThreads, nw, nk);
+                if (!MULTI) {
+                    // The summary after the commit: the best key exactly (this node held it), the minimum
+                    // thresholds only as a lower bound -- folding the node's new word in is exact while
+                    // thresholds shrink with every commit (the usual case) and merely conservative
+                    // otherwise: a stale-low minimum sends the thread through the full scan, never past it.
+                    uint32_t b = 0u;
 #pragma unroll
-                for (int k = 0; k < NPT; ++k) {
-                    if (k == kidx) {
-                        w[k] = nw;
-#pragma unroll
-                        for (int q = 0; q < KS; ++q) key[q][k] = nk[q];
-                    }
+                    for (int k = 0; k < NPT; ++k) b = max(b, key[0][k]);
+                    kbest = b;
+                    if (nk[0] != 0u) wmin = __vminu2(wmin, nw);
                 }
-                if (!MULTI) fast_summary<NPT>(w, key[0], wmin, kbest);
             }
         }
     }
