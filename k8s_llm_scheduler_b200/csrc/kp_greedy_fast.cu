@@ -460,10 +460,15 @@ fast_greedy_kernel(FastIn in, FastRun r)
                     // thresholds only as a lower bound -- folding the node's new word in is exact while
                     // thresholds shrink with every commit (the usual case) and merely conservative
                     // otherwise: a stale-low minimum sends the thread through the full scan, never past it.
-                    uint32_t b = 0u;
+                    uint32_t b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u;          // four chains: this is on the critical path
 #pragma unroll
-                    for (int k = 0; k < NPT; ++k) b = max(b, key[0][k]);
-                    kbest = b;
+                    for (int k = 0; k < NPT; ++k) {
+                        if ((k & 3) == 0) b0 = max(b0, key[0][k]);
+                        else if ((k & 3) == 1) b1 = max(b1, key[0][k]);
+                        else if ((k & 3) == 2) b2 = max(b2, key[0][k]);
+                        else b3 = max(b3, key[0][k]);
+                    }
+                    kbest = max(max(b0, b1), max(b2, b3));
                     if (nk[0] != 0u) wmin = __vminu2(wmin, nw);
                 }
             }
