@@ -486,7 +486,60 @@ def run_extras(args, torch, placement, lib, dev):
         extras["ingest"] = run_ingest_extra(torch, lib, dev)
     except Exception as ex:  # noqa: BLE001
         extras["ingest"] = {"error": repr(ex)}
+    try:
+        extras["cache_keys"] = run_cachekey_extra(torch, lib, dev)
+    except Exception as ex:  # noqa: BLE001
+        extras["cache_keys"] = {"error": repr(ex)}
     return extras
+
+
+def run_cachekey_extra(torch, lib, dev, n_pods=100_000, n_nodes=1000, cpu_sample=3000):
+    """RequestCache keys (md5 of pod prefix + shared node text) for a batch of
+    pods in one kernel; hashlib on one core over a sample as the CPU baseline."""
+    import ctypes
+    import hashlib
+    from k8s_llm_scheduler_b200 import cachekey, ingest, synth
+    from k8s_llm_scheduler_b200.tables import NodeMetrics, PodSpec
+    nodes, pods = synth.config2(n_nodes, n_pods)
+    recs = [NodeMetrics(f"node-{i}", float(nodes.cpu_usage_pct[i]), float(nodes.mem_usage_pct[i]), 32.0, 128.0,
+                        int(nodes.pod_count[i]), int(nodes.max_pods[i])) for i in range(n_nodes)]
+    specs = [PodSpec(f"p{j}", "default", c / 1000.0, m / 2 ** 30) for j, (c, m) in
+             enumerate(zip(pods.req_cpu_milli.tolist(), pods.req_mem_bytes.tolist()))]
+    text = cachekey.nodes_text(recs)
+    t0 = time.perf_counter()
+    prefix, off = ingest.pack_strings([cachekey.pod_prefix(p) for p in specs])
+    host_s = time.perf_counter() - t0
+    d_prefix, d_off = torch.from_numpy(prefix).to(dev), torch.from_numpy(off).to(dev)
+    d_text = torch.from_numpy(np.frombuffer(bytearray(text, "utf-8"), dtype=np.uint8)).to(dev)
+    out = torch.empty((n_pods, 16), dtype=torch.uint8, device=dev)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def launch():
+        assert lib.kp_cache_keys(d_prefix.data_ptr(), d_off.data_ptr(), n_pods, d_text.data_ptr(), d_text.numel(),
+                                 out.data_ptr(), stream) == 0
+
+    for _ in range(3):
+        launch()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    a.record()
+    for _ in range(reps):
+        launch()
+    b.record()
+    torch.cuda.synchronize()
+    t_dev = a.elapsed_time(b) * 1e-3 / reps
+    t0 = time.perf_counter()
+    want = [hashlib.md5((cachekey.pod_prefix(p) + text).encode()).hexdigest() for p in specs[:cpu_sample]]
+    cpu_s = time.perf_counter() - t0
+    got = [row.tobytes().hex() for row in out[:cpu_sample].cpu().numpy()]
+    hashed = float(n_pods) * (len(text) + float(off[-1]) / n_pods)
+    return {"workload": f"{n_pods} pods x {n_nodes} nodes, node text {len(text)} bytes",
+            "device_ms": t_dev * 1e3, "keys_per_sec_device": n_pods / t_dev, "hashed_GB_per_sec": hashed / t_dev / 1e9,
+            "host_prefix_format_ms": host_s * 1e3,
+            "cpu_baseline": {"value": cpu_sample / cpu_s, "unit": "keys/s", "cores": 1, "kind": "port",
+                             "sample": f"first {cpu_sample} pods, hashlib.md5 over the reference's key string"},
+            "parity_vs_cpu_sample": got == want}
 
 
 def run_ingest_extra(torch, lib, dev, n_pods=1_000_000, cpu_sample=40_000):

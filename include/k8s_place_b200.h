@@ -256,6 +256,17 @@ int kp_ingest_nodes(const kp_node_strings *in, int64_t *out_alloc_cpu_milli,
                     double *out_mem_usage_pct, double *out_available_cpu,
                     double *out_available_memory, uint8_t *out_status, void *stream);
 
+/* ---- cache keys in bulk, device pointers ---------------------------------------------
+ * RequestCache._generate_key (scheduler.py:265-271): md5 over
+ *     f"{cpu_request}_{memory_request}_{priority}_" + "_".join(f"{name}_{cpu%:.1f}_{mem%:.1f}" for nodes sorted by name)
+ * for every pod of a batch against one node table.  The caller formats
+ * the per-pod prefixes (Python float repr) and the node text once; the device hashes
+ * prefix_j + nodes_text for all pods in parallel.  prefix_offsets has n_pods + 1 entries;
+ * out_digest receives 16 bytes per pod in hexdigest() byte order and must be 4-byte aligned.
+ */
+int kp_cache_keys(const uint8_t *prefix_text, const int64_t *prefix_offsets, int64_t n_pods,
+                  const uint8_t *nodes_text, int64_t nodes_len, uint8_t *out_digest, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,6 +76,7 @@ SYMBOLS = {
     "kp_session_last_copy_bytes": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),
     "kp_ingest_pod_requests": (c_int, [POINTER(KpPodRequestStrings), c_void_p, c_void_p, c_void_p,
                                        c_void_p, c_void_p, c_void_p]),
+    "kp_cache_keys": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "kp_ingest_nodes": (c_int, [POINTER(KpNodeStrings), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_void_p, c_void_p]),
 }

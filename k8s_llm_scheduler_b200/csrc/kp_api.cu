@@ -373,6 +373,18 @@ int kp_ingest_nodes(const kp_node_strings *in, int64_t *out_alloc_cpu_milli, int
                                out_available_memory, out_status, (cudaStream_t)stream);
 }
 
+int kp_cache_keys(const uint8_t *prefix_text, const int64_t *prefix_offsets, int64_t n_pods, const uint8_t *nodes_text,
+                  int64_t nodes_len, uint8_t *out_digest, void *stream)
+{
+    if (n_pods < 0 || nodes_len < 0) { set_error("cache keys: negative size"); return KP_ERR_INVALID_ARG; }
+    if (n_pods > 0 && (!prefix_offsets || !out_digest || (nodes_len > 0 && !nodes_text))) {
+        set_error("cache keys: prefix_offsets / nodes_text / out_digest is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    if (reinterpret_cast<uintptr_t>(out_digest) & 3u) { set_error("cache keys: out_digest must be 4-byte aligned"); return KP_ERR_INVALID_ARG; }
+    return cache_keys_device(prefix_text, prefix_offsets, n_pods, nodes_text, nodes_len, out_digest, (cudaStream_t)stream);
+}
+
 int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_session **out)
 {
     if (!out || max_nodes < 0 || max_pods < 0) { set_error("bad session arguments"); return KP_ERR_INVALID_ARG; }

@@ -232,6 +232,9 @@ int ingest_pods_device(const kp_pod_request_strings &in, int64_t *out_milli, int
 int ingest_nodes_device(const kp_node_strings &in, int64_t *out_milli, int64_t *out_bytes,
                         int64_t *out_max_pods, double *out_cu, double *out_mu, double *out_avail_cpu,
                         double *out_avail_mem, uint8_t *out_status, cudaStream_t stream);
+// kp_cachekey.cu: md5 of (per-pod prefix + shared node text) for a batch of pods
+int cache_keys_device(const uint8_t *prefix, const int64_t *prefix_off, int64_t n_pods, const uint8_t *nodes_text,
+                      int64_t nodes_len, uint8_t *out, cudaStream_t stream);
 int sm_count_cached();
 // kp_sort.cu: library radix sort / scan for the large-table plan (temp storage from the workspace)
 size_t sort_temp_bytes(int64_t n);

@@ -502,6 +502,34 @@ def gen_prompts(sched):
     return out
 
 
+def gen_cache_keys(sched):
+    """RequestCache._generate_key (scheduler.py:265-271) on a few clusters and pods."""
+    cache = sched.RequestCache()
+    rng = np.random.Generator(np.random.PCG64(43))
+    out = []
+    for c, n_nodes in enumerate([0, 1, 3, 40, 700]):
+        nodes = []
+        for i in rng.permutation(n_nodes):
+            mp = int(rng.choice([30, 58, 110, 250]))
+            pc = int(rng.integers(0, mp + 1))
+            nodes.append(dict(name=f"ip-10-0-{int(i) // 250}-{int(i) % 250}.ec2.internal" if c % 2 else f"node-{int(i)}",
+                              pc=pc, mp=mp, cu_bits=f64_bits(usage_a3(pc, mp))))
+        recs = [mk_node(sched, 0, n["pc"], n["mp"]) for n in nodes]
+        for r, n in zip(recs, nodes):
+            r.name = n["name"]
+        pods, keys = [], []
+        for j in range(12):
+            cpu = [0.25, 0.5, 0.1, 0.30000000000000004, 4.0, 1e-05, 123456.789, 0.0][j % 8]
+            mem = [0.25, 0.5, 0.125, 1.0, 16.0, 0.0009765625, 1e22, 0.0][(j * 3) % 8]
+            prio = [0, 1000, -5, 2000000000][j % 4]
+            pod = sched.PodSpec(name=f"p{j}", namespace="default", cpu_request=cpu, memory_request=mem,
+                                node_selector={}, tolerations=[], affinity_rules={}, priority=prio)
+            pods.append(dict(cpu_bits=f64_bits(cpu), mem_bits=f64_bits(mem), priority=prio))
+            keys.append(cache._generate_key(pod, recs))
+        out.append({"nodes": nodes, "pods": pods, "keys": keys})
+    return out
+
+
 def gen_config1_trace(sched):
     """BASELINE config 1 through the reference's own _schedule_pod."""
     import yaml
@@ -563,6 +591,7 @@ def main():
         "config1_trace.json": gen_config1_trace(sched),
         "ingest.json": gen_ingest(sched),
         "prompts.json": gen_prompts(sched),
+        "cache_keys.json": gen_cache_keys(sched),
     }
     for name, obj in outputs.items():
         (OUT_DIR / name).write_text(json.dumps(obj, indent=1, sort_keys=True) + "\n")
