@@ -59,5 +59,28 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+def pyobj_path() -> Path:
+    import sysconfig
+    return PKG_DIR / ("_kp_pyobj" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+
+
+def build_pyobj(force: bool = False) -> Path:
+    """gcc build of the small CPython extension that walks reference-style record lists in C
+    (csrc/kp_pyobj.c); optional: tables.py keeps the same conversions in Python."""
+    import sysconfig
+    out, src = pyobj_path(), CSRC / "kp_pyobj.c"
+    if not force and out.exists() and out.stat().st_mtime >= src.stat().st_mtime:
+        return out
+    cc = os.environ.get("CC") or shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        raise RuntimeError("no C compiler for the record-walker extension")
+    cmd = [cc, "-O2", "-shared", "-fPIC", "-I", sysconfig.get_paths()["include"], str(src), "-o", str(out), "-lm"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"{cc} failed:\n{res.stdout}\n{res.stderr}")
+    return out
+
+
 if __name__ == "__main__":
     print(build_library(force=True, verbose=True))
+    print(build_pyobj(force=True))

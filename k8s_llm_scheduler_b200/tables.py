@@ -130,6 +130,24 @@ def gib_to_bytes(gib: float, exact: bool = True) -> int:
     return b
 
 
+_WALKER = [False]
+
+
+def _record_walker():
+    """The optional C walker over reference-style records (built by build.build_pyobj); None when it
+    has not been built or KP_NO_PYOBJ is set -- the Python loops below are then used, same results."""
+    if _WALKER[0] is False:
+        import os
+        mod = None
+        if not os.environ.get("KP_NO_PYOBJ"):
+            try:
+                from . import _kp_pyobj as mod          # noqa: PLC0415
+            except ImportError:
+                mod = None
+        _WALKER[0] = mod
+    return _WALKER[0]
+
+
 # ---- wire tables --------------------------------------------------------------------
 NODE_COLUMNS = ("alloc_cpu_milli", "alloc_mem_bytes", "pod_count", "max_pods", "ready",
                 "cpu_usage_pct", "mem_usage_pct")
@@ -171,6 +189,12 @@ class NodeTable:
         t = cls(np.empty(n, np.int64), np.empty(n, np.int64), np.empty(n, np.int64),
                 np.empty(n, np.int64), np.empty(n, np.uint8), np.empty(n, np.float64),
                 np.empty(n, np.float64), [None] * n)
+        walker = _record_walker()
+        if walker is not None:               # same conversions and checks, in C (csrc/kp_pyobj.c)
+            walker.node_metrics_to_columns(nodes, t.alloc_cpu_milli, t.alloc_mem_bytes, t.pod_count, t.max_pods,
+                                           t.ready, t.cpu_usage_pct, t.mem_usage_pct, exact)
+            t.names = [nd.name for nd in nodes]
+            return t
         for i, nd in enumerate(nodes):
             t.alloc_cpu_milli[i] = cores_to_milli(nd.available_cpu, exact)
             t.alloc_mem_bytes[i] = gib_to_bytes(nd.available_memory, exact)
@@ -217,8 +241,13 @@ class PodTable:
     @classmethod
     def from_pod_specs(cls, pods: Sequence[Any], strategies: Optional[Sequence[str]] = None,
                        exact: bool = True) -> "PodTable":
-        cpu = np.array([cores_to_milli(p.cpu_request, exact) for p in pods], dtype=np.int64)
-        mem = np.array([gib_to_bytes(p.memory_request, exact) for p in pods], dtype=np.int64)
+        walker = _record_walker()
+        if walker is not None:
+            cpu, mem = np.empty(len(pods), np.int64), np.empty(len(pods), np.int64)
+            walker.pod_specs_to_columns(pods, cpu, mem, exact)
+        else:
+            cpu = np.array([cores_to_milli(p.cpu_request, exact) for p in pods], dtype=np.int64)
+            mem = np.array([gib_to_bytes(p.memory_request, exact) for p in pods], dtype=np.int64)
         sid = None if strategies is None else np.array([strategy_id(s) for s in strategies], np.int64)
         return cls(cpu, mem, sid, [p.name for p in pods])
 

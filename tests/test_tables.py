@@ -88,3 +88,45 @@ def test_config5_infeasible_fraction():
                                strategy_ids=pods.strategy_ids, filter_mode=1, threads=4)
     frac = (idx < 0).mean()
     assert 0.27 < frac < 0.33, frac
+
+
+def test_c_record_walker_equals_the_python_loops(monkeypatch):
+    """csrc/kp_pyobj.c against the Python loops of tables.py on the same records: columns, readiness
+    (every condition variant of the golden decisions), exactness errors, range errors."""
+    import k8s_llm_scheduler_b200.tables as T
+    from k8s_llm_scheduler_b200.build import build_pyobj
+    from tests.helpers import COND
+    build_pyobj()
+    rng = np.random.Generator(np.random.PCG64(17))
+    conds = list(COND.values()) + [[{"type": "Ready"}], [{"status": "True"}], [{"type": "Ready", "status": True}]]
+    nodes = [T.NodeMetrics(f"n{i}", float(rng.random() * 50), 0 if i % 7 == 0 else float(rng.random() * 50),
+                           int(rng.integers(1, 64000)) / 1000.0, int(rng.integers(1, 1 << 40)) / 1024 / 1024 / 1024,
+                           int(rng.integers(0, 200)), int(rng.integers(0, 200)), conditions=conds[i % len(conds)])
+             for i in range(500)]
+    pods = [T.PodSpec(f"p{j}", "d", int(rng.integers(0, 64000)) / 1000.0, int(rng.integers(0, 1 << 36)) / 2 ** 30)
+            for j in range(500)]
+
+    def both(fn):
+        monkeypatch.setattr(T, "_WALKER", [False])
+        monkeypatch.delenv("KP_NO_PYOBJ", raising=False)
+        assert T._record_walker() is not None
+        fast = fn()
+        monkeypatch.setattr(T, "_WALKER", [None])
+        return fast, fn()
+
+    a, b = both(lambda: T.NodeTable.from_node_metrics(nodes))
+    for col in T.NODE_COLUMNS:
+        assert np.array_equal(getattr(a, col), getattr(b, col)), col
+        assert getattr(a, col).dtype == getattr(b, col).dtype
+    assert a.names == b.names and a.ready.sum() not in (0, len(nodes))
+    a, b = both(lambda: T.PodTable.from_pod_specs(pods))
+    assert np.array_equal(a.req_cpu_milli, b.req_cpu_milli) and np.array_equal(a.req_mem_bytes, b.req_mem_bytes)
+    for bad in (0.1 + 0.2, float("nan"), 1e300):
+        for exact in (True, False):
+            def one(bad=bad, exact=exact):
+                try:
+                    return T.PodTable.from_pod_specs([T.PodSpec("p", "d", bad, 1.0)], exact=exact).req_cpu_milli.tolist()
+                except ValueError:
+                    return "ValueError"
+            fast, slow = both(one)
+            assert fast == slow, (bad, exact)
