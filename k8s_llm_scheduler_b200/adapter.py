@@ -34,7 +34,11 @@ class FallbackPlacer:
         self.config = config if config is not None else {}
         self.decision_cls = decision_cls
         self.session = Session(device=device, max_nodes=max_nodes, max_pods=max_pods)
-        self._one_pod = PodTable.from_columns([0], [0])
+        # one-decision calls: the single (dummy) request and the result live in pinned host memory, so the
+        # kernels read / write them in place and the call needs no pod or result copies
+        import torch
+        self._one_pod = (torch.zeros(1, dtype=torch.int64).pin_memory(), torch.zeros(1, dtype=torch.int64).pin_memory(), None)
+        self._one_out = (torch.empty(1, dtype=torch.int64).pin_memory(), torch.empty(1, dtype=torch.float64).pin_memory())
 
     def strategy(self) -> str:
         return self.config.get("fallback", {}).get("strategy", "resource_balanced")
@@ -46,7 +50,7 @@ class FallbackPlacer:
         strategy = self.strategy()
         try:
             table = NodeTable.from_node_metrics(node_metrics, exact=False)   # Ready-only filter
-            idx, _ = self.session.snapshot(table, self._one_pod, strategy_id(strategy), FILTER_READY)
+            idx, _ = self.session.snapshot(table, self._one_pod, strategy_id(strategy), FILTER_READY, out=self._one_out)
             i = int(idx[0])
         except PlacementError as e:        # never raise into the scheduling loop
             logger.error("GPU fallback placement failed: %s", e)
