@@ -12,6 +12,7 @@
 #include <Python.h>
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 static PyObject *s_available_cpu, *s_available_memory, *s_pod_count, *s_max_pods, *s_conditions,
     *s_cpu_usage, *s_mem_usage, *s_cpu_request, *s_memory_request, *s_type, *s_status, *s_get;
@@ -203,9 +204,109 @@ static PyObject *pod_specs_to_columns(PyObject *self, PyObject *args)
     Py_RETURN_NONE;
 }
 
+/* ---- pack_pod_requests(pods) -> (begin, cpu_text, cpu_off, mem_text, mem_off, odd) -------------------------
+ * ingest.flatten_pod_requests + pack_strings in one pass: per pod a sequence of container `requests`
+ * mappings (None / empty = container without requests, dropped like scheduler.py:738); a missing key
+ * reads as "0" (:739-740); a pod holding a non-string quantity is listed in `odd` (the host mirror
+ * redoes it) and contributes "0" placeholders.  Buffers come back as bytearrays (int64 little-endian
+ * for the offset arrays). */
+typedef struct { char *p; Py_ssize_t len, cap; } buf_t;
+
+static int buf_put(buf_t *b, const void *src, Py_ssize_t n)
+{
+    if (b->len + n > b->cap) {
+        Py_ssize_t cap = b->cap ? b->cap * 2 : 1 << 16;
+        while (cap < b->len + n) cap *= 2;
+        char *q = PyMem_Realloc(b->p, (size_t)cap);
+        if (!q) { PyErr_NoMemory(); return -1; }
+        b->p = q;
+        b->cap = cap;
+    }
+    memcpy(b->p + b->len, src, (size_t)n);
+    b->len += n;
+    return 0;
+}
+
+static int put_quantity(PyObject *req, PyObject *key, buf_t *text, buf_t *off, int *odd)
+{
+    PyObject *v = PyDict_CheckExact(req) ? PyDict_GetItemWithError(req, key) : NULL;   /* borrowed */
+    PyObject *owned = NULL;
+    if (!v) {
+        if (PyErr_Occurred()) return -1;
+        if (!PyDict_CheckExact(req)) {                  /* any mapping with .get */
+            owned = PyObject_CallMethodObjArgs(req, s_get, key, NULL);
+            if (!owned) return -1;
+            v = owned == Py_None ? NULL : owned;
+        }
+    }
+    const char *str = "0";
+    Py_ssize_t n = 1;
+    if (v) {
+        if (PyUnicode_Check(v)) {
+            str = PyUnicode_AsUTF8AndSize(v, &n);
+            if (!str) { Py_XDECREF(owned); return -1; }
+        } else {
+            *odd = 1;
+        }
+    }
+    int rc = buf_put(text, str, n);
+    Py_XDECREF(owned);
+    if (rc < 0) return -1;
+    const int64_t end = (int64_t)text->len;
+    return buf_put(off, &end, 8);
+}
+
+static PyObject *pack_pod_requests(PyObject *self, PyObject *arg)
+{
+    static PyObject *s_cpu = NULL, *s_memory = NULL;
+    if (!s_cpu) { s_cpu = PyUnicode_InternFromString("cpu"); s_memory = PyUnicode_InternFromString("memory"); }
+    PyObject *seq = PySequence_Fast(arg, "pods must be a sequence");
+    if (!seq) return NULL;
+    const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
+    buf_t begin = {0}, ct = {0}, co = {0}, mt = {0}, mo = {0};
+    PyObject *odd = PyList_New(0), *result = NULL;
+    const int64_t zero = 0;
+    int ok = odd && buf_put(&begin, &zero, 8) == 0 && buf_put(&co, &zero, 8) == 0 && buf_put(&mo, &zero, 8) == 0;
+    int64_t rows = 0;
+    for (Py_ssize_t j = 0; ok && j < n; ++j) {
+        PyObject *containers = PySequence_Fast(PySequence_Fast_GET_ITEM(seq, j), "a pod's containers must be a sequence");
+        if (!containers) { ok = 0; break; }
+        int is_odd = 0;
+        const Py_ssize_t k = PySequence_Fast_GET_SIZE(containers);
+        for (Py_ssize_t c = 0; ok && c < k; ++c) {
+            PyObject *req = PySequence_Fast_GET_ITEM(containers, c);
+            const int truth = PyObject_IsTrue(req);
+            if (truth < 0) { ok = 0; break; }
+            if (!truth) continue;
+            int o2 = 0;
+            if (put_quantity(req, s_cpu, &ct, &co, &o2) < 0 || put_quantity(req, s_memory, &mt, &mo, &o2) < 0) { ok = 0; break; }
+            is_odd |= o2;
+            ++rows;
+        }
+        Py_DECREF(containers);
+        if (!ok) break;
+        if (is_odd) {
+            PyObject *idx = PyLong_FromSsize_t(j);
+            if (!idx || PyList_Append(odd, idx) < 0) { Py_XDECREF(idx); ok = 0; break; }
+            Py_DECREF(idx);
+        }
+        if (buf_put(&begin, &rows, 8) < 0) ok = 0;
+    }
+    if (ok) {
+        result = Py_BuildValue("(NNNNNO)", PyByteArray_FromStringAndSize(begin.p, begin.len),
+                               PyByteArray_FromStringAndSize(ct.p ? ct.p : "", ct.len), PyByteArray_FromStringAndSize(co.p, co.len),
+                               PyByteArray_FromStringAndSize(mt.p ? mt.p : "", mt.len), PyByteArray_FromStringAndSize(mo.p, mo.len), odd);
+    }
+    PyMem_Free(begin.p); PyMem_Free(ct.p); PyMem_Free(co.p); PyMem_Free(mt.p); PyMem_Free(mo.p);
+    Py_XDECREF(odd);
+    Py_DECREF(seq);
+    return result;
+}
+
 static PyMethodDef methods[] = {
     {"node_metrics_to_columns", node_metrics_to_columns, METH_VARARGS, "NodeMetrics list -> node table columns"},
     {"pod_specs_to_columns", pod_specs_to_columns, METH_VARARGS, "PodSpec list -> pod table columns"},
+    {"pack_pod_requests", pack_pod_requests, METH_O, "per-pod container requests -> CSR + packed quantity strings"},
     {NULL, NULL, 0, NULL}};
 
 static struct PyModuleDef module = {PyModuleDef_HEAD_INIT, "_kp_pyobj", "record lists -> wire columns", -1, methods};

@@ -20,7 +20,7 @@ import torch
 
 from . import _lib
 from ._lib import ROW_CPU_INEXACT, ROW_HOST, ROW_MEM_INEXACT, KpNodeStrings, KpPodRequestStrings, check
-from .tables import (WIRE_LIMIT, NodeTable, PodTable, cores_to_milli, gib_to_bytes, is_ready, parse_cpu,
+from .tables import (WIRE_LIMIT, NodeTable, PodTable, _record_walker, cores_to_milli, gib_to_bytes, is_ready, parse_cpu,
                      parse_memory, pod_requests, usage_percent)
 
 
@@ -107,15 +107,28 @@ def _round_inexact(status, flag, values, scale, wire, scalar_fn, exact) -> None:
     wire[rows] = np.rint(scaled).astype(np.int64)
 
 
+def pack_pod_requests(pods: Sequence[Sequence[Optional[Dict[str, Any]]]]):
+    """``flatten_pod_requests`` + ``pack_strings`` -> (begin, cpu_text, cpu_off, mem_text, mem_off, odd).
+    One pass in C when the record walker is built (csrc/kp_pyobj.c), else the Python functions above."""
+    walker = _record_walker()
+    if walker is not None and type(pods) in (list, tuple):
+        b, ct, co, mt, mo, odd = walker.pack_pod_requests(pods)
+        u8 = lambda x: np.frombuffer(x, dtype=np.uint8)      # noqa: E731
+        i64 = lambda x: np.frombuffer(x, dtype=np.int64)     # noqa: E731
+        return i64(b), u8(ct), i64(co), u8(mt), i64(mo), odd
+    begin, cpu, mem, odd = flatten_pod_requests(pods)
+    cpu_text, cpu_off = pack_strings(cpu)
+    mem_text, mem_off = pack_strings(mem)
+    return begin, cpu_text, cpu_off, mem_text, mem_off, odd
+
+
 def ingest_pod_requests(pods: Sequence[Sequence[Optional[Dict[str, Any]]]], device="cuda:0",
                         exact: bool = True, strategy_ids=None, redo: bool = True) -> PodIngest:
     """GPU form of ``PodTable.from_container_requests`` (same inputs, same table, same errors).
     ``redo=False`` returns the raw device results (flagged rows left as the device wrote them)."""
     lib = _lib.load()
     n = len(pods)
-    begin, cpu, mem, odd = flatten_pod_requests(pods)
-    cpu_text, cpu_off = pack_strings(cpu)
-    mem_text, mem_off = pack_strings(mem)
+    begin, cpu_text, cpu_off, mem_text, mem_off, odd = pack_pod_requests(pods)
     dev = torch.device(device)
     d = [_dev(a, dev) for a in (begin, cpu_text, cpu_off, mem_text, mem_off)]
     out_milli = torch.empty(n, dtype=torch.int64, device=dev)

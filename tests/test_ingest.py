@@ -96,3 +96,25 @@ def test_inexact_rows_are_rounded_or_refused_like_the_host_tables():
     w = np.array([-1], dtype=np.int64)
     _round_inexact(np.array([1], dtype=np.uint8), 1, only_zero, 1000.0, w, tables.cores_to_milli, exact=True)
     assert w.tolist() == [0]                                        # -0.0 == 0: fine for tables.py, fine here
+
+
+def test_c_packer_equals_the_python_packer():
+    """csrc/kp_pyobj.c pack_pod_requests == flatten_pod_requests + pack_strings (non-ASCII, missing keys,
+    containers without requests, non-string quantities)."""
+    from k8s_llm_scheduler_b200 import tables as T
+    from k8s_llm_scheduler_b200.build import build_pyobj
+    from k8s_llm_scheduler_b200.ingest import flatten_pod_requests, pack_pod_requests, pack_strings
+    build_pyobj()
+    T._WALKER[0] = False
+    assert T._record_walker() is not None
+    pods = [rec["containers"] for rec in GOLD["pods"]] + [[{"cpu": "٣", "memory": "1Gi"}], [], [None, {}], [{"memory": 5}]]
+    begin, ct, co, mt, mo, odd = pack_pod_requests(pods)
+    b2, cpu, mem, odd2 = flatten_pod_requests(pods)
+    (ct2, co2), (mt2, mo2) = pack_strings(cpu), pack_strings(mem)
+    assert np.array_equal(begin, b2) and odd == odd2
+    assert len(co) == len(co2) == len(mo) == len(mo2) == int(begin[-1]) + 1
+    clean = [j for j in range(len(pods)) if j not in set(odd)]          # odd pods carry placeholders on both sides
+    for j in clean:
+        for c in range(int(begin[j]), int(begin[j + 1])):
+            assert bytes(ct[co[c]:co[c + 1]]) == bytes(ct2[co2[c]:co2[c + 1]])
+            assert bytes(mt[mo[c]:mo[c + 1]]) == bytes(mt2[mo2[c]:mo2[c + 1]])
