@@ -557,8 +557,7 @@ def run_ingest_extra(torch, lib, dev, n_pods=1_000_000, cpu_sample=40_000):
     it = iter(zip(cm.tolist(), mm.tolist()))
     pods = [[{"cpu": f"{c}m", "memory": f"{m}Mi"} for c, m in (next(it) for _ in range(kk))] for kk in k.tolist()]
     t0 = time.perf_counter()
-    begin, cpu, mem, _ = ingest.flatten_pod_requests(pods)
-    (ct, co), (mt, mo) = ingest.pack_strings(cpu), ingest.pack_strings(mem)
+    begin, ct, co, mt, mo, _ = ingest.pack_pod_requests(pods)          # the packer the product path uses
     pack_s = time.perf_counter() - t0
     d = [torch.from_numpy(a).to(dev) for a in (begin, ct, co, mt, mo)]
     outs = [torch.empty(n_pods, dtype=dt, device=dev) for dt in (torch.int64, torch.int64, torch.float64, torch.float64, torch.uint8)]
