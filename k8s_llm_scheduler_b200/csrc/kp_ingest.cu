@@ -34,23 +34,35 @@ __device__ bool parse_decimal(const uint8_t *s, int len, double *out)
         neg = s[0] == '-';
         i = 1;
     }
-    unsigned long long d = 0;
+    // the first nine digits cannot overflow 32 bits: one IMAD per character, no range check;
+    // anything longer continues in 64 bits with the 2^53 check
+    unsigned d32 = 0;
     int ndig = 0, frac = 0;
-    bool seen_point = false;
+    unsigned bad = 0, points = 0;
+    for (; i < len && ndig < 9; ++i) {
+        const unsigned c = s[i];
+        const unsigned v = c - '0';
+        const unsigned isd = v <= 9u, isp = c == '.';
+        bad |= (isd | isp) ^ 1u;
+        points += isp;
+        frac += (int)(isd & (points != 0u));
+        ndig += (int)isd;
+        d32 = isd ? d32 * 10u + v : d32;
+    }
+    unsigned long long d = d32;
     for (; i < len; ++i) {
         const unsigned c = s[i];
         if (c == '.') {
-            if (seen_point) return false;
-            seen_point = true;
+            ++points;
             continue;
         }
         const unsigned v = c - '0';
-        if (v > 9u) return false;
-        if (d >= kMaxMantissa / 10) return false;          // next digit could pass 2^53
+        if (v > 9u || d >= kMaxMantissa / 10) return false;  // not a digit, or the next digit could pass 2^53
         d = d * 10 + v;
         ++ndig;
-        if (seen_point) ++frac;
+        frac += points != 0u;
     }
+    if (bad | (points > 1u)) return false;
     if (ndig == 0 || frac > 22) return false;
     const double mag = frac ? __ddiv_rn((double)d, c_pow10[frac]) : (double)d;
     *out = neg ? -mag : mag;
