@@ -209,7 +209,9 @@ place_kernel(const PlaceParams p)
     const int tile_nodes = swar ? kTileNodesPacked : kTileNodesWide;
     const int elem = swar ? 4 : 8;
     const int tiles_per_seg = swar ? (p.tiles_per_seg_wide + 1) / 2 : p.tiles_per_seg_wide;
-    const int ntiles_all = (nvalid4 + tile_nodes - 1) / tile_nodes;
+    const int tile_shift = swar ? 10 : 9;                            // log2(tile_nodes): a shift, not a run-time division
+    static_assert(kTileNodesPacked == 1 << 10 && kTileNodesWide == 1 << 9, "tile sizes are powers of two");
+    const int ntiles_all = (nvalid4 + tile_nodes - 1) >> tile_shift;
     const int t_lo = min(ntiles_all, (int)blockIdx.y * tiles_per_seg);          // this CTA's tiles [t_lo, t_hi)
     const int t_hi = min(ntiles_all, t_lo + tiles_per_seg);
     const unsigned char *table = swar ? reinterpret_cast<const unsigned char *>(p.packed + (size_t)s * p.npad)
