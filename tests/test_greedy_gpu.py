@@ -212,3 +212,12 @@ def test_full_size_config3_greedy():
     o = oracle_greedy(nodes, head, 0, 1)
     assert_same_idx(idx[:30_000], o[0])
     assert_same_f64(score[:30_000], o[1])
+
+
+def test_tables_beyond_the_fast_path_capacity_use_the_fp64_kernel():
+    """More nodes than eight CTAs hold in registers (163 840; 81 920 with per-pod strategies)."""
+    nodes, pods = synth.config5(170_000, 2100, seed=38)
+    _check_greedy(nodes, pods, 0, 1, what="170k uniform")
+    nodes, pods = synth.config5(90_000, 2100, seed=39)
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="90k per-pod")
+    _check_greedy(nodes, pods, 1, 1, what="90k uniform (cluster of 8)")
