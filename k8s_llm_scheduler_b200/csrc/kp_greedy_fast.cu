@@ -335,6 +335,18 @@ __device__ __forceinline__ void fast_summary(const uint32_t (&w)[NPT], const uin
     kbest = b;
 }
 
+// one 32-bit word into CTA `target` of this cluster at the address `slot` has in the calling CTA, completing
+// 4 bytes of the transaction count of the mbarrier at `bar` in the SAME target CTA
+__device__ __forceinline__ void dsmem_send_u32(uint32_t slot, uint32_t bar, uint32_t target, uint32_t value)
+{
+    uint32_t rslot, rbar;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot) : "r"(slot), "r"(target));
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(bar), "r"(target));
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(rslot), "r"(value),
+                 "r"(rbar)
+                 : "memory");
+}
+
 template <int NPT, bool MULTI, int CSIZE>
 __global__ void __launch_bounds__(kFastThreads, 1)
 fast_greedy_kernel(FastIn in, FastRun r)
@@ -344,6 +356,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
     __shared__ uint8_t s_sid[kFastPodBatch + 4];
     __shared__ uint32_t w_res[2][32];
     __shared__ uint32_t c_res[2][8];                                   // best key of every CTA of the cluster
+    __shared__ __align__(8) uint64_t xbar[2];                          // mbarriers of the per-pod exchange
     __shared__ uint32_t s_tbase[kFastMaxShapes + 1];
 
     if (!r.hdr->ok) return;                                          // the fp64 kernel does the work instead
@@ -391,8 +404,14 @@ fast_greedy_kernel(FastIn in, FastRun r)
     }
     uint32_t wmin = 0u, kbest = 0u;                                    // uniform strategy only (one key per node)
     if (!MULTI) fast_summary<NPT>(w, key[0], wmin, kbest);
+    if (CLUSTER && tid == 0) {
+        mbar_init(&xbar[0], 1);
+        mbar_init(&xbar[1], 1);
+        mbar_fence_init();
+    }
+    uint32_t round = 0;
     __syncthreads();
-    if (CLUSTER) cluster_barrier();                                    // every CTA of the cluster is running before any peer stores into it
+    if (CLUSTER) cluster_barrier();                                    // every CTA's mbarriers exist before any peer signals them
 
     for (long long base = 0; base < in.n_pods; base += kFastPodBatch) {
         const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
@@ -421,16 +440,23 @@ fast_greedy_kernel(FastIn in, FastRun r)
             __syncthreads();
             best = __reduce_max_sync(0xffffffffu, lane < NW ? w_res[par][lane] : 0u);
             if (CLUSTER) {
-                // every CTA stores its best key into slot [crank] of every CTA's shared memory (DSMEM); the
-                // cluster barrier (release / acquire at cluster scope, no device-wide fence) completes the
-                // exchange.  Measured alternative, dropped: tagging the stored word with the pod number and
-                // spinning on the local slots instead of the barrier was 1.6x slower.
-                if (tid < CSIZE) *cluster.map_shared_rank(&c_res[par][crank], tid) = best;
-                cluster_barrier();
-                uint32_t g = 0u;
+                // Exchange through DSMEM without a cluster barrier: every CTA sends its best key to every
+                // peer with st.async, which writes the word into the peer's slot AND signals the peer's
+                // mbarrier (complete_tx); each CTA then waits on its OWN mbarrier only.  A cluster barrier
+                // here (even release / acquire at cluster scope) cost ~0.5 us per pod in ERRBAR + barrier
+                // latency -- 40 % of the kernel; tagging plain stores and spinning was slower still.
+                // Slots and mbarriers alternate by round parity: a CTA can be at most one round ahead of a
+                // peer, because round r + 1 needs the peer's word of round r + 1.
+                const int xp = (int)(round & 1u);
+                if (tid == 0) mbar_expect_tx(&xbar[xp], 4u * (CSIZE - 1));
+                if (tid < CSIZE && tid != crank)
+                    dsmem_send_u32(smem_u32(&c_res[xp][crank]), smem_u32(&xbar[xp]), (uint32_t)tid, best);
+                mbar_wait(&xbar[xp], (round >> 1) & 1u);
+                uint32_t g = best;
 #pragma unroll
-                for (int c = 0; c < CSIZE; ++c) g = max(g, c_res[par][c]);
+                for (int c = 0; c < CSIZE; ++c) if (c != crank) g = max(g, c_res[xp][c]);
                 best = g;
+                ++round;
             }
             x = x_next;
             s = s_next;

@@ -1,4 +1,4 @@
-"""One greedy placement for profiling: python tools/greedy_one.py [c3|c5] [n_pods] (GPU box)."""
+"""One greedy placement for profiling: python tools/greedy_one.py [c3|c5|c5u] [n_pods] (GPU box)."""
 import sys
 import time
 from pathlib import Path
@@ -12,6 +12,9 @@ p = int(sys.argv[2]) if len(sys.argv) > 2 else 100_000
 if kind == "c5":
     nodes, pods = synth.config5(20_000, p)
     strat = torch.as_tensor(pods.strategy_ids).cuda()
+elif kind == "c5u":                       # config-5 nodes and pods, one strategy for all pods
+    nodes, pods = synth.config5(20_000, p)
+    strat = 0
 else:
     nodes, pods = synth.config3(5000, p)
     strat = 0
