@@ -49,16 +49,17 @@ class FallbackPlacer:
             return self.decision_cls("", 0.0, "No nodes available", True)
         strategy = self.strategy()
         try:
-            table = NodeTable.from_node_metrics(node_metrics, exact=False)   # Ready-only filter
+            # Ready-only filter: available_cpu / available_memory are dead inputs (the reference never reads
+            # them, scheduler.py:531-549) and are not even looked at
+            table = NodeTable.from_node_metrics(node_metrics, ready_only=True)
             idx, _ = self.session.snapshot(table, self._one_pod, strategy_id(strategy), FILTER_READY, out=self._one_out)
             i = int(idx[0])
-        except PlacementError as e:        # never raise into the scheduling loop
+            if i >= 0:                                              # scheduler.py:551-557
+                return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
+                                         reasoning=f"Fallback ({strategy}): {reason}",
+                                         fallback_needed=True)
+        except Exception as e:  # noqa: BLE001 -- never raise into the scheduling loop
             logger.error("GPU fallback placement failed: %s", e)
-            i = -1
-        if i >= 0:                                                  # scheduler.py:551-557
-            return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
-                                     reasoning=f"Fallback ({strategy}): {reason}",
-                                     fallback_needed=True)
         return self.decision_cls("", 0.0, f"Fallback failed: {reason}", True)   # :558-559
 
     # ---- extension: the same decision with the capacity filter for a given pod ----
@@ -71,13 +72,12 @@ class FallbackPlacer:
             pods = PodTable.from_pod_specs([pod_spec])
             idx, _ = self.session.snapshot(table, pods, strategy_id(strategy), FILTER_CAPACITY)
             i = int(idx[0])
-        except PlacementError as e:
+            if i >= 0:
+                return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
+                                         reasoning=f"Fallback ({strategy}): {reason}",
+                                         fallback_needed=True)
+        except Exception as e:  # noqa: BLE001 -- same contract as fallback_decision
             logger.error("GPU fallback placement failed: %s", e)
-            i = -1
-        if i >= 0:
-            return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
-                                     reasoning=f"Fallback ({strategy}): {reason}",
-                                     fallback_needed=True)
         return self.decision_cls("", 0.0, f"Fallback failed: {reason}", True)
 
     # ---- batched forms over reference-style records ----

@@ -207,6 +207,26 @@ int upload_pods(kp_session *s, const kp_pod_table *pods, kp_pod_table *dview)
     return KP_OK;
 }
 
+int check_session_sizes(const kp_session *s, const kp_node_table *nodes, const kp_pod_table *pods)
+{
+    if (nodes && nodes->n_nodes > s->max_nodes) {
+        set_error("session holds at most %lld nodes, got %lld", (long long)s->max_nodes, (long long)nodes->n_nodes);
+        return KP_ERR_CAPACITY;
+    }
+    if (pods->n_pods > s->max_pods) {
+        set_error("session holds at most %lld pods, got %lld", (long long)s->max_pods, (long long)pods->n_pods);
+        return KP_ERR_CAPACITY;
+    }
+    return KP_OK;
+}
+
+// error return after work was enqueued: drain the stream first (the staging buffer is reused by the next call)
+int fail_drained(kp_session *s, int st)
+{
+    cudaStreamSynchronize(s->stream);
+    return st;
+}
+
 }  // namespace
 
 extern "C" {
@@ -462,6 +482,9 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     if ((st = check_filter(filter_mode)) != KP_OK) return st;
     DeviceGuard guard(s->device);
     s->h2d = s->d2h = 0;
+    // sizes are checked before anything is enqueued: the node upload is an async copy out of the
+    // session's one pinned staging buffer, and an early return must not leave it in flight
+    if ((st = check_session_sizes(s, nodes, pods)) != KP_OK) return st;
     if (nodes) {
         if ((st = check_tables(nodes, pods)) != KP_OK) return st;
         if ((st = upload_nodes(s, nodes)) != KP_OK) return st;
@@ -470,8 +493,8 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
         return KP_ERR_INVALID_ARG;
     }
     const kp_node_table dn = session_node_view(s, s->resident_nodes);
-    if ((st = check_tables(&dn, pods)) != KP_OK) return st;
-    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return KP_ERR_INVALID_ARG; }
+    if ((st = check_tables(&dn, pods)) != KP_OK) return fail_drained(s, st);
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return fail_drained(s, KP_ERR_INVALID_ARG); }
     const size_t pcol = align_up(sizeof(int64_t) * (size_t)s->max_pods);
     const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
     int64_t *d_idx = reinterpret_cast<int64_t *>(s->d_out);
@@ -503,14 +526,14 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
             out_in_place = true;
         }
     }
-    if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return st;
+    if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return fail_drained(s, st);
     PlaceTuning tuning;
     if (in_place) {
         tuning.flow = s->d_flow;
         tuning.flow_window = kFlowWindowCtas;
     }
     st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream, tuning);
-    if (st != KP_OK) return st;
+    if (st != KP_OK) return fail_drained(s, st);
     if (b8) {
         if (!out_in_place) {
             KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
@@ -531,6 +554,9 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
     if ((st = check_filter(filter_mode)) != KP_OK) return st;
     DeviceGuard guard(s->device);
     s->h2d = s->d2h = 0;
+    // sizes are checked before anything is enqueued: the node upload is an async copy out of the
+    // session's one pinned staging buffer, and an early return must not leave it in flight
+    if ((st = check_session_sizes(s, nodes, pods)) != KP_OK) return st;
     if (nodes) {
         if ((st = check_tables(nodes, pods)) != KP_OK) return st;
         if ((st = upload_nodes(s, nodes)) != KP_OK) return st;
@@ -540,10 +566,10 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
     }
     const int64_t n = s->resident_nodes;
     const kp_node_table dn = session_node_view(s, n);
-    if ((st = check_tables(&dn, pods)) != KP_OK) return st;
-    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return KP_ERR_INVALID_ARG; }
+    if ((st = check_tables(&dn, pods)) != KP_OK) return fail_drained(s, st);
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) { set_error("output pointer is NULL"); return fail_drained(s, KP_ERR_INVALID_ARG); }
     kp_pod_table dp{};
-    if ((st = upload_pods(s, pods, &dp)) != KP_OK) return st;
+    if ((st = upload_pods(s, pods, &dp)) != KP_OK) return fail_drained(s, st);
     const size_t pcol = align_up(sizeof(int64_t) * (size_t)s->max_pods);
     const size_t ncol = align_up(sizeof(int64_t) * (size_t)s->max_nodes);
     int64_t *d_idx = reinterpret_cast<int64_t *>(s->d_out);
@@ -553,7 +579,7 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
     double *d_mu = reinterpret_cast<double *>(s->d_state + 2 * ncol);
     st = greedy_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, d_pc, d_cu, d_mu, s->d_ws,
                              s->ws_bytes, s->stream);
-    if (st != KP_OK) return st;
+    if (st != KP_OK) return fail_drained(s, st);
     const size_t b8 = sizeof(int64_t) * (size_t)pods->n_pods;
     const size_t n8 = sizeof(int64_t) * (size_t)n;
     if (b8) {

@@ -203,7 +203,7 @@ void count_launch(int n = 1);
 // Launch options of the placement kernel that only the host-buffer session uses.
 struct PlaceTuning {
     int resident_cap = 0;          // > 0: at most this many CTAs resident per SM
-    unsigned *flow = nullptr;      // two zeroed device words: pace the in-place reads of pinned pod rows
+    unsigned *flow = nullptr;      // three zeroed device words (arrived, finished, spare flag): pace the in-place reads of pinned pod rows
     unsigned flow_window = 0;      // CTAs whose rows may be in flight at once
 };
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
@@ -236,6 +236,15 @@ int ingest_nodes_device(const kp_node_strings &in, int64_t *out_milli, int64_t *
 int cache_keys_device(const uint8_t *prefix, const int64_t *prefix_off, int64_t n_pods, const uint8_t *nodes_text,
                       int64_t nodes_len, uint8_t *out, cudaStream_t stream);
 int sm_count_cached();
+// Ordinal of the current device, clamped to [0, kMaxDevices): index of per-device once-flags.  Function
+// attributes (opt-in shared memory sizes) belong to a device's context, so such flags are kept per device.
+constexpr int kMaxDevices = 64;
+inline int device_slot()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = 0;
+    return dev;
+}
 // kp_sort.cu: library radix sort / scan for the large-table plan (temp storage from the workspace)
 size_t sort_temp_bytes(int64_t n);
 int sort_pairs_u64(void *temp, size_t temp_bytes, const unsigned long long *keys_in, unsigned long long *keys_out,

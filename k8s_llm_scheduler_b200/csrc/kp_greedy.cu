@@ -20,8 +20,9 @@
 // exact-fp64 operation sequence as the snapshot path (cu == mu after a commit, so the shared
 // sub-expression 100 - usage is computed once; the dependent chain is two divisions deep).
 // Usage outputs are derived once at the end from the final pod counts.  Tables beyond the
-// register budget use the same kernel with the hot state in global memory (slower; a
-// thread-block-cluster version is the planned replacement).
+// register budget use the same kernel with the hot state in global memory (slower).  This
+// kernel is the fallback: kp_greedy_fast.cu (integer state machine, thread-block clusters for
+// large tables) runs first and this one returns at once when that path did the work.
 #include <algorithm>
 
 #include "kp_common.cuh"
@@ -315,11 +316,12 @@ static int launch_greedy(const GreedyParams &g, cudaStream_t stream)
 {
     if (g.n_nodes <= kGreedySmemNodes) {
         const size_t smem = (size_t)kGreedyColdBytes * g.n_nodes;
-        static size_t attr_bytes = 0;
-        if (smem > attr_bytes) {
+        static bool attr_set[kMaxDevices] = {false};                 // the opt-in is per device
+        const int dev = device_slot();
+        if (!attr_set[dev]) {
             KP_CUDA(cudaFuncSetAttribute(greedy_kernel<NPT, MULTI, true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kGreedyColdBytes * kGreedySmemNodes));
-            attr_bytes = (size_t)kGreedyColdBytes * kGreedySmemNodes;
+            attr_set[dev] = true;
         }
         greedy_kernel<NPT, MULTI, true><<<1, kGreedyThreads, smem, stream>>>(g);
     } else {

@@ -18,8 +18,9 @@
 //  * A node's hot state is therefore two registers; the per-pod block arg-max is one REDUX.MAX
 //    per warp, one barrier, one more REDUX.MAX; the winner's index is read back out of the key.
 //  * Tables that exceed one CTA's registers run on a thread-block CLUSTER (2, 4 or 8 CTAs):
-//    per pod each CTA stores its best key into every peer's shared memory (DSMEM) and a
-//    cluster barrier completes the exchange.
+//    per pod each CTA sends its best key to every peer with st.async (the word lands in the
+//    peer's shared memory and completes a transaction on the peer's mbarrier) and then waits
+//    on its own mbarrier only -- no cluster barrier on the per-pod path.
 //
 // Whether the preconditions hold is decided on the device (ok flag); the fp64 kernel is always
 // launched behind this path and returns at once when the flag says the work is done.
@@ -80,6 +81,9 @@ fast_shapes_kernel(FastIn in, FastHeader *hdr, uint32_t *__restrict__ shape_id)
             const long long pc = in.pod_count0[n];
             want = in.ready[n] != 0 && mp > 0 && pc < mp;            // otherwise never chosen, never committed
             if (want && (pc < 0 || mp >= (1ll << 24))) bad_value = true;
+            // choosable under the entries' rule (ready && pc < mp) but without a trajectory: max_pods <= 0 with
+            // a negative pod count.  Such a table goes to the fp64 kernel.
+            if (in.ready[n] != 0 && pc < mp && mp <= 0) bad_value = true;
         }
         int found = -1;
         for (;;) {
@@ -612,11 +616,12 @@ size_t greedy_fast_workspace_bytes(int64_t n, int64_t p)
 template <int NPT, bool MULTI, int CSIZE>
 static int launch_fast(const FastIn &in, const FastRun &r, size_t smem, cudaStream_t stream)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {false};                     // the opt-in is per device
+    const int dev = device_slot();
+    if (!attr_set[dev]) {
         KP_CUDA(cudaFuncSetAttribute(fast_greedy_kernel<NPT, MULTI, CSIZE>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(CSIZE, 1, 1);

@@ -135,12 +135,16 @@ static int writable(PyObject *obj, Py_buffer *view, Py_ssize_t itemsize, Py_ssiz
     return 0;
 }
 
-/* node_metrics_to_columns(nodes, cpu_milli, mem_bytes, pod_count, max_pods, ready, cpu_usage, mem_usage, exact) */
+/* node_metrics_to_columns(nodes, cpu_milli, mem_bytes, pod_count, max_pods, ready, cpu_usage, mem_usage, mode)
+ * mode 0: allocatable rounded to the nearest wire integer, 1: must be exact, 2: allocatable columns not read at all
+ * (zeros) -- the reference's own decision (scheduler.py:531-549) never looks at available_cpu / available_memory,
+ * so under the Ready-only filter whatever they hold (inf, nan, 1e300, ...) must not matter. */
 static PyObject *node_metrics_to_columns(PyObject *self, PyObject *args)
 {
     PyObject *nodes, *o[7];
-    int exact;
-    if (!PyArg_ParseTuple(args, "OOOOOOOOp", &nodes, &o[0], &o[1], &o[2], &o[3], &o[4], &o[5], &o[6], &exact)) return NULL;
+    int mode;
+    if (!PyArg_ParseTuple(args, "OOOOOOOOi", &nodes, &o[0], &o[1], &o[2], &o[3], &o[4], &o[5], &o[6], &mode)) return NULL;
+    const int exact = mode == 1, skip_alloc = mode == 2;
     PyObject *seq = PySequence_Fast(nodes, "node_metrics must be a sequence");
     if (!seq) return NULL;
     const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
@@ -158,9 +162,10 @@ static PyObject *node_metrics_to_columns(PyObject *self, PyObject *args)
         for (Py_ssize_t i = 0; i < n && ok; ++i) {
             PyObject *nd = items[i];
             double cores, gib;
-            if (get_double(nd, s_available_cpu, &cores) < 0 || get_double(nd, s_available_memory, &gib) < 0 ||
-                cores_to_milli(cores, exact, &milli[i]) < 0 || gib_to_bytes(gib, exact, &bytes[i]) < 0 ||
-                get_int64(nd, s_pod_count, &pc[i]) < 0 || get_int64(nd, s_max_pods, &mp[i]) < 0 ||
+            if (skip_alloc) milli[i] = bytes[i] = 0;
+            else if (get_double(nd, s_available_cpu, &cores) < 0 || get_double(nd, s_available_memory, &gib) < 0 ||
+                     cores_to_milli(cores, exact, &milli[i]) < 0 || gib_to_bytes(gib, exact, &bytes[i]) < 0) { ok = 0; break; }
+            if (get_int64(nd, s_pod_count, &pc[i]) < 0 || get_int64(nd, s_max_pods, &mp[i]) < 0 ||
                 get_double(nd, s_cpu_usage, &cu[i]) < 0 || get_double(nd, s_mem_usage, &mu[i]) < 0) { ok = 0; break; }
             PyObject *conds = PyObject_GetAttr(nd, s_conditions);
             if (!conds) { ok = 0; break; }

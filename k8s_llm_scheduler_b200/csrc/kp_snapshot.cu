@@ -365,7 +365,7 @@ constexpr int kFallbackCfg = 4;          // few pods: 128 pods per CTA, 8 warps 
 template <int THREADS, int R, int NSPLIT>
 static int place_occupancy()
 {
-    static int occ = 0;
+    static int occ = 0;                                             // same on every device this library runs on (sm_100)
     if (occ == 0) {
         int v = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, place_kernel<THREADS, R, NSPLIT>, THREADS, 0) != cudaSuccess || v <= 0)
@@ -394,8 +394,9 @@ static int cfg_occupancy(int c)
 template <int THREADS, int R, int NSPLIT>
 static cudaError_t launch_place_pdl(const PlaceParams &pp, dim3 grid, cudaStream_t stream, int resident_cap)
 {
-    static size_t static_smem = 0;
-    static size_t max_dyn_set = 0;
+    static size_t static_smem = 0;                                  // a property of the kernel image
+    static size_t max_dyn_set_dev[kMaxDevices] = {0};               // the opt-in is per device
+    size_t &max_dyn_set = max_dyn_set_dev[device_slot()];
     size_t dyn = 0;
     if (resident_cap > 0) {
         if (static_smem == 0) {

@@ -253,31 +253,34 @@ class Session:
         if all(type(t) is torch.Tensor and t is k for t, k in zip(tensors, keep)):
             self._memo[slot] = (owner, [(t, t.data_ptr(), t.numel()) for t in tensors], value)
 
+    # Both helpers return (struct, keep): `keep` holds whatever arrays the struct points into --
+    # including temporaries made by _host_ptr when an input needed a dtype / layout conversion --
+    # and the caller keeps it alive until the C call has returned.
     def _node_struct_memo(self, nodes):
         if type(nodes) is not dict:
-            return self._node_struct(nodes)[0]
+            return self._node_struct(nodes)
         tensors = [nodes[k] for k in NODE_COLUMNS]
-        st = self._memo_get("nodes", nodes, tensors)
-        if st is None:
-            st, keep = self._node_struct(nodes)
-            self._memo_put("nodes", nodes, tensors, keep, st)
-        return st
+        hit = self._memo_get("nodes", nodes, tensors)
+        if hit is None:
+            hit = self._node_struct(nodes)
+            self._memo_put("nodes", nodes, tensors, hit[1], hit)
+        return hit
 
     def _pod_struct_memo(self, pods):
         if type(pods) is not tuple:
-            return self._pod_struct(pods)[0]
+            return self._pod_struct(pods)
         tensors = [t for t in pods if t is not None]
-        st = self._memo_get("pods", pods, tensors)
-        if st is None:
-            st, keep = self._pod_struct(pods)
-            self._memo_put("pods", pods, tensors, keep, st)
-        return st
+        hit = self._memo_get("pods", pods, tensors)
+        if hit is None:
+            hit = self._pod_struct(pods)
+            self._memo_put("pods", pods, tensors, hit[1], hit)
+        return hit
 
     def snapshot(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY, out=None):
         """nodes=None reuses the table kept by set_nodes().  Returns (idx, score) numpy arrays,
         or fills ``out`` = (idx, score) host buffers (numpy or pinned torch)."""
-        nst = self._node_struct_memo(nodes) if nodes is not None else None
-        pst = self._pod_struct_memo(pods)
+        nst, _keep_nodes = self._node_struct_memo(nodes) if nodes is not None else (None, None)
+        pst, _keep_pods = self._pod_struct_memo(pods)
         p = pst.n_pods
         if out is None:
             out = (np.empty(p, np.int64), np.empty(p, np.float64))

@@ -182,9 +182,11 @@ class NodeTable:
                    list(names) if names is not None else None)
 
     @classmethod
-    def from_node_metrics(cls, nodes: Sequence[Any], exact: bool = True) -> "NodeTable":
+    def from_node_metrics(cls, nodes: Sequence[Any], exact: bool = True, ready_only: bool = False) -> "NodeTable":
         """From a list of reference-style NodeMetrics records (duck-typed: the reference's
-        own dataclass instances work)."""
+        own dataclass instances work).  ``ready_only``: the table is for the Ready-only filter, i.e. the
+        reference's own decision (scheduler.py:531-549), which never reads available_cpu / available_memory:
+        those fields are then not read either (zeros), whatever they hold."""
         n = len(nodes)
         t = cls(np.empty(n, np.int64), np.empty(n, np.int64), np.empty(n, np.int64),
                 np.empty(n, np.int64), np.empty(n, np.uint8), np.empty(n, np.float64),
@@ -192,12 +194,12 @@ class NodeTable:
         walker = _record_walker()
         if walker is not None:               # same conversions and checks, in C (csrc/kp_pyobj.c)
             walker.node_metrics_to_columns(nodes, t.alloc_cpu_milli, t.alloc_mem_bytes, t.pod_count, t.max_pods,
-                                           t.ready, t.cpu_usage_pct, t.mem_usage_pct, exact)
+                                           t.ready, t.cpu_usage_pct, t.mem_usage_pct, 2 if ready_only else int(bool(exact)))
             t.names = [nd.name for nd in nodes]
             return t
         for i, nd in enumerate(nodes):
-            t.alloc_cpu_milli[i] = cores_to_milli(nd.available_cpu, exact)
-            t.alloc_mem_bytes[i] = gib_to_bytes(nd.available_memory, exact)
+            t.alloc_cpu_milli[i] = 0 if ready_only else cores_to_milli(nd.available_cpu, exact)
+            t.alloc_mem_bytes[i] = 0 if ready_only else gib_to_bytes(nd.available_memory, exact)
             t.pod_count[i] = nd.pod_count
             t.max_pods[i] = nd.max_pods
             t.ready[i] = 1 if is_ready(nd.conditions) else 0

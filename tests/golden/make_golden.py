@@ -203,13 +203,15 @@ def gen_decisions(sched, tap):
             out[s] = {"idx": idx, "score_bits": f64_bits(tap.best_score),
                       "confidence": dec.confidence, "reasoning": dec.reasoning,
                       "fallback_needed": dec.fallback_needed}
-        cases.append({"tag": tag,
-                      "nodes": [{"pc": sp[0], "mp": sp[1],
-                                 "cu_bits": f64_bits(n.cpu_usage_percent),
-                                 "mu_bits": f64_bits(n.memory_usage_percent),
-                                 "cond": sp[4] if len(sp) > 4 else "ready"}
-                                for sp, n in zip(spec, nodes)],
-                      "expect": out})
+        rows = []
+        for sp, n in zip(spec, nodes):
+            row = {"pc": sp[0], "mp": sp[1], "cu_bits": f64_bits(n.cpu_usage_percent),
+                   "mu_bits": f64_bits(n.memory_usage_percent), "cond": sp[4] if len(sp) > 4 else "ready"}
+            if len(sp) > 5:                     # allocatable fields the decision never reads (scheduler.py:531-549)
+                row["avail_cpu_bits"] = f64_bits(n.available_cpu)
+                row["avail_mem_bits"] = f64_bits(n.available_memory)
+            rows.append(row)
+        cases.append({"tag": tag, "nodes": rows, "expect": out})
 
     # behavioural known answers from SURVEY.md §8(c)
     record("kat-10-5-5", [(10, 110), (5, 110), (5, 110)])
@@ -248,6 +250,15 @@ def gen_decisions(sched, tap):
                 mu = float(np.round(rng.uniform(0, 120), 3))
             spec.append((pc, mp, cu, mu, cond))
         record(f"rand-{c}", spec)
+    # inputs the reference accepts because it never reads them (available_cpu / available_memory) or
+    # because plain float arithmetic copes (inf / nan / huge / negative usage)
+    inf, nan = float("inf"), float("nan")
+    record("odd-alloc", [(10, 110, None, None, "ready", inf, nan), (5, 110, None, None, "ready", 1e300, -4.0),
+                         (5, 110, None, None, "ready", nan, inf), (7, 110, None, None, "ready", -inf, 2.0 ** 60)])
+    record("odd-alloc-notready", [(1, 110, None, None, "false", nan, nan), (3, 110, None, None, "ready", -1e300, 1e300)])
+    record("odd-usage", [(10, 110, inf, 3.0), (5, 110, nan, nan), (6, 110, -5.0, -7.5), (4, 110, 1e300, 0.0),
+                         (9, 110, 20.0, 20.0), (8, 110, -inf, 1.0)])
+    record("odd-usage-only", [(10, 110, nan, 3.0), (5, 110, 3.0, nan), (2, 110, inf, inf)])
     return cases
 
 

@@ -21,8 +21,12 @@ def placer():
 
 
 def records(case):
-    return [NodeMetrics(f"node-{i}", from_bits(n["cu_bits"]), from_bits(n["mu_bits"]), 8.0,
-                        15.616012573242188, n["pc"], n["mp"], conditions=COND[n["cond"]])
+    # the "odd-alloc" cases carry available_cpu / available_memory values (inf, nan, 1e300, negative) that
+    # the reference accepts because its decision never reads those fields (scheduler.py:531-549)
+    return [NodeMetrics(f"node-{i}", from_bits(n["cu_bits"]), from_bits(n["mu_bits"]),
+                        from_bits(n["avail_cpu_bits"]) if "avail_cpu_bits" in n else 8.0,
+                        from_bits(n["avail_mem_bits"]) if "avail_mem_bits" in n else 15.616012573242188,
+                        n["pc"], n["mp"], conditions=COND[n["cond"]])
             for i, n in enumerate(case["nodes"])]
 
 
@@ -40,6 +44,34 @@ def test_reference_decisions_through_adapter(placer, golden_dir):
             assert dec.confidence == exp["confidence"]
             assert dec.reasoning == exp["reasoning"]
             assert dec.fallback_needed is True
+
+
+def test_adapter_never_raises(placer, golden_dir):
+    """no exception may reach the scheduling loop; anything the GPU path cannot take comes
+    back as the reference's in-band failure record (scheduler.py:558-559)."""
+    class Broken:
+        name = "broken"
+        conditions = COND["ready"]
+        cpu_usage_percent = memory_usage_percent = 1.0
+        available_cpu = available_memory = 1.0
+        max_pods = 110
+
+        @property
+        def pod_count(self):
+            raise RuntimeError("record went away")
+
+    placer.config["fallback"] = {"strategy": "least_loaded"}
+    for bad in ([Broken()], [NodeMetrics("x", 1.0, 1.0, 1.0, 1.0, "seven", 110, conditions=COND["ready"])],
+                [NodeMetrics("y", 1.0, 1.0, 1.0, 1.0, 2 ** 70, 110, conditions=COND["ready"])], [object()]):
+        dec = placer.fallback_decision(bad, "why")
+        assert (dec.selected_node, dec.confidence, dec.reasoning, dec.fallback_needed) == ("", 0.0, "Fallback failed: why", True)
+    ok = placer.fallback_decision([NodeMetrics("z", 1.0, 1.0, float("nan"), float("inf"), 3, 110, conditions=COND["ready"])], "why")
+    assert ok.selected_node == "z" and ok.confidence == 0.4
+    # the per-pod extension reads the allocatable fields, so there the same record is a failure, not an exception
+    from k8s_llm_scheduler_b200.tables import PodSpec
+    dec = placer.fallback_decision_for_pod([NodeMetrics("z", 1.0, 1.0, float("nan"), 2.0, 3, 110, conditions=COND["ready"])],
+                                           PodSpec("p", "default", 0.1, 0.125), "why")
+    assert dec.selected_node == "" and dec.reasoning == "Fallback failed: why"
 
 
 def test_default_strategy_and_capacity_extension(placer):

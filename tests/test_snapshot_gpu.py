@@ -260,6 +260,31 @@ def test_session_host_api_matches_device_api():
             s.snapshot(nodes, PodTable.from_columns(np.zeros(40_000), np.zeros(40_000)), 0, 1)
 
 
+def test_session_inputs_that_need_conversion_stay_alive_for_the_call():
+    """Columns of the 'wrong' dtype or layout (bool ready, int32 counts, Python lists, strided views, float
+    tensors) are converted to temporaries; the temporaries must live until kp_session_snapshot has returned."""
+    import gc
+    import torch
+    from k8s_llm_scheduler_b200.placement import Session
+    nodes, pods = synth.config5(4000, 50_000, seed=43)
+    uniform = PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes)
+    want = oracle_snapshot(nodes, uniform, 0, 1)
+    c = nodes.columns()
+    odd = {"alloc_cpu_milli": c["alloc_cpu_milli"].tolist(), "alloc_mem_bytes": np.repeat(c["alloc_mem_bytes"], 2)[::2],
+           "pod_count": c["pod_count"].astype(np.int32), "max_pods": torch.as_tensor(c["max_pods"]).to(torch.int32),
+           "ready": c["ready"].astype(bool), "cpu_usage_pct": c["cpu_usage_pct"].astype(np.longdouble),
+           "mem_usage_pct": torch.as_tensor(c["mem_usage_pct"])}
+    odd_pods = (pods.req_cpu_milli.astype(np.float64), torch.as_tensor(pods.req_mem_bytes).to(torch.float64), None)
+    with Session(0, max_nodes=4096, max_pods=65_536) as s:
+        for _ in range(3):
+            junk = [np.full(50_000, -1, np.int64) for _ in range(8)]      # churn the allocator between calls
+            gi, gs = s.snapshot(odd, odd_pods, 0, 1)
+            del junk
+            gc.collect()
+            assert_same_idx(gi, want[0])
+            assert_same_f64(gs, want[1])
+
+
 @pytest.mark.parametrize("n,p", [(1000, 30_000), (8192, 5_000), (9000, 5_000), (3, 1), (700, 257), (500, 400_000)])
 def test_session_pinned_buffers_are_used_in_place(n, p):
     """Pinned host tables: small tables with one strategy are read / written by the kernels

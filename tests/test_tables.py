@@ -130,3 +130,21 @@ def test_c_record_walker_equals_the_python_loops(monkeypatch):
                     return "ValueError"
             fast, slow = both(one)
             assert fast == slow, (bad, exact)
+    # ready_only (the adapter's form for the reference's own filter): the allocatable fields are not read
+    odd = [T.NodeMetrics(f"o{i}", 3.0, 4.0, v, w, 5, 110, conditions=COND["ready"])
+           for i, (v, w) in enumerate([(float("inf"), float("nan")), (1e300, -4.0), ("text", None)])]
+    a, b = both(lambda: T.NodeTable.from_node_metrics(odd, ready_only=True))
+    for col in T.NODE_COLUMNS:
+        assert np.array_equal(getattr(a, col), getattr(b, col)), col
+    assert not a.alloc_cpu_milli.any() and not a.alloc_mem_bytes.any() and a.pod_count.tolist() == [5, 5, 5]
+    for exact in (True, False):
+        fast, slow = both(lambda exact=exact: _raises(lambda: T.NodeTable.from_node_metrics(odd[:2], exact=exact)))
+        assert fast == slow == "ValueError"
+
+
+def _raises(fn):
+    try:
+        fn()
+    except ValueError:
+        return "ValueError"
+    return "ok"
