@@ -2,20 +2,25 @@
 """Benchmark of the fallback placement path (BASELINE.json metric: pod x node scores/sec
 and pods placed/sec), own arm and reference arm.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c4shard|c5|c5greedy]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c4shard|c5|c5greedy|c5node]
   python bench.py --impl reference ...        # the reference's CPU algorithm on host cores
   torchrun --nproc-per-node N bench.py --gpus N ...   # one rank per GPU, NCCL
 
 A "step" is one pass of the hot path over one batch of synthetic input:
-  * default workload c2 = BASELINE configs[1]: least_loaded snapshot scoring, 1 000 nodes x
-    100 000 pending pods per GPU, capacity filter.  With N > 1 GPUs every rank scores its
-    own 100 000-pod shard against the node table broadcast from rank 0 (weak scaling, no
-    data-path collective).
+  * default workload c4 = BASELINE configs[3], the configuration the north star sizes:
+    resource_balanced snapshot scoring, 50 000 nodes x 10 000 000 pending pods, capacity
+    filter.  It fits one GPU (N = 1 scores all 10 M pods).  With N > 1 GPUs the SAME 10 M pods
+    are split into N contiguous shards, one per rank, against the node table broadcast from
+    rank 0 over NCCL (strong scaling, no data-path collective).  Snapshot workloads named with
+    --workload shard the same way; greedy workloads run independent replicas at N > 1;
+    c5node is config 5 with the NODES sharded and a per-pod arg-max reduce across ranks.
   * `value` times the device path with the tables already resident in HBM (CUDA events on
-    the launching stream, L2 flushed between steps, max over ranks).
+    the launching stream, L2 flushed between steps, max over ranks).  Pairs are counted over
+    the ELIGIBLE nodes (Ready, room for a pod), which is what the kernel scans.
   * `e2e` times the reference-facing host API (kp_session_snapshot): pinned host tables in,
     H2D copies, kernels, D2H of the results, all inside the timed region.
-  * `roofline` is for the dominant kernel (place_kernel), timed live with CUDA events.
+  * `roofline` is for the dominant kernel (place_kernel), timed live with CUDA events, against
+    the theoretical issue rate and against the issue peak measured in this run (kp_issue_peak).
   * `cpu_baseline` / `--impl reference` time the CPU restatement of the reference's loop
     (oracle/py_oracle.py, same CPython data structures) on the box's host cores over a
     bounded sample of the same workload.  Only these two legs touch oracle/.
@@ -45,45 +50,81 @@ STRATEGY_NAMES = {0: "resource_balanced", 1: "least_loaded", 2: "round_robin"}
 
 
 # --------------------------------------------------------------------------------------
-# workloads; pods_per_gpu fixed as N grows (weak scaling)
+# workloads: the WHOLE job; ranks take shards of it (local_pods)
 # --------------------------------------------------------------------------------------
-def make_workload(name: str, rank: int):
+DEFAULT_WORKLOAD = "c4"
+
+
+def make_workload(name: str):
     from k8s_llm_scheduler_b200 import synth
-    seed_shift = 1000 * rank              # every rank scores a different pod shard
     if name == "c2":
-        nodes, _ = synth.config2(1000, 1)
-        _, pods = synth.config2(1000, 100_000, seed=2 + seed_shift)
-        return nodes, pods, dict(mode="snapshot", strategy=1, filter=1, per_pod=False,
-                                 desc="c2: least_loaded snapshot, 1000 nodes x 100000 pods per GPU, capacity filter")
+        nodes, pods = synth.config2(1000, 100_000)
+        return nodes, pods, dict(mode="snapshot", strategy=1, filter=1, per_pod=False, config="configs[1]",
+                                 desc="c2: least_loaded snapshot, 1000 nodes x 100000 pods, capacity filter")
     if name == "c4shard":
-        nodes, _ = synth.config4(50_000, 1)
-        _, pods = synth.config4(50_000, 1_250_000, seed=4 + seed_shift)
-        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=False,
-                                 desc="c4 shard: resource_balanced snapshot, 50000 nodes x 1250000 pods per GPU "
-                                      "(10M pods / 8), capacity filter")
+        nodes, pods = synth.config4(50_000, 1_250_000)
+        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=False, config="configs[3] / 8",
+                                 desc="c4 shard: resource_balanced snapshot, 50000 nodes x 1250000 pods "
+                                      "(what one of 8 GPUs scores of config 4), capacity filter")
     if name == "c4":
-        nodes, _ = synth.config4(50_000, 1)
-        _, pods = synth.config4(50_000, 10_000_000, seed=4 + seed_shift)
-        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=False,
-                                 desc="c4: resource_balanced snapshot, 50000 nodes x 10000000 pods per GPU, capacity filter")
-    if name == "c5":
-        nodes, _ = synth.config5(20_000, 1)
-        _, pods = synth.config5(20_000, 2_000_000, seed=5 + seed_shift)
-        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=True,
-                                 desc="c5 (snapshot form): mixed strategies, 20000 heterogeneous nodes x 2000000 pods "
-                                      "per GPU, 30% infeasible, capacity filter")
+        nodes, pods = synth.config4(50_000, 10_000_000)
+        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=False, config="configs[3]",
+                                 desc="c4: resource_balanced snapshot, 50000 nodes x 10000000 pods, capacity filter")
+    if name in ("c5", "c5node"):
+        nodes, pods = synth.config5(20_000, 2_000_000)
+        return nodes, pods, dict(mode="snapshot", strategy=0, filter=1, per_pod=True, config="configs[4]",
+                                 node_sharded=name == "c5node",
+                                 desc="c5 (snapshot form): mixed strategies, 20000 heterogeneous nodes x 2000000 pods, "
+                                      "30% infeasible, capacity filter" +
+                                      (", nodes sharded over the ranks with a per-pod arg-max reduce" if name == "c5node" else ""))
     if name == "c3":
-        nodes, pods = synth.config3(5000, 1_000_000, seed=3 + seed_shift)
-        return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=False,
-                                 desc="c3: resource_balanced greedy commit, 5000 nodes x 1000000 pods per GPU, "
+        nodes, pods = synth.config3(5000, 1_000_000)
+        return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=False, config="configs[2]",
+                                 desc="c3: resource_balanced greedy commit, 5000 nodes x 1000000 pods, "
                                       "capacity filter (replicas at N > 1)")
     if name == "c5greedy":
-        nodes, _ = synth.config5(20_000, 1)
-        _, pods = synth.config5(20_000, 2_000_000, seed=5 + seed_shift)
-        return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=True,
-                                 desc="c5 (greedy form): mixed strategies, 20000 heterogeneous nodes x 2000000 pods "
-                                      "per GPU, 30% infeasible, sequential commit (replicas at N > 1)")
+        nodes, pods = synth.config5(20_000, 2_000_000)
+        return nodes, pods, dict(mode="greedy", strategy=0, filter=1, per_pod=True, config="configs[4]",
+                                 desc="c5 (greedy form): mixed strategies, 20000 heterogeneous nodes x 2000000 pods, "
+                                      "30% infeasible, sequential commit (replicas at N > 1)")
     raise SystemExit(f"unknown workload {name}")
+
+
+def shard_bounds(n_items: int, rank: int, world: int):
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def local_pods(pods, meta, rank: int, world: int):
+    """This rank's part of the job: a contiguous pod shard for pod-sharded snapshots (strong scaling); the
+    whole pod list for greedy replicas and for the node-sharded form."""
+    from k8s_llm_scheduler_b200.tables import PodTable
+    if meta["mode"] != "snapshot" or meta.get("node_sharded") or world == 1:
+        return pods, 0
+    lo, hi = shard_bounds(len(pods), rank, world)
+    return PodTable.from_columns(pods.req_cpu_milli[lo:hi], pods.req_mem_bytes[lo:hi],
+                                 None if pods.strategy_ids is None else pods.strategy_ids[lo:hi]), lo
+
+
+def eligible_nodes(nodes, meta) -> int:
+    """Nodes the placement kernel scans: Ready, and under the capacity filter with room for one more pod
+    (scores of the synthetic tables are all above the -1 sentinel)."""
+    ok = nodes.ready != 0
+    if meta["filter"] == 1:
+        ok &= nodes.pod_count < nodes.max_pods
+    return int(ok.sum())
+
+
+def config_block(meta, nodes, pods, world: int, extra=None):
+    """`config` of the JSON line; identical in both arms apart from the run-specific tail."""
+    cfg = {"workload": meta["desc"], "baseline_config": meta["config"], "nodes": len(nodes), "pods": len(pods),
+           "nodes_eligible": eligible_nodes(nodes, meta),
+           "strategy": "per-pod mix" if meta["per_pod"] else STRATEGY_NAMES[meta["strategy"]],
+           "filter": "capacity" if meta["filter"] == 1 else "ready", "mode": meta["mode"],
+           "pairs_counted": "pods x eligible nodes"}
+    cfg.update(extra or {})
+    return cfg
 
 
 # --------------------------------------------------------------------------------------
@@ -156,11 +197,11 @@ def host_cores() -> int:
     return len(os.sched_getaffinity(0))
 
 
-def cpu_port_run(nodes, pods, meta, budget_s: float, calibrate=True):
+def cpu_port_run(nodes, pods, meta, budget_s: float):
     """Time oracle/py_oracle.py on a bounded sample.  Returns dict(value, cores, sample, idx, n_sample)."""
     import multiprocessing as mp
     from oracle import py_oracle as po
-    n = len(nodes)
+    n, n_el = len(nodes), eligible_nodes(nodes, meta)
     recs = po.nodes_from_arrays(**nodes.columns())
     names = ([po.strategy_name(s) for s in pods.strategy_ids] if meta["per_pod"]
              else po.strategy_name(meta["strategy"]))
@@ -188,9 +229,26 @@ def cpu_port_run(nodes, pods, meta, budget_s: float, calibrate=True):
             parts = pool.map(_cpu_worker, spans, chunksize=1)
             el = time.perf_counter() - t
         idx = [i for part in parts for i in part]
-    return dict(value=s * n / el, pods_per_s=s / el, seconds=el, cores=cores, n_sample=s, idx=np.array(idx),
-                sample=f"first {s} pods x all {n} nodes of the workload, CPython port of the reference loop "
-                       f"(oracle/py_oracle.py), {cores} process(es), {el:.1f} s")
+    idx = np.array(idx)
+    return dict(value=s * n_el / el, pods_per_s=s / el, placed_per_s=float((idx >= 0).sum()) / el, seconds=el,
+                cores=cores, n_sample=s, idx=idx,
+                sample=f"first {s} pods x all {n} nodes ({n_el} eligible) of the workload, CPython port of the "
+                       f"reference loop (oracle/py_oracle.py), {cores} process(es), {el:.1f} s")
+
+
+def c_oracle_check(nodes, pods, meta, got_idx, count: int = 2000):
+    """Parity bit for every bench line (any world size): the first `count` decisions of this rank against
+    the C oracle on all host cores.  Checker only -- nothing measured comes from here."""
+    from oracle import c_oracle
+    k = int(min(count, len(pods)))
+    sid = pods.strategy_ids[:k] if meta["per_pod"] else None
+    if meta["mode"] == "greedy":
+        want = c_oracle.greedy(nodes.columns(), pods.req_cpu_milli[:k], pods.req_mem_bytes[:k], strategy=meta["strategy"],
+                               strategy_ids=sid, filter_mode=meta["filter"])[0]
+    else:
+        want = c_oracle.snapshot(nodes.columns(), pods.req_cpu_milli[:k], pods.req_mem_bytes[:k], strategy=meta["strategy"],
+                                 strategy_ids=sid, filter_mode=meta["filter"], threads=host_cores())[0]
+    return bool(np.array_equal(np.asarray(got_idx[:k]), want)), k
 
 
 # --------------------------------------------------------------------------------------
@@ -200,7 +258,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    nodes, pods, meta = make_workload(args.workload, 0)
+    nodes, pods, meta = make_workload(args.workload)
     per_step = max(1.0, min(12.0, 150.0 / (args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_port_run(nodes, pods, meta, per_step)
@@ -213,18 +271,23 @@ def run_reference(args):
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "pods_per_sec": value / len(nodes),
-        "config": {"workload": meta["desc"], "nodes": len(nodes), "strategy": STRATEGY_NAMES[meta["strategy"]],
-                   "sample_pods_per_step": last["n_sample"]},
+        "higher_is_better": True, "scaling": scaling_of(meta), "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "pods_per_sec": value / eligible_nodes(nodes, meta),
+        "config": config_block(meta, nodes, pods, args.gpus),
+        "sample_pods_per_step": last["n_sample"],
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port",
                          "sample": last["sample"]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "the reference is pure Python with a K8s/HF import chain that cannot travel to the GPU box; "
-                "this arm times its CPU restatement (pinned to reference-generated vectors) on the host cores",
+                "this arm times its CPU restatement (pinned to reference-generated vectors; BASELINE.md compares it "
+                "with the imported reference on one host) on the host cores",
     }
     print(json.dumps(out))
+
+
+def scaling_of(meta) -> str:
+    return "strong" if meta["mode"] == "snapshot" else "weak"
 
 
 # --------------------------------------------------------------------------------------
@@ -241,18 +304,67 @@ def measured_peaks():
     return 6650.0, 1965.0, "fallback"
 
 
+def issue_peak_pairs_per_s(torch, lib, dev, min_ms: float = 50.0):
+    """roofline.peak_measured: the three instructions of the inner loop with nothing around them (kp_issue_peak)."""
+    import ctypes
+    scratch = torch.zeros(256, dtype=torch.uint8, device=dev)
+    out = ctypes.c_double()
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = lib.kp_issue_peak(ctypes.c_void_p(scratch.data_ptr()), 256, float(min_ms), stream, ctypes.byref(out))
+    return out.value if rc == 0 else None
+
+
+def place_roofline(p, n_el, n, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src, clk, peak_meas, hbm_peak,
+                   traffic, per_pod):
+    """Issue roofline of place_kernel: 3 lane-ops (subtract, test, predicated update) per pod x eligible node."""
+    t_place = statistics.mean(place_ms) * 1e-3
+    peak_issue = sm_count * 128 * sm_max_mhz * 1e6           # lane-ops/s: 4 schedulers x 32 lanes per SM-clock
+    ach = 3.0 * p * n_el / t_place
+    pod_bytes = 40.0 if per_pod else 32.0
+    r = {"kernel": "place_kernel", "bound": "issue", "achieved": ach / 1e12, "peak": peak_issue / 1e12,
+         "unit": "Tlane-op/s", "frac": ach / peak_issue, "traffic": traffic,
+         "ops_per_launch": 3.0 * p * n_el, "ops_per_unit": "3 lane-ops per pod x eligible node (DESIGN.md 5.1)",
+         "peak_source": f"theoretical: {sm_count} SMs x 128 lanes x {sm_max_mhz:.0f} MHz (MEASURED_PEAKS.json sm_max_mhz, {peak_src}); "
+                        "no entry of MEASURED_PEAKS.json bounds this kernel (HBM view below)",
+         "peak_measured": None if not peak_meas else 3.0 * peak_meas / 1e12,
+         "frac_measured": None if not peak_meas else ach / (3.0 * peak_meas),
+         "peak_measured_source": "kp_issue_peak in this run: the same three instructions per pair on a shared-memory tile, "
+                                 "best of the two update mixes, 4 CTAs per SM",
+         "frac_at_sampled_clock": ach / (sm_count * 128 * clk * 1e6),
+         "achieved_survey_4op": 4.0 * p * n_el / t_place / 1e12,
+         "kernel_ms": t_place * 1e3, "plan_ms": statistics.mean(plan_ms),
+         "kernel_share_of_step": statistics.mean(place_ms) / statistics.mean(step_ms),
+         "kernel_timing": "CUDA events around place_kernel in a second pass of the same steps (instrumented)",
+         "hbm": {"bound": "hbm", "achieved": (pod_bytes * p + 56.0 * n) / t_place / 1e9, "peak": hbm_peak,
+                 "unit": "GB/s", "frac": (pod_bytes * p + 56.0 * n) / t_place / 1e9 / hbm_peak,
+                 "note": "algorithmic HBM bytes are negligible for this kernel; issue-bound (SURVEY.md §8d regime X)"}}
+    return r
+
+
+def load_traffic(name):
+    tr = ROOT / "profiles" / "traffic.json"
+    if tr.exists():
+        try:
+            return json.loads(tr.read_text()).get(name)
+        except Exception:  # noqa: BLE001
+            pass
+    return None
+
+
 def run_ours(args):
+    import ctypes
     import torch
     import torch.distributed as dist
     from k8s_llm_scheduler_b200 import _lib, placement
     from k8s_llm_scheduler_b200.build import build_library
-    from k8s_llm_scheduler_b200.tables import NODE_COLUMNS, NodeTable
+    from k8s_llm_scheduler_b200.tables import NODE_COLUMNS
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    pin_to_gpu_numa_node(local)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -264,8 +376,11 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
-    nodes, pods, meta = make_workload(args.workload, rank)
-    n, p = len(nodes), len(pods)
+    nodes, all_pods, meta = make_workload(args.workload)
+    if meta.get("node_sharded"):
+        return run_node_sharded(args, torch, dist, placement, lib, dev, nodes, all_pods, meta, world, rank, local)
+    pods, pod_lo = local_pods(all_pods, meta, rank, world)
+    n, p, n_el = len(nodes), len(pods), eligible_nodes(nodes, meta)
     # node table: rank 0's copy is broadcast over NCCL/NVLink (replicated table, sharded pods)
     dn = placement.nodes_to_device(nodes, dev)
     if world > 1:
@@ -275,6 +390,7 @@ def run_ours(args):
     rm = torch.as_tensor(pods.req_mem_bytes).to(dev)
     strat = torch.as_tensor(pods.strategy_ids).to(dev) if meta["per_pod"] else meta["strategy"]
     snapshot = meta["mode"] == "snapshot"
+    res = {}
     if snapshot:
         ws = torch.empty(placement.snapshot_workspace_bytes(n, p, meta["per_pod"]), dtype=torch.uint8, device=dev)
         out = (torch.empty(p, dtype=torch.int64, device=dev), torch.empty(p, dtype=torch.float64, device=dev))
@@ -283,10 +399,14 @@ def run_ours(args):
             placement.snapshot_place(dn, rc, rm, strat, meta["filter"], workspace=ws, out=out)
     else:
         ws = torch.empty(placement.greedy_workspace_bytes(n, p), dtype=torch.uint8, device=dev)
-        res = {}
 
         def step():
             res["out"] = placement.greedy_place(dn, rc, rm, strat, meta["filter"], workspace=ws)
+
+    # the kernel's own count of eligible nodes must agree with the host's (it is what `value` counts)
+    el_dev = int(placement.node_scores(dn, 0 if meta["per_pod"] else meta["strategy"], meta["filter"])[3].sum().item())
+    if el_dev != n_el:
+        raise SystemExit(f"eligible nodes: host says {n_el}, device says {el_dev}")
 
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -295,16 +415,18 @@ def run_ours(args):
             flush_buf.zero_()
 
     hbm_peak, sm_max_mhz, peak_src = measured_peaks()
+    peak_meas = issue_peak_pairs_per_s(torch, lib, dev) if rank == 0 and snapshot else None
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    import ctypes
     place_ms, plan_ms = [], []
 
     # timed region (device time, per-step CUDA events on the launching stream); no
     # instrumentation inside the steps, so the kernels chain with dependent launches
-    for _ in range(args.warmup):
+    steps = args.steps if snapshot else max(1, min(args.steps, 3))
+    warmup = args.warmup if snapshot else 1
+    for _ in range(warmup):
         step()
     torch.cuda.synchronize()
     barrier()
@@ -312,7 +434,7 @@ def run_ours(args):
     launches0 = placement.launch_count()
     evs = []
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         flush()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
@@ -323,11 +445,12 @@ def run_ours(args):
     t1 = time.perf_counter()
     barrier()
     launches = placement.launch_count() - launches0
+    dev_idx = (out[0] if snapshot else res["out"][0])[:4096].cpu().numpy()
     # second pass of the same K steps with CUDA events around the plan and the place kernel
     # (kp_profile_*): the live duration of the dominant kernel for the roofline
     if snapshot and meta["filter"] == 1:
         lib.kp_profile_enable(1)
-        for _ in range(args.steps):
+        for _ in range(steps):
             flush()
             step()
             fa, fb = ctypes.c_float(), ctypes.c_float()
@@ -341,8 +464,10 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     total_ms = float(tot.item())
-    ms_per_step = total_ms / args.steps
-    pairs_per_step = float(world) * p * n
+    ms_per_step = total_ms / steps
+    # whole-job units: the sharded snapshot scores all pods once; greedy replicas each do the whole job
+    pods_per_step = float(len(all_pods)) * (1 if snapshot else world)
+    pairs_per_step = pods_per_step * n_el
     value = pairs_per_step / (ms_per_step * 1e-3)
     clocks = sampler.stop(t0, t1) if rank == 0 else None
 
@@ -357,21 +482,26 @@ def run_ours(args):
         if snapshot:
             sess.snapshot(hn, hp, meta["strategy"], meta["filter"], out=ho)
         else:
-            sess.greedy(hn, hp, meta["strategy"], meta["filter"])
+            res["e2e"] = sess.greedy(hn, hp, meta["strategy"], meta["filter"])
 
-    e2e_steps = args.steps if snapshot else max(1, min(args.steps, 3))
-    for _ in range(min(args.warmup, 3) if not snapshot else args.warmup):
+    for _ in range(min(warmup, 3)):
         e2e_step()
     barrier()
-    t = time.perf_counter()
-    for _ in range(e2e_steps):
+    e2e_each = []
+    for _ in range(steps):
+        t = time.perf_counter()
         e2e_step()
-    e2e_s = torch.tensor([(time.perf_counter() - t) / e2e_steps], dtype=torch.float64, device=dev)
+        e2e_each.append(time.perf_counter() - t)
+    e2e_s = torch.tensor([sum(e2e_each) / steps], dtype=torch.float64, device=dev)
+    e2e_all = [torch.zeros_like(e2e_s) for _ in range(world)]
     if world > 1:
+        dist.all_gather(e2e_all, e2e_s)
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    else:
+        e2e_all = [e2e_s]
     h2d, d2h = sess.last_copy_bytes()
     e2e_value = pairs_per_step / float(e2e_s.item())
-    e2e_idx = ho[0].numpy().copy() if snapshot else None
+    e2e_idx = ho[0].numpy().copy() if snapshot else res["e2e"][0]
     sess.close()
 
     if rank != 0:
@@ -379,105 +509,173 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
-    # roofline of the dominant kernel
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    clk = (clocks or {}).get("sm_mhz") or sm_max_mhz
     roofline = None
     if place_ms:
-        t_place = statistics.mean(place_ms) * 1e-3
-        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-        clk = (clocks or {}).get("sm_mhz") or sm_max_mhz
-        peak_issue = sm_count * 128 * sm_max_mhz * 1e6           # lane-ops/s: 4 schedulers x 32 lanes per SM-clock
-        ach = 3.0 * p * n / t_place                              # 2 compares + 1 select per pair
-        roofline = {
-            "kernel": "place_kernel", "bound": "issue", "achieved": ach / 1e12, "peak": peak_issue / 1e12,
-            "unit": "Tlane-op/s", "frac": ach / peak_issue, "traffic": None,
-            "peak_source": f"{sm_count} SMs x 128 lanes x {sm_max_mhz:.0f} MHz (MEASURED_PEAKS.json sm_max_mhz, {peak_src})",
-            "frac_at_sampled_clock": ach / (sm_count * 128 * clk * 1e6),
-            "achieved_survey_4op": 4.0 * p * n / t_place / 1e12,
-            "kernel_ms": t_place * 1e3, "plan_ms": statistics.mean(plan_ms),
-            "kernel_share_of_step": statistics.mean(place_ms) / statistics.mean(step_ms),
-            "kernel_timing": "CUDA events around place_kernel in a second pass of the same steps (instrumented)",
-            "hbm": {"bound": "hbm", "achieved": (32.0 * p + 56.0 * n) / t_place / 1e9, "peak": hbm_peak,
-                    "unit": "GB/s", "frac": (32.0 * p + 56.0 * n) / t_place / 1e9 / hbm_peak,
-                    "note": "algorithmic HBM bytes are negligible for this kernel; issue-bound (SURVEY.md §8d regime X)"},
-        }
-        tr = ROOT / "profiles" / "traffic.json"
-        if tr.exists():
-            try:
-                roofline["traffic"] = json.loads(tr.read_text()).get(args.workload)
-            except Exception:  # noqa: BLE001
-                pass
+        roofline = place_roofline(p, n_el, n, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src, clk, peak_meas,
+                                  hbm_peak, load_traffic(args.workload if world == 1 else f"{args.workload}/{world}"),
+                                  meta["per_pod"])
 
+    # parity: every line carries a C-oracle check of this rank's first decisions (device pass AND host-API pass);
+    # the single-GPU line also compares with the CPython port it times as the CPU baseline
+    ok_dev, k_chk = c_oracle_check(nodes, pods, meta, dev_idx)
+    ok_e2e, _ = c_oracle_check(nodes, pods, meta, e2e_idx)
+    parity = ok_dev and ok_e2e
     cpu_baseline = None
-    parity = None
     if world == 1 and not args.no_cpu:
-        cb = cpu_port_run(nodes, pods, meta, args.cpu_seconds)
+        if NUMA_NOTE.get("orig_affinity"):
+            os.sched_setaffinity(0, NUMA_NOTE["orig_affinity"])     # the CPU baseline gets every core the process may use
+        cb = cpu_port_run(nodes, all_pods, meta, args.cpu_seconds)
         cpu_baseline = {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port",
                         "sample": cb["sample"], "pods_per_sec": cb["pods_per_s"]}
-        if snapshot:
-            got = e2e_idx[:cb["n_sample"]]
-        else:
-            got = res["out"][0][:cb["n_sample"]].cpu().numpy()
-        parity = bool(np.array_equal(got, cb["idx"]))
+        parity = parity and bool(np.array_equal(e2e_idx[:cb["n_sample"]], cb["idx"]))
 
-    out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+    sharding = "single GPU"
+    if world > 1:
+        sharding = (f"the {len(all_pods)} pods split into {world} contiguous shards, node table broadcast from rank 0 (NCCL), "
+                    "no data-path collective" if snapshot else f"{world} independent replicas (greedy does not shard, DESIGN.md 7)")
+    out_line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling_of(meta),
         "vs_baseline": None, "dtype": "f64 scores, i32 rank compares", "data": "synthetic",
-        "pods_per_sec": float(world) * p / (ms_per_step * 1e-3),
-        "config": {"workload": meta["desc"], "nodes": n, "pods_per_gpu": p,
-                   "strategy": "per-pod mix" if meta["per_pod"] else STRATEGY_NAMES[meta["strategy"]],
-                   "filter": "capacity" if meta["filter"] == 1 else "ready", "mode": meta["mode"],
-                   "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)",
-                   "sharding": "pods sharded per rank, node table broadcast from rank 0 (NCCL)" if world > 1 else "single GPU"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": float(e2e_s.item()) * 1e3, "api": "kp_session_snapshot" if snapshot else "kp_session_greedy"},
+        "pods_per_sec": pods_per_step / (ms_per_step * 1e-3),
+        "config": config_block(meta, nodes, all_pods, world),
+        "run": {"pods_per_gpu": p, "sharding": sharding,
+                "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d * (world if snapshot else 1),
+                "d2h_bytes_per_step": d2h * (world if snapshot else 1),
+                "ms_per_step": float(e2e_s.item()) * 1e3, "api": "kp_session_snapshot" if snapshot else "kp_session_greedy",
+                "per_rank_ms": [float(t.item()) * 1e3 for t in e2e_all],
+                "rank0_ms_min_median": [min(e2e_each) * 1e3, statistics.median(e2e_each) * 1e3],
+                "host_numa": NUMA_NOTE.get("note")},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "cpu_baseline": cpu_baseline, "parity_vs_cpu_sample": parity,
+        "parity_detail": {"c_oracle_pods_checked": k_chk, "device_pass": ok_dev, "host_api_pass": ok_e2e,
+                          "python_port_sample": None if cpu_baseline is None else "first pods of the cpu_baseline sample"},
     }
+    if not snapshot:
+        out_line["greedy"] = greedy_report(torch, placement, dn, rc, rm, strat, meta, res["out"], ws)
     if world == 1 and args.extra:
-        out["extra"] = run_extras(args, torch, placement, lib, dev)
-    print(json.dumps(out))
+        out_line["extra"] = run_extras(args, torch, placement, lib, dev, peak_meas)
+    print(json.dumps(out_line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_extras(args, torch, placement, lib, dev):
+NUMA_NOTE = {}
+
+
+def pin_to_gpu_numa_node(local: int):
+    """Before any pinned allocation: run this process (and so place its pinned pages) on the CPUs of the
+    GPU's own NUMA node.  Without it every rank's pinned tables land wherever the launcher ran, and at 8
+    ranks the e2e path (host link both ways every step) crosses sockets for half the GPUs."""
+    try:
+        import pynvml
+        NUMA_NOTE["orig_affinity"] = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [v.strip() for v in vis.split(",") if v.strip()]
+        phys = int(ids[local]) if ids and all(v.isdigit() for v in ids) and local < len(ids) else local
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            NUMA_NOTE["note"] = f"process bound to the GPU's {len(use)} local CPUs (of {len(allowed)} allowed)"
+        else:
+            NUMA_NOTE["note"] = f"GPU-local CPU set covers all {len(allowed)} allowed CPUs: no binding needed"
+    except Exception as e:  # noqa: BLE001
+        NUMA_NOTE["note"] = f"no NUMA binding ({type(e).__name__})"
+
+
+def greedy_report(torch, placement, dn, rc, rm, strat, meta, out, ws):
+    """BASELINE's second metric is pods PLACED per second.  A greedy run has three regimes: pods placed, pods
+    rejected because nothing fits them, and -- once the cluster is full -- a tail in which every pod is
+    rejected at once.  Report them apart, and time the run up to the depletion point on its own."""
+    idx = out[0]
+    placed = int((idx >= 0).sum().item())
+    total = idx.numel()
+    last = int(torch.nonzero(idx >= 0)[-1].item()) if placed else -1
+    rep = {"pods": total, "pods_placed": placed, "pods_rejected": total - placed, "last_placed_pod": last}
+    if placed:
+        k = last + 1
+        rck, rmk = rc[:k].contiguous(), rm[:k].contiguous()
+        sk = strat[:k].contiguous() if meta["per_pod"] else strat
+        placement.greedy_place(dn, rck, rmk, sk, meta["filter"], workspace=ws)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        placement.greedy_place(dn, rck, rmk, sk, meta["filter"], workspace=ws)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        rep.update({"ms_to_depletion": ms, "pods_decided_to_depletion": k,
+                    "placed_per_sec": placed / (ms * 1e-3), "ns_per_placed_pod": ms * 1e6 / placed})
+    return rep
+
+
+def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, world, rank, local):
+    raise SystemExit("workload c5node: node-sharded snapshot is not wired into bench.py yet")
+
+
+def run_extras(args, torch, placement, lib, dev, peak_meas):
     """Secondary single-GPU numbers for the other BASELINE configs (not the headline)."""
     import ctypes
     extras = {}
-    for name, steps in (("c4shard", 3), ("c4", 2), ("c5", 2), ("c3", 1), ("c5greedy", 1)):
+    hbm_peak, sm_max_mhz, peak_src = measured_peaks()
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for name, steps in (("c2", 20), ("c4shard", 3), ("c5", 3), ("c3", 1), ("c5greedy", 1)):
+        if name == args.workload:
+            continue
         try:
-            nodes, pods, meta = make_workload(name, 0)
-            n, p = len(nodes), len(pods)
+            nodes, pods, meta = make_workload(name)
+            n, p, n_el = len(nodes), len(pods), eligible_nodes(nodes, meta)
             dn = placement.nodes_to_device(nodes, dev)
             rc = torch.as_tensor(pods.req_cpu_milli).to(dev)
             rm = torch.as_tensor(pods.req_mem_bytes).to(dev)
             strat = torch.as_tensor(pods.strategy_ids).to(dev) if meta["per_pod"] else meta["strategy"]
-            if meta["mode"] == "snapshot":
-                lib.kp_profile_enable(1)
-                fn = lambda: placement.snapshot_place(dn, rc, rm, strat, meta["filter"])  # noqa: E731
+            snapshot = meta["mode"] == "snapshot"
+            res = {}
+            if snapshot:
+                ws = torch.empty(placement.snapshot_workspace_bytes(n, p, meta["per_pod"]), dtype=torch.uint8, device=dev)
+                fn = lambda: res.__setitem__("out", placement.snapshot_place(dn, rc, rm, strat, meta["filter"], workspace=ws))  # noqa: E731
             else:
-                fn = lambda: placement.greedy_place(dn, rc, rm, strat, meta["filter"])  # noqa: E731
-            fn()
+                ws = torch.empty(placement.greedy_workspace_bytes(n, p), dtype=torch.uint8, device=dev)
+                fn = lambda: res.__setitem__("out", placement.greedy_place(dn, rc, rm, strat, meta["filter"], workspace=ws))  # noqa: E731
+            for _ in range(3 if snapshot else 1):
+                fn()
             torch.cuda.synchronize()
-            ms, place = [], []
-            for _ in range(steps):
+            ms, place, plan = [], [], []
+            for _ in range(steps):                                 # uninstrumented: the step time
+                flush_buf.zero_()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record(); fn(); b.record()
                 torch.cuda.synchronize()
                 ms.append(a.elapsed_time(b))
-                if meta["mode"] == "snapshot":
+            if snapshot:
+                lib.kp_profile_enable(1)
+                for _ in range(steps):                             # instrumented: plan / place split
+                    flush_buf.zero_()
+                    fn()
                     fa, fb = ctypes.c_float(), ctypes.c_float()
                     if lib.kp_profile_last_ms(ctypes.byref(fa), ctypes.byref(fb)) == 0:
+                        plan.append(fa.value)
                         place.append(fb.value)
-            lib.kp_profile_enable(0)
+                lib.kp_profile_enable(0)
             t = statistics.mean(ms) * 1e-3
-            e = {"workload": meta["desc"], "ms_per_step": t * 1e3, "pairs_per_sec": p * n / t, "pods_per_sec": p / t}
+            ok, k = c_oracle_check(nodes, pods, meta, res["out"][0][:4096].cpu().numpy())
+            e = {"workload": meta["desc"], "baseline_config": meta["config"], "nodes_eligible": n_el,
+                 "ms_per_step": t * 1e3, "pairs_per_sec": p * n_el / t, "pods_per_sec": p / t,
+                 "parity_vs_cpu_sample": ok, "c_oracle_pods_checked": k}
             if place:
-                tp = statistics.mean(place) * 1e-3
-                sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-                e["place_kernel_ms"] = tp * 1e3
-                e["issue_frac_3op"] = 3.0 * p * n / tp / (sm_count * 128 * measured_peaks()[1] * 1e6)
+                e["roofline"] = place_roofline(p, n_el, n, place, plan, ms, sm_count, sm_max_mhz, peak_src, sm_max_mhz,
+                                               peak_meas, hbm_peak, load_traffic(name), meta["per_pod"])
+            if not snapshot:
+                e["greedy"] = greedy_report(torch, placement, dn, rc, rm, strat, meta, res["out"], ws)
             extras[name] = e
         except Exception as ex:  # noqa: BLE001
             extras[name] = {"error": repr(ex)}
@@ -607,7 +805,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c4shard", "c5", "c5greedy"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD,
+                    choices=["c2", "c3", "c4", "c4shard", "c5", "c5greedy", "c5node"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--extra", action=argparse.BooleanOptionalAction, default=True)

@@ -105,6 +105,13 @@ int64_t kp_launch_count(void);
  * Process-global and not thread-safe; off by default (no events are recorded). */
 int kp_profile_enable(int enable);
 int kp_profile_last_ms(float *plan_ms, float *place_ms);
+/* Diagnostic with no counterpart in the reference: the MEASURED issue peak of the snapshot inner
+ * loop on the current device.  Runs the three instructions place_kernel executes per pod x node pair
+ * (subtract, test with predicate output, predicated update) on a shared-memory tile with nothing
+ * around them, in both update mixes the real kernel can use, for at least min_ms milliseconds on
+ * `stream`, and returns the best rate in pairs per second.  `scratch` = 256 bytes of device memory.
+ * Synchronises the stream.  bench.py reports it as roofline.peak_measured. */
+int kp_issue_peak(void *scratch, size_t scratch_bytes, double min_ms, void *stream, double *out_pairs_per_sec);
 
 /* ---- snapshot placement, device pointers ------------------------------------------
  * Replaces: one `_fallback_decision` call per pod (scheduler.py:521-559) over the SAME

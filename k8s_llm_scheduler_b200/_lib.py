@@ -55,6 +55,7 @@ SYMBOLS = {
     "kp_launch_count": (c_int64, []),
     "kp_profile_enable": (c_int, [c_int]),
     "kp_profile_last_ms": (c_int, [POINTER(ctypes.c_float), POINTER(ctypes.c_float)]),
+    "kp_issue_peak": (c_int, [c_void_p, c_size_t, c_double, c_void_p, POINTER(c_double)]),
     "kp_snapshot_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "kp_snapshot_place": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -276,6 +276,11 @@ int kp_profile_last_ms(float *plan_ms, float *place_ms)
     return KP_OK;
 }
 
+int kp_issue_peak(void *scratch, size_t scratch_bytes, double min_ms, void *stream, double *out_pairs_per_sec)
+{
+    return issue_peak_device(scratch, scratch_bytes, min_ms, (cudaStream_t)stream, out_pairs_per_sec);
+}
+
 int kp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor)
 {
     int count = 0;

@@ -236,6 +236,8 @@ int ingest_nodes_device(const kp_node_strings &in, int64_t *out_milli, int64_t *
 int cache_keys_device(const uint8_t *prefix, const int64_t *prefix_off, int64_t n_pods, const uint8_t *nodes_text,
                       int64_t nodes_len, uint8_t *out, cudaStream_t stream);
 int sm_count_cached();
+// kp_diag.cu: measured issue peak of the snapshot inner loop
+int issue_peak_device(void *scratch, size_t scratch_bytes, double min_ms, cudaStream_t stream, double *pairs_per_sec);
 // Ordinal of the current device, clamped to [0, kMaxDevices): index of per-device once-flags.  Function
 // attributes (opt-in shared memory sizes) belong to a device's context, so such flags are kept per device.
 constexpr int kMaxDevices = 64;

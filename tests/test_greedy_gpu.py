@@ -7,8 +7,8 @@ import pytest
 
 from k8s_llm_scheduler_b200 import synth
 from k8s_llm_scheduler_b200.tables import NodeTable, PodTable, strategy_id
-from tests.helpers import (COND, assert_same_f64, assert_same_idx, bits, device_greedy,
-                           oracle_greedy)
+from tests.helpers import (COND, assert_same_f64, assert_same_idx, bits, check_greedy_from_checkpoint,
+                           device_greedy, oracle_greedy, state_after)
 
 pytestmark = pytest.mark.gpu
 
@@ -212,6 +212,41 @@ def test_full_size_config3_greedy():
     o = oracle_greedy(nodes, head, 0, 1)
     assert_same_idx(idx[:30_000], o[0])
     assert_same_f64(score[:30_000], o[1])
+    # Checkpointed oracle runs: greedy is Markov in the node state, so the oracle restarted from the state
+    # the device's own decisions imply must continue identically.  The cluster has 414 448 free pod slots:
+    # checkpoints sit in the regime where trajectories run towards max_pods, straddle the depletion point
+    # (the last placement), and in the all-rejected tail.
+    free_slots = int((nodes.max_pods - nodes.pod_count)[nodes.ready != 0].clip(min=0).sum())
+    last_placed = int(np.nonzero(placed)[0][-1])
+    assert free_slots == 414_448 and int(placed.sum()) == free_slots and last_placed == free_slots - 1
+    for k in (200_000, 400_000, last_placed - 2_500, 700_000, 995_000):
+        check_greedy_from_checkpoint(nodes, pods, idx, score, k, 5_000, 0, 1, what=f"c3 checkpoint {k}")
+    final = state_after(nodes, idx)
+    assert np.array_equal(final.pod_count, pc)
+
+
+def test_full_size_config5_greedy_form():
+    """BASELINE config 5 in greedy form at full size: 20k heterogeneous nodes x 2M pods, per-pod strategies
+    (cluster of 2 CTAs with the st.async exchange), 30 % infeasible pods.  Conservation properties over the
+    whole run plus checkpointed oracle runs of 5 000 pods each, from the head to the tail."""
+    nodes, pods = synth.config5(20_000, 2_000_000)
+    idx, score, pc, cu, mu = device_greedy(nodes, pods, 0, 1, per_pod=True)
+    placed = idx >= 0
+    per_node = np.bincount(idx[placed], minlength=len(nodes))
+    assert np.array_equal(pc - nodes.pod_count, per_node)
+    assert (pc <= np.maximum(nodes.max_pods, nodes.pod_count)).all()
+    assert (per_node[nodes.ready == 0] == 0).all()
+    assert (score[~placed] == -1.0).all()
+    touched = per_node > 0
+    assert_same_f64(cu[touched], synth.usage_a3(pc[touched], nodes.max_pods[touched]), "final cpu usage")
+    assert_same_f64(cu[~touched], nodes.cpu_usage_pct[~touched], "untouched cpu usage")
+    # round_robin pods pile onto the fullest fitting node, the other two spread: all three kinds place pods
+    for sid in (0, 1, 2):
+        assert placed[pods.strategy_ids == sid].any()
+    last_placed = int(np.nonzero(placed)[0][-1])
+    cps = sorted({0, 250_000, 1_000_000, max(0, last_placed - 2_500), 1_600_000, 1_995_000})
+    for k in cps:
+        check_greedy_from_checkpoint(nodes, pods, idx, score, k, 5_000, 0, 1, per_pod=True, what=f"c5 checkpoint {k}")
 
 
 def test_tables_beyond_the_fast_path_capacity_use_the_fp64_kernel():

@@ -233,3 +233,19 @@ def test_c_oracle_matches_py_oracle_capacity_filter():
             assert [bits(x) for x in cs] == [bits(x) for x in gs]
             assert fpc.tolist() == [w.pod_count for w in work]
             assert [bits(x) for x in fcu] == [bits(w.cpu_usage_percent) for w in work]
+
+
+def test_oracle_restarted_from_a_checkpoint_continues_identically():
+    """The checkpoint helper the full-size GPU greedy tests rely on (tests/helpers.py: state_after), pinned on
+    the oracle itself: a run restarted from the state implied by its own first k decisions repeats the rest."""
+    from k8s_llm_scheduler_b200 import synth
+    from tests.helpers import check_greedy_from_checkpoint, oracle_greedy
+    nodes, pods = synth.config3(300, 30_000)                       # fills up around pod 16 000
+    o = oracle_greedy(nodes, pods, 0, 1)
+    assert (o[0] < 0).any()
+    for k in (0, 9_000, 15_500, 25_000):
+        check_greedy_from_checkpoint(nodes, pods, o[0], o[1], k, 3_000, 0, 1)
+    nodes, pods = synth.config5(1500, 40_000)
+    o = oracle_greedy(nodes, pods, 0, 1, per_pod=True)
+    for k in (0, 20_000, 37_000):
+        check_greedy_from_checkpoint(nodes, pods, o[0], o[1], k, 3_000, 0, 1, per_pod=True)

@@ -3,7 +3,8 @@ memory when they call us (GPU memory fully owned by another runtime's pool, or a
 budget that rules out cudaMalloc/cudaFree).  Its scratch is a fixed array inside the
 library, so consecutive calls reuse the same bytes: the second call must not see anything
 the first one left behind.  Checked bit-for-bit against kp_snapshot_place (which gets a
-fresh torch-allocated workspace), through the C ABI, on two calls in a row.
+fresh torch-allocated workspace) and against the CPU oracle, through the C ABI, on calls in
+a row.
 
 Collected last on purpose (file name): if it fails under -x every other test has already run.
 """
@@ -14,6 +15,7 @@ import numpy as np
 import pytest
 
 from k8s_llm_scheduler_b200 import synth
+from tests.helpers import assert_same_f64, assert_same_idx, oracle_snapshot
 
 pytestmark = pytest.mark.gpu
 
@@ -54,6 +56,10 @@ def test_two_calls_in_a_row_match_the_workspace_entry_point():
         assert torch.equal(got_idx, want_idx)
         assert np.array_equal(got_score.cpu().numpy().view(np.uint64), want_score.cpu().numpy().view(np.uint64))
         assert (got_idx >= -1).all()
+        oi, os_ = oracle_snapshot(nodes, pods, strategy if strategy != "per_pod" else 0, filter_mode,
+                                  per_pod=strategy == "per_pod")
+        assert_same_idx(got_idx.cpu().numpy(), oi)
+        assert_same_f64(got_score.cpu().numpy(), os_)
 
 
 def test_sizes_beyond_the_built_in_scratch_are_rejected():
