@@ -617,6 +617,32 @@ def greedy_report(torch, placement, dn, rc, rm, strat, meta, out, ws):
     return rep
 
 
+def session_probe(torch, placement, dev, nodes, pods, meta, steps=30):
+    """kp_session_snapshot on pinned host buffers: table sent with every call (what the reference's per-pod
+    loop does) against a table made resident once with kp_session_set_nodes, whose node plan is then reused."""
+    from k8s_llm_scheduler_b200.tables import NODE_COLUMNS
+    p = len(pods)
+    hn = {k: torch.as_tensor(getattr(nodes, k)).pin_memory() for k in NODE_COLUMNS}
+    hp = (torch.as_tensor(pods.req_cpu_milli).pin_memory(), torch.as_tensor(pods.req_mem_bytes).pin_memory(), None)
+    ho = (torch.empty(p, dtype=torch.int64).pin_memory(), torch.empty(p, dtype=torch.float64).pin_memory())
+    out = {}
+    with placement.Session(dev.index or 0, max_nodes=len(nodes), max_pods=p) as sess:
+        for rnd in range(3):                                   # alternate the two forms; best median of the rounds
+            for label, table in (("table_per_call_ms", hn), ("resident_table_ms", None)):
+                sess.set_nodes(hn)
+                for _ in range(10):
+                    sess.snapshot(table, hp, meta["strategy"], meta["filter"], out=ho)
+                ts = []
+                for _ in range(steps):
+                    t = time.perf_counter()
+                    sess.snapshot(table, hp, meta["strategy"], meta["filter"], out=ho)
+                    ts.append(time.perf_counter() - t)
+                out[label] = min(out.get(label, 1e9), statistics.median(ts) * 1e3)
+        ok, _ = c_oracle_check(nodes, pods, meta, ho[0].numpy())
+    out["parity_vs_cpu_sample"] = ok
+    return out
+
+
 def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, world, rank, local):
     raise SystemExit("workload c5node: node-sharded snapshot is not wired into bench.py yet")
 
@@ -676,6 +702,8 @@ def run_extras(args, torch, placement, lib, dev, peak_meas):
                                                peak_meas, hbm_peak, load_traffic(name), meta["per_pod"])
             if not snapshot:
                 e["greedy"] = greedy_report(torch, placement, dn, rc, rm, strat, meta, res["out"], ws)
+            if name == "c2":
+                e["host_api"] = session_probe(torch, placement, dev, nodes, pods, meta)
             extras[name] = e
         except Exception as ex:  # noqa: BLE001
             extras[name] = {"error": repr(ex)}

@@ -103,6 +103,9 @@ struct kp_session {
     unsigned char *h_stage = nullptr;
     size_t stage_bytes = 0;
     int direct = 3;                     // bit 0: pinned pod columns read in place, bit 1: pinned results written in place
+    // node plan kept in d_ws for the resident table (kp_session_set_nodes + snapshots with nodes == NULL):
+    // signature of the last snapshot's plan, 0 = none; cleared whenever the table or the workspace changes hands
+    unsigned long long plan_sig = 0;
 };
 
 namespace {
@@ -179,6 +182,7 @@ int upload_nodes(kp_session *s, const kp_node_table *nodes)
     }
     s->h2d += 6 * (int64_t)b8 + n;
     s->resident_nodes = n;
+    s->plan_sig = 0;                    // a new table: whatever plan the workspace holds is stale
     return KP_OK;
 }
 
@@ -537,8 +541,15 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
         tuning.flow = s->d_flow;
         tuning.flow_window = kFlowWindowCtas;
     }
+    // resident table, same strategy / filter / layout as the snapshot before: its node plan is still in d_ws
+    unsigned long long sig = 0;
+    tuning.plan_sig = &sig;
+    tuning.reuse_plan = s->plan_sig != 0 &&
+                        s->plan_sig == snapshot_plan_signature(dn.n_nodes, dp.n_pods, dp.strategy_ids != nullptr, strategy, filter_mode);
+    s->plan_sig = 0;
     st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream, tuning);
     if (st != KP_OK) return fail_drained(s, st);
+    s->plan_sig = sig;
     if (b8) {
         if (!out_in_place) {
             KP_CUDA(cudaMemcpyAsync(out_node_idx, d_idx, b8, cudaMemcpyDeviceToHost, s->stream));
@@ -582,6 +593,7 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
     int64_t *d_pc = reinterpret_cast<int64_t *>(s->d_state);
     double *d_cu = reinterpret_cast<double *>(s->d_state + ncol);
     double *d_mu = reinterpret_cast<double *>(s->d_state + 2 * ncol);
+    s->plan_sig = 0;                    // the greedy kernels take over the workspace
     st = greedy_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, d_pc, d_cu, d_mu, s->d_ws,
                              s->ws_bytes, s->stream);
     if (st != KP_OK) return fail_drained(s, st);

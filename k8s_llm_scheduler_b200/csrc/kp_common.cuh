@@ -205,7 +205,15 @@ struct PlaceTuning {
     int resident_cap = 0;          // > 0: at most this many CTAs resident per SM
     unsigned *flow = nullptr;      // three zeroed device words (arrived, finished, spare flag): pace the in-place reads of pinned pod rows
     unsigned flow_window = 0;      // CTAs whose rows may be in flight at once
+    // Node-plan reuse (session with a resident node table): `plan_sig` receives a signature of everything the
+    // plan in the workspace depends on besides the node table itself (strategies, filter, layout); with
+    // `reuse_plan` set the caller vouches that the workspace still holds the plan of an earlier call on the SAME
+    // node table with the SAME signature, and the plan kernels are skipped.
+    bool reuse_plan = false;
+    unsigned long long *plan_sig = nullptr;
 };
+// signature the session compares before it sets reuse_plan (0 = this call's plan cannot be reused)
+unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool per_pod, int strategy, int filter_mode);
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                           int filter_mode, int64_t *out_idx, double *out_score, void *ws,
                           size_t ws_bytes, cudaStream_t stream, const PlaceTuning &tuning = PlaceTuning());

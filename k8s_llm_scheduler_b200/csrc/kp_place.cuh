@@ -52,6 +52,8 @@ struct PlaceParams {
     int tiles_per_seg_wide;            // tiles (of 512 nodes) per node segment; the packed form uses half
     int small_table_len;               // > 0: small-table plan -- packed form, thresholds sorted WITH duplicates
                                        // (n_nodes of them), table length known on the host: no header reads
+    long long share_q;                 // place_small_kernel, one strategy: warp g owns share_q pods, the first share_r
+    int share_r;                       // warps one more (the split is made on the host: no 64-bit division per warp)
     const double *uniq;                // [2][npad] ascending distinct thresholds
     const uint2 *ab;                   // [3][npad] best-first {RA, RB}
     const uint32_t *packed;            // [3][npad] best-first packed ranks
@@ -423,6 +425,237 @@ place_kernel(const PlaceParams p)
         if (atomicAdd(p.flow + 1, 1u) == gridDim.x - 1) {
             p.flow[0] = 0u;
             p.flow[1] = 0u;
+        }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------
+// place_small_kernel: small tables (the one-launch plan, <= 8192 nodes) -- NODES in registers
+// ---------------------------------------------------------------------------------------
+// place_kernel keeps pods in registers and broadcasts nodes from shared memory; its fixed costs
+// (a CTA-wide prologue, tile staging, barriers, 11 loop instructions per four nodes spread over
+// only R = 4 pods per lane) are what a 1 000-node table cannot amortise: 14.1 M warp instructions
+// for 9.4 M useful on config 2.  Here the roles are swapped.  A warp holds a slice of the
+// best-first table in registers -- NPT packed words per lane, four consecutive table positions per
+// 16-byte load -- and its pods are broadcast one after the other: per pod x node pair the same
+// three instructions (subtract, LOP3 with predicate output, predicated update; the update
+// alternates between the ALU and the FMA pipe from pod to pod), the position is an immediate
+// operand (no index arithmetic, no loop), and one REDUX.MIN over the lanes per pod yields the
+// best-ranked fitting node of the slice.  Per pod: 3 NPT + ~8 instructions.
+//
+// Warps are autonomous: each takes at most 32 pods at a time (lane = pod for the request ->
+// rank prologue and for the position -> node / score epilogue, coalesced both ways), so any number
+// of pods splits evenly over all resident warps, no barrier follows the start-up, and warps in
+// their prologue or epilogue overlap with warps that scan.  Tables longer than 32 NPT are
+// scanned slice by slice (re-loaded from L1/L2 per slice), the running minimum kept per pod.
+#ifndef KP_SMALL_UPDATE
+#define KP_SMALL_UPDATE 1         // candidate update: 0 = alternate VIMNMX / IMAD per pod, 1 = IMAD for every pod, 2 = VIMNMX for every pod
+#endif
+constexpr int kSmallWarps = 8;
+constexpr int kSmallThreads = 32 * kSmallWarps;
+constexpr int kSmallUniqStage = 2048;                  // sorted thresholds staged in shared memory up to this many nodes
+constexpr uint32_t kSmallNone = 0x7fffff00u;           // "no node": above every position, survives + lane
+
+// The update writes the position (an immediate) over `best`.  Both forms read `best` on purpose: a plain
+// predicated move of a constant gets its constant hoisted into a register by ptxas (one register per node
+// slot), and `one * imm` is hoisted the same way.  FMA == true: best = best * zero + imm (IMAD, FMA pipe);
+// FMA == false: best = min(best, imm) (VIMNMX, ALU pipe; positions only fall during the scan); `zero` is a run-time 0.
+// The subtraction is written as x * (-1) + w with a run-time -1 so that it issues as IMAD on the FMA pipe:
+// per pair the FMA pipe then carries 1.5 instructions (subtract, every other update) and the ALU pipe 1.5
+// (test, every other update) -- the two 16-lane pipes are the issue bound.
+template <bool FMA, int IMM>
+__device__ __forceinline__ void small_step(uint32_t &best, uint32_t x, uint32_t w, uint32_t zero, uint32_t minus1)
+{
+    if (FMA)
+        asm volatile("{ .reg .pred p; .reg .b32 t, d; mad.lo.u32 t, %2, %5, %1; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0;\n"
+                     "  @!p mad.lo.u32 %0, %0, %3, %4; }"
+                     : "+r"(best) : "r"(w), "r"(x), "r"(zero), "n"(IMM), "r"(minus1));
+    else
+        asm volatile("{ .reg .pred p; .reg .b32 t, d; mad.lo.u32 t, %2, %4, %1; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0;\n"
+                     "  @!p min.u32 %0, %0, %3; }"
+                     : "+r"(best) : "r"(w), "r"(x), "n"(IMM), "r"(minus1));
+}
+
+template <int NPT, int K, int NP>
+struct SmallScan {
+    // nodes K-1 .. 0 of the slice against NP pods: worst -> best, "fits" overwrites
+    static __device__ __forceinline__ void run(uint32_t (&b)[NP], const uint32_t (&x)[NP], const uint32_t (&w)[NPT], uint32_t zero,
+                                               uint32_t minus1)
+    {
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            if (KP_SMALL_UPDATE == 1 || (KP_SMALL_UPDATE == 0 && (q & 1)))
+                small_step<true, 128 * ((K - 1) / 4) + (K - 1) % 4>(b[q], x[q], w[K - 1], zero, minus1);
+            else
+                small_step<false, 128 * ((K - 1) / 4) + (K - 1) % 4>(b[q], x[q], w[K - 1], zero, minus1);
+        }
+        SmallScan<NPT, K - 1, NP>::run(b, x, w, zero, minus1);
+    }
+};
+template <int NPT, int NP>
+struct SmallScan<NPT, 0, NP> {
+    static __device__ __forceinline__ void run(uint32_t (&)[NP], const uint32_t (&)[NP], const uint32_t (&)[NPT], uint32_t, uint32_t) {}
+};
+
+// NP pods (lanes first .. first + NP - 1 of the pass hold their requests and running minima) against the slice in w
+template <int NPT, int NP>
+__device__ __forceinline__ void small_group(const uint32_t (&w)[NPT], uint32_t xmine, uint32_t &mine, int first, int lane,
+                                            uint32_t slice_pos, uint32_t zero, uint32_t minus1)
+{
+    uint32_t x[NP], b[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) {
+        x[q] = __shfl_sync(0xffffffffu, xmine, first + q);
+        b[q] = kSmallNone;
+    }
+    SmallScan<NPT, NPT, NP>::run(b, x, w, zero, minus1);
+#pragma unroll
+    for (int q = 0; q < NP; ++q) {
+        const uint32_t r = __reduce_min_sync(0xffffffffu, b[q] + slice_pos);
+        if (lane == first + q) mine = min(mine, r);
+    }
+}
+
+// two searches of the same depth side by side (independent load chains): #{a[i] < xa} and #{b[i] < xb}
+__device__ __forceinline__ void lower_bound_lt_pair(const double *a, const double *b, int n, double xa, double xb,
+                                                    uint32_t &ra, uint32_t &rb)
+{
+    int la = 0, lb = 0;
+    for (int step = 1 << (31 - __clz(n | 1)); step > 0; step >>= 1) {
+        const int na = la + step, nb = lb + step;
+        const double va = a[min(na, n) - 1], vb = b[min(nb, n) - 1];
+        if (na <= n && va < xa) la = na;
+        if (nb <= n && vb < xb) lb = nb;
+    }
+    ra = (uint32_t)la;
+    rb = (uint32_t)lb;
+}
+
+// w[4 j .. 4 j + 3] = table[slice + 128 j + 4 lane .. + 3]: one 16-byte load per four nodes.  The table is
+// padded (with entries that fit nothing) far enough that no bounds check is needed.
+template <int NPT>
+__device__ __forceinline__ void small_load_slice(uint32_t (&w)[NPT], const uint32_t *table, int slice, int lane)
+{
+    static_assert(NPT % 4 == 0, "node words are loaded four at a time");
+    const uint4 *src = reinterpret_cast<const uint4 *>(table + (size_t)slice * 32 * NPT) + lane;
+#pragma unroll
+    for (int j = 0; j < NPT / 4; ++j) {
+        const uint4 v = src[32 * j];
+        w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
+    }
+}
+
+#ifndef KP_SMALL_GROUP
+#define KP_SMALL_GROUP 4          // pods scanned together (4 or 8; measured equal on config 2): the per-group overhead is shared by this many pods
+#endif
+#ifndef KP_SMALL_OCC32
+#define KP_SMALL_OCC32 3          // resident CTAs per SM asked of the compiler for NPT <= 32
+#endif
+constexpr int small_occupancy(int npt) { return npt <= 32 ? KP_SMALL_OCC32 : (npt <= 40 ? 3 : 2); }
+
+template <int NPT>
+__global__ void __launch_bounds__(kSmallThreads, small_occupancy(NPT))
+place_small_kernel(const PlaceParams p)
+{
+    __shared__ __align__(16) double s_uniq[2][kSmallUniqStage];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned gwarp = blockIdx.x * kSmallWarps + (tid >> 5), nwarps = gridDim.x * kSmallWarps;
+    const int n = p.n_nodes;                                  // thresholds: n sorted values per dimension (duplicates kept)
+    const int nslices = (p.small_table_len + 32 * NPT - 1) / (32 * NPT);   // best-first table entries to scan, in slices
+    const bool uniform = p.uniform_strategy >= 0;
+
+    // this warp's pods.  One strategy: a contiguous, balanced share of all pods.  Per-pod strategies: 32-slot
+    // batches of the strategy-grouped slot space, strided over the warps.
+    long long lo, hi;
+    if (uniform) {
+        lo = p.share_q * gwarp + min(gwarp, (unsigned)p.share_r);
+        hi = lo + p.share_q + (gwarp < (unsigned)p.share_r ? 1 : 0);
+    } else {
+        lo = (long long)gwarp * 32;
+        hi = ((p.n_pods + 31) / 32 + (kMaxStrategies - 1)) * 32;
+    }
+    const long long stride = uniform ? 32 : (long long)nwarps * 32;
+
+    // before the node plan is needed (programmatic dependent launch): the first requests
+    long long raw_c = 0, raw_m = 0;
+    bool pre = uniform && lo + lane < hi;
+    if (pre) { raw_c = p.req_cpu[lo + lane]; raw_m = p.req_mem[lo + lane]; }
+    asm volatile("griddepcontrol.wait;" ::: "memory");        // the plan kernel has completed
+
+    uint32_t w[NPT];
+    int loaded = -1;                                          // strategy * 8 + slice held in w
+    if (uniform && nslices == 1) {                            // the whole table: on its way before anything else
+        small_load_slice<NPT>(w, p.packed + (size_t)p.uniform_strategy * p.npad, 0, lane);
+        loaded = p.uniform_strategy * 8;
+    }
+    // sorted thresholds: in shared memory when they fit (searched at shared-memory latency; every warp of the
+    // kernel is in its first prologue at the same time, so that latency is exposed), else from L1 / L2
+    const bool staged = n <= kSmallUniqStage;
+    if (staged) {
+        for (int i = tid; i < n; i += kSmallThreads) {
+            s_uniq[0][i] = p.uniq[i];
+            s_uniq[1][i] = p.uniq[p.npad + i];
+        }
+        __syncthreads();                                      // the only block-wide barrier
+    }
+    const double *ua = staged ? s_uniq[0] : p.uniq, *ub = staged ? s_uniq[1] : p.uniq + p.npad;
+    const uint32_t zero = (uint32_t)p.one - 1u;               // 0, but not to the compiler (see small_step)
+    const uint32_t minus1 = zero - (uint32_t)p.one;           // -1
+
+    for (long long s0 = lo; s0 < hi; s0 += stride) {
+        int s = p.uniform_strategy, count;
+        if (uniform) {
+            count = (int)min((long long)32, hi - s0);
+        } else {
+            long long gb[kMaxStrategies];
+            group_begins(p.hdr, 32, gb);
+            s = 0;
+#pragma unroll
+            for (int g = 1; g < kMaxStrategies; ++g) if (s0 >= gb[g]) s = g;
+            const long long left = (long long)p.hdr->group_count[s] - (s0 - gb[s]);
+            if (left <= 0) continue;                          // warp-uniform
+            count = (int)min((long long)32, left);
+        }
+        // ---- prologue: lane = pod; request -> packed threshold ranks ----
+        uint32_t xmine = kSwarDeadPod;
+        if (lane < count) {
+            if (!pre) {
+                const long long pod = p.perm ? (long long)p.perm[s0 + lane] : s0 + lane;
+                raw_c = p.req_cpu[pod];
+                raw_m = p.req_mem[pod];
+            }
+            uint32_t ra, rb;
+            lower_bound_lt_pair(ua, ub, n, req_cores(raw_c), req_gib(raw_m), ra, rb);
+            xmine = ((rb + 1u) << 16) | (ra + 1u);
+        }
+        pre = false;
+        uint32_t mine = kSmallNone;
+        const uint32_t *table = p.packed + (size_t)s * p.npad;
+        for (int sl = nslices - 1; sl >= 0; --sl) {
+            if (loaded != s * 8 + sl) {                       // one slice: loaded once per strategy, not per pass
+                small_load_slice<NPT>(w, table, sl, lane);
+                loaded = s * 8 + sl;
+            }
+            const uint32_t slice_pos = (uint32_t)(sl * 32 * NPT + 4 * lane);
+#pragma unroll 1
+            for (int g = 0; g + KP_SMALL_GROUP <= count; g += KP_SMALL_GROUP)
+                small_group<NPT, KP_SMALL_GROUP>(w, xmine, mine, g, lane, slice_pos, zero, minus1);
+            if (KP_SMALL_GROUP == 8 && (count & 4)) small_group<NPT, 4>(w, xmine, mine, count & ~7, lane, slice_pos, zero, minus1);
+            if (count & 2) small_group<NPT, 2>(w, xmine, mine, count & ~3, lane, slice_pos, zero, minus1);
+            if (count & 1) small_group<NPT, 1>(w, xmine, mine, count & ~1, lane, slice_pos, zero, minus1);
+        }
+        // ---- epilogue: lane = pod; rank position -> node index and score ----
+        if (lane < count) {
+            const long long pod = p.perm ? (long long)p.perm[s0 + lane] : s0 + lane;
+            long long idx = -1;
+            double sc = -1.0;
+            if (mine < kSmallNone) {
+                idx = p.order[(size_t)s * p.npad + mine];
+                sc = p.score_by_pos[(size_t)s * p.npad + mine];
+            }
+            p.out_idx[pod] = idx;
+            p.out_score[pod] = sc;
         }
     }
 }

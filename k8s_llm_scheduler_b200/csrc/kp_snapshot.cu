@@ -41,6 +41,7 @@ namespace kp {
 // workspace layout
 // ---------------------------------------------------------------------------------------
 constexpr int kArgmaxMaxBlocks = 256;
+constexpr int kSmallPad = 1536;
 constexpr int kMaxChunkPods = 2048;
 
 struct SnapLayout {
@@ -59,7 +60,9 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     SnapLayout L{};
     L.n = n;
     L.p = p;
-    L.npad = (n + 3) / 4 * 4 + 4;
+    // small tables: place_small_kernel loads whole register slices without bounds checks, up to 256 entries
+    // past the table per slice (kSmallPad covers five slices); the plan fills the padding with entries that fit nothing
+    L.npad = (n + 3) / 4 * 4 + 4 + (n > kSmallMaxNodes ? 0 : kSmallPad);
     L.slots = p + 3 * kMaxChunkPods;
     L.chunks = L.slots / 32 + 1;
     const bool big = n > kSmallMaxNodes;                 // multi-kernel plan, node segments possible
@@ -103,6 +106,17 @@ size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod)
 bool snapshot_single_pass(int64_t n_nodes, bool per_pod)
 {
     return n_nodes <= kSmallMaxNodes && !per_pod;
+}
+
+// What a node plan depends on besides the node table: which strategy tables were built, the filter, and where
+// the arrays sit in the workspace (for large tables the layout moves with the pod count).  Plans with per-pod
+// strategies are not reused: their header carries per-call pod group counters.
+unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool per_pod, int strategy, int filter_mode)
+{
+    if (per_pod || filter_mode != KP_FILTER_CAPACITY || n_nodes <= 0) return 0ull;
+    const SnapLayout L = make_layout(n_nodes, n_pods, false);
+    return 0x8000000000000000ull | ((unsigned long long)canon_strategy(strategy) << 60) |
+           ((unsigned long long)(L.off_keys & 0xfffffffffffull) << 16) | (unsigned long long)(n_nodes & 0xffff);
 }
 
 static NodePtrs node_ptrs(const kp_node_table &t)
@@ -443,6 +457,55 @@ static int launch_place_cfg(int c, const PlaceParams &pp, dim3 grid, cudaStream_
     return KP_OK;
 }
 
+// place_small_kernel (tables of the one-launch plan): NPT = node words per lane, a multiple of 8 up to 64
+template <int NPT>
+static cudaError_t launch_small_pdl(const PlaceParams &pp, int ctas, cudaStream_t stream)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)ctas, 1, 1);
+    cfg.blockDim = dim3(kSmallThreads, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, place_small_kernel<NPT>, pp);
+}
+
+static int launch_place_small(const PlaceParams &pp, int64_t n, int64_t P, bool per_pod, cudaStream_t stream)
+{
+    const int nslices = (int)((n + 1791) / 1792);                       // at most 56 words per lane and slice
+    int npt = (int)((n + 32 * nslices - 1) / (32 * nslices));
+    npt = std::max(8, (npt + 7) / 8 * 8);
+    const int occ = small_occupancy(npt);
+    const int64_t max_ctas = (int64_t)sm_count_cached() * occ;
+    // enough pods per warp to pay for loading its table slice (16), otherwise every resident warp gets a share
+    const int64_t want = per_pod ? ((P + 31) / 32 + kMaxStrategies - 1 + kSmallWarps - 1) / kSmallWarps
+                                 : (P + 16 * kSmallWarps - 1) / (16 * kSmallWarps);
+    int ctas = (int)std::max<int64_t>(1, std::min(want, max_ctas));
+    if (const char *v = getenv("KP_SMALL_CTAS")) ctas = std::max(1, atoi(v));       // experiments only
+    PlaceParams pq = pp;
+    const int64_t nwarps = (int64_t)ctas * kSmallWarps;
+    pq.share_q = P / nwarps;
+    pq.share_r = (int)(P % nwarps);
+    cudaError_t e = cudaErrorInvalidValue;
+    switch (npt) {
+        case 8: e = launch_small_pdl<8>(pq, ctas, stream); break;
+        case 16: e = launch_small_pdl<16>(pq, ctas, stream); break;
+        case 24: e = launch_small_pdl<24>(pq, ctas, stream); break;
+        case 32: e = launch_small_pdl<32>(pq, ctas, stream); break;
+        case 40: e = launch_small_pdl<40>(pq, ctas, stream); break;
+        case 48: e = launch_small_pdl<48>(pq, ctas, stream); break;
+        case 56: e = launch_small_pdl<56>(pq, ctas, stream); break;
+        default: break;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "place_small_kernel launch");
+    count_launch();
+    return KP_OK;
+}
+
 // Side streams for the independent radix sorts of the large-table plan (one pool per device, made on
 // first use and kept for the life of the process).  NULL = could not be created: the sorts then run one
 // after the other on the caller's stream.
@@ -536,7 +599,12 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         const int c = atoi(force);
         if (c >= 0 && c < kNumPlaceCfgs) cfg = c;
     }
-    const int chunk_pods = kPlaceCfgs[cfg].chunk;
+    // small tables: the nodes-in-registers kernel (kp_place.cuh); its per-pod strategy groups are 32 slots wide
+    // (pinned host pod rows read in place keep the paced place_kernel: the order in which the rows cross the
+    // host link matters more there than the instruction count)
+    bool use_small = !big && !(tuning.flow && flow_window > 0 && !per_pod);
+    if (const char *v = getenv("KP_SMALL_OLD")) if (v[0] == '1') use_small = false;   // experiments only
+    const int chunk_pods = use_small ? 32 : kPlaceCfgs[cfg].chunk;
     const int64_t n_chunks = (P + chunk_pods - 1) / chunk_pods + (per_pod ? kMaxStrategies - 1 : 0);
     int nseg = 1, tiles_per_seg = ntiles_wide;
     if (max_nseg > 1) {
@@ -570,7 +638,13 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
 
     ProfileEvents &pe = profile_events();
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e0, stream));
-    if (!big) {
+    const unsigned long long sig = snapshot_plan_signature(n, P, per_pod, strategy, filter_mode);
+    if (tuning.plan_sig) *tuning.plan_sig = sig;
+    if (tuning.reuse_plan && sig != 0ull) {
+        // the workspace holds this table's plan: only the per-call merge counters of the segmented form are reset
+        if (big && L.zero_bytes > L.off_chunk_done)
+            KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.zero_bytes - L.off_chunk_done, stream));
+    } else if (!big) {
         // no sort, no memset, one launch: every node counts its own sorted positions
         const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
         plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(t, strat_mask, po);
@@ -648,18 +722,19 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.order = po.order;
     pp.score = po.score;
     pp.score_by_pos = po.score_pos;
-    pp.small_table_len = (!big && !per_pod) ? (int)((n + 3) / 4 * 4) : 0;
+    pp.small_table_len = use_small ? (int)n : ((!big && !per_pod) ? (int)((n + 3) / 4 * 4) : 0);
     pp.hdr = hdr;
     pp.chunk_done = reinterpret_cast<uint32_t *>(w + L.off_chunk_done);
     pp.best_pos = best_pos;
     pp.out_idx = (long long *)out_idx;
     pp.out_score = out_score;
     // pacing applies to the kernels that fetch a CTA's requests up front (node splits, one strategy)
-    const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && kPlaceCfgs[cfg].nsplit > 1;
+    const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && !use_small && kPlaceCfgs[cfg].nsplit > 1;
     pp.flow = paced ? tuning.flow : nullptr;
     pp.flow_window = flow_window;
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e1, stream));
-    const int st = launch_place_cfg(cfg, pp, dim3((unsigned)n_chunks, (unsigned)nseg, 1), stream, resident_cap);
+    const int st = use_small ? launch_place_small(pp, n, P, per_pod, stream)
+                             : launch_place_cfg(cfg, pp, dim3((unsigned)n_chunks, (unsigned)nseg, 1), stream, resident_cap);
     if (st == KP_OK && pe.enabled) {
         KP_CUDA(cudaEventRecord(pe.e2, stream));
         pe.valid = true;

@@ -260,6 +260,52 @@ def test_session_host_api_matches_device_api():
             s.snapshot(nodes, PodTable.from_columns(np.zeros(40_000), np.zeros(40_000)), 0, 1)
 
 
+@pytest.mark.parametrize("n", [1000, 2500, 12_000])
+def test_session_resident_table_reuses_its_node_plan(n):
+    """kp_session_set_nodes keeps the table on the device; snapshots with nodes=None that follow with the same
+    strategy / filter reuse the node plan of the snapshot before (no plan kernels).  Every answer must stay
+    the oracle's, whatever happens in between: other pods, another strategy, a greedy call on the same
+    workspace, a new table."""
+    from k8s_llm_scheduler_b200 import placement
+    from k8s_llm_scheduler_b200.placement import Session
+    nodes, pods = synth.config5(n, 30_000, seed=50 + n)
+    other, _ = synth.config5(n, 1, seed=51 + n)
+    a = PodTable.from_columns(pods.req_cpu_milli[:20_000], pods.req_mem_bytes[:20_000])
+    b = PodTable.from_columns(pods.req_cpu_milli[20_000:], pods.req_mem_bytes[20_000:])
+    lib = placement._lib.load()
+    with Session(0, max_nodes=n, max_pods=30_000) as s:
+        s.set_nodes(nodes)
+
+        def check(table, part, strat, mode=1, per_pod=False):
+            before = placement.launch_count()
+            gi, gs = s.snapshot(None, part, strat, mode)
+            oi, os_ = oracle_snapshot(table, part, strat, mode, per_pod=per_pod)
+            assert_same_idx(gi, oi)
+            assert_same_f64(gs, os_)
+            return placement.launch_count() - before
+
+        first = check(nodes, a, 0)
+        again = check(nodes, a, 0)
+        assert again < first and again == 1                    # only the placement kernel ran
+        assert check(nodes, b, 0) == (1 if n <= 8192 else first)   # large tables: the layout moves with the pod count
+        assert check(nodes, b, 1) == first                     # another strategy: its table is not in the plan
+        assert check(nodes, b, 1) == 1
+        assert check(nodes, a, 1, mode=0) >= 1                 # the reference's own filter has no plan
+        assert check(nodes, a, 1) == first
+        with_ids = PodTable.from_columns(a.req_cpu_milli, a.req_mem_bytes, pods.strategy_ids[:20_000])
+        check(nodes, with_ids, 0, per_pod=True)                # per-pod strategies: never reused ...
+        assert check(nodes, a, 1) == first                     # ... and they invalidate what was there
+        assert check(nodes, a, 1) == 1
+        s.greedy(None, PodTable.from_columns(a.req_cpu_milli[:3000], a.req_mem_bytes[:3000]), 1, 1)   # takes the workspace
+        assert check(nodes, a, 1) == first
+        s.set_nodes(other)                                     # a new table
+        assert check(other, a, 1) == first
+        assert check(other, b, 1) == (1 if n <= 8192 else first)
+        gi, _ = s.snapshot(nodes, a, 1, 1)                     # table passed with the call: planned afresh
+        assert_same_idx(gi, oracle_snapshot(nodes, a, 1, 1)[0])
+    assert lib is not None
+
+
 def test_session_inputs_that_need_conversion_stay_alive_for_the_call():
     """Columns of the 'wrong' dtype or layout (bool ready, int32 counts, Python lists, strided views, float
     tensors) are converted to temporaries; the temporaries must live until kp_session_snapshot has returned."""

@@ -10,7 +10,7 @@ import bench  # noqa: E402
 from k8s_llm_scheduler_b200 import placement  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "c2"
-nodes, pods, meta = bench.make_workload(name, 0)
+nodes, pods, meta = bench.make_workload(name)
 dev = torch.device("cuda:0")
 dn = placement.nodes_to_device(nodes, dev)
 rc = torch.as_tensor(pods.req_cpu_milli).to(dev)

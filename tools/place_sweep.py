@@ -9,7 +9,7 @@ from k8s_llm_scheduler_b200 import _lib, placement
 import bench
 
 def run(name, steps=5):
-    nodes, pods, meta = bench.make_workload(name, 0)
+    nodes, pods, meta = bench.make_workload(name)
     dev = torch.device("cuda", 0)
     dn = placement.nodes_to_device(nodes, dev)
     rc = torch.as_tensor(pods.req_cpu_milli).to(dev); rm = torch.as_tensor(pods.req_mem_bytes).to(dev)
@@ -32,7 +32,7 @@ for w in (sys.argv[1:] or ["c2", "c4shard", "c5"]):
 
 def loop_avg(name, iters=300):
     """Average device time per call over many back-to-back calls (event resolution is ~2 us)."""
-    nodes, pods, meta = bench.make_workload(name, 0)
+    nodes, pods, meta = bench.make_workload(name)
     dev = torch.device("cuda", 0)
     dn = placement.nodes_to_device(nodes, dev)
     rc = torch.as_tensor(pods.req_cpu_milli).to(dev); rm = torch.as_tensor(pods.req_mem_bytes).to(dev)

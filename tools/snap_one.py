@@ -8,7 +8,7 @@ import bench  # noqa: E402
 from k8s_llm_scheduler_b200 import placement  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "c5"
-nodes, pods, meta = bench.make_workload(name, 0)
+nodes, pods, meta = bench.make_workload(name)
 dn = placement.nodes_to_device(nodes, "cuda:0")
 rc = torch.as_tensor(pods.req_cpu_milli).cuda()
 rm = torch.as_tensor(pods.req_mem_bytes).cuda()
