@@ -150,6 +150,44 @@ int kp_snapshot_place_noalloc(const kp_node_table *nodes, const kp_pod_table *po
                               int filter_mode, int64_t *out_node_idx, double *out_score,
                               void *stream);
 
+/* ---- snapshot placement with the NODES sharded over several GPUs, device pointers ------------
+ * Replaces the same P independent `_fallback_decision` calls (scheduler.py:521-559) when the node list is
+ * split over W ranks (one process per GPU): rank r holds the contiguous slice of the list that starts at
+ * global index node_offset (offsets grow with the rank), every rank passes the same pods, and the per-pod
+ * winner over the whole list -- strict '>' with first-in-list-order ties, scheduler.py:547 -- is reduced
+ * across the ranks by this library's kernels over peer-mapped memory (NVLink; CUDA IPC), with no host
+ * round trip and no collective library on the data path.  Pods are owned in W contiguous shards
+ * (first n_pods % W shards one longer): rank r receives the results of shard r.  Capacity filter only.
+ *
+ * A kp_exchange owns this rank's share of the exchange memory.  Set-up, once: kp_exchange_create on every
+ * rank, kp_exchange_handle -> 64 opaque bytes, gathered from all ranks by the caller (any transport) and
+ * given to kp_exchange_connect in rank order.  kp_exchange_connect_local links exchanges that live in ONE
+ * process (several GPUs, or several emulated ranks on one GPU) without IPC.
+ *
+ * kp_snapshot_place_node_sharded = kp_ns_keys + kp_ns_place + kp_ns_reduce, all stream-ordered and
+ * asynchronous; every rank must make the same calls in the same order.  (The three steps are separate so
+ * that ranks emulated on ONE device can be driven in lock step: a kernel there must never wait for a
+ * kernel that has not been launched yet.)  A rank that waits more than 4 s for a peer gives up and sets
+ * the error word that kp_exchange_error reads (after synchronising): the results are then invalid.
+ * Workspace: kp_snapshot_workspace_bytes(local n_nodes, n_pods, per_pod_strategy).
+ */
+typedef struct kp_exchange kp_exchange;
+int kp_exchange_create(int device, int rank, int world, int64_t max_pods, int64_t max_local_nodes, kp_exchange **out);
+int kp_exchange_handle(kp_exchange *ex, unsigned char *out_handle64);
+int kp_exchange_connect(kp_exchange *ex, const unsigned char *handles /* world x 64 bytes, rank order */);
+int kp_exchange_connect_local(kp_exchange *ex, kp_exchange *const *all /* world exchanges, rank order */);
+void kp_exchange_destroy(kp_exchange *ex);
+int kp_exchange_error(kp_exchange *ex, int *out_error);
+int kp_ns_keys(kp_exchange *ex, const kp_node_table *local_nodes, int64_t node_offset, int strategy,
+               int per_pod_strategy, void *stream);
+int kp_ns_place(kp_exchange *ex, const kp_node_table *local_nodes, const kp_pod_table *pods, int strategy,
+                int filter_mode, void *workspace, size_t workspace_bytes, void *stream);
+int kp_ns_reduce(kp_exchange *ex, int64_t *out_idx_shard, double *out_score_shard, void *stream);
+int kp_snapshot_place_node_sharded(kp_exchange *ex, const kp_node_table *local_nodes, int64_t node_offset,
+                                   const kp_pod_table *pods, int strategy, int filter_mode,
+                                   int64_t *out_idx_shard, double *out_score_shard, void *workspace,
+                                   size_t workspace_bytes, void *stream);
+
 /* ---- greedy placement with commit, device pointers ---------------------------------
  * Replaces: the sequential loop `_schedule_pod` -> `_fallback_decision` -> bind ->
  * next `get_node_metrics()` (scheduler.py:690-729, :598, :144-151).  Pods are placed in

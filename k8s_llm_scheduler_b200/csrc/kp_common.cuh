@@ -211,6 +211,11 @@ struct PlaceTuning {
     // node table with the SAME signature, and the plan kernels are skipped.
     bool reuse_plan = false;
     unsigned long long *plan_sig = nullptr;
+    // Node-sharded form (kp_exchange.cu): besides index and score the epilogue stores, per pod, the chosen node's
+    // GLOBAL rank position gpos_node[strategy * gpos_stride + local node index] (0xffffffff = no node).
+    uint32_t *out_gpos = nullptr;
+    const uint32_t *gpos_node = nullptr;
+    long long gpos_stride = 0;
 };
 // signature the session compares before it sets reuse_plan (0 = this call's plan cannot be reused)
 unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool per_pod, int strategy, int filter_mode);

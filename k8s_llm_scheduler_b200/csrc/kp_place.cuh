@@ -52,6 +52,9 @@ struct PlaceParams {
     int tiles_per_seg_wide;            // tiles (of 512 nodes) per node segment; the packed form uses half
     int small_table_len;               // > 0: small-table plan -- packed form, thresholds sorted WITH duplicates
                                        // (n_nodes of them), table length known on the host: no header reads
+    uint32_t *out_gpos;                // node-sharded form: global rank position of the chosen node per pod (NULL = off)
+    const uint32_t *gpos_node;         // [3][gpos_stride] global rank position of every local node
+    long long gpos_stride;
     long long share_q;                 // place_small_kernel, one strategy: warp g owns share_q pods, the first share_r
     int share_r;                       // warps one more (the split is made on the host: no 64-bit division per warp)
     const double *uniq;                // [2][npad] ascending distinct thresholds
@@ -419,6 +422,7 @@ place_kernel(const PlaceParams p)
         }
         p.out_idx[pod] = idx;
         p.out_score[pod] = sc;
+        if (p.out_gpos) p.out_gpos[pod] = idx >= 0 ? p.gpos_node[(size_t)s * p.gpos_stride + idx] : 0xffffffffu;
     }
     if (p.flow && tid == 0) {                                // flow control off again for the next launch
         __threadfence();
@@ -656,6 +660,7 @@ place_small_kernel(const PlaceParams p)
             }
             p.out_idx[pod] = idx;
             p.out_score[pod] = sc;
+            if (p.out_gpos) p.out_gpos[pod] = idx >= 0 ? p.gpos_node[(size_t)s * p.gpos_stride + idx] : 0xffffffffu;
         }
     }
 }

@@ -728,6 +728,9 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.best_pos = best_pos;
     pp.out_idx = (long long *)out_idx;
     pp.out_score = out_score;
+    pp.out_gpos = tuning.out_gpos;
+    pp.gpos_node = tuning.gpos_node;
+    pp.gpos_stride = tuning.gpos_stride;
     // pacing applies to the kernels that fetch a CTA's requests up front (node splits, one strategy)
     const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && !use_small && kPlaceCfgs[cfg].nsplit > 1;
     pp.flow = paced ? tuning.flow : nullptr;

@@ -6,12 +6,17 @@ Two ways to split one snapshot over W ranks:
   contiguous range of pods against the whole node table.  The table (<= 2.8 MB at 50 k nodes)
   is replicated with one broadcast from the source rank; there is no collective on the data
   path; results stay sharded unless ``gather=True``.
-* **node-sharded** (``snapshot_node_sharded``): each rank holds a contiguous range of the node
-  list (contiguity keeps "first in list order wins" meaningful) and scores ALL pods against its
-  range; the per-pod winner is then an arg-max reduce over ranks under (score desc, index asc):
-  an all-reduce MAX over the fp64 scores followed by an all-reduce MIN over the global indices
-  of the ranks that attain that maximum.  Both are exact: scores are compared as fp64 values,
-  exactly as the reference compares them (scheduler.py:547), and -1.0 / -1 stay "no node".
+* **node-sharded**: each rank holds a contiguous range of the node list (contiguity keeps "first
+  in list order wins" meaningful) and scores ALL pods against its range; the per-pod winner is
+  then an arg-max reduce over ranks under (score desc, index asc).  On GPUs this is
+  ``NodeShardedPlacer``: the library's own kernels exchange one 32-bit global rank position per
+  pod and rank over peer-mapped memory (NVLink, CUDA IPC) and the owner of a pod shard decodes
+  the winner -- no collective library and no host round trip on the data path
+  (csrc/kp_exchange.cu).  ``snapshot_node_sharded`` is the same reduce written with two
+  ``torch.distributed`` all-reduces (MAX over the fp64 scores, MIN over the global indices that
+  attain it); it is what the CPU (gloo) tests of the sharding logic run, and a cross-check of
+  the fused path on GPUs.  Both are exact: scores are compared exactly as the reference compares
+  them (scheduler.py:547), and -1.0 / -1 stay "no node".
 
 Greedy placement is a dependent chain over pods and does not shard without one exchange per
 pod; it runs on one GPU (replicas at N > 1), see DESIGN.md.
@@ -21,7 +26,8 @@ inject a stand-in so that the sharding / collective logic runs under gloo withou
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, Optional, Tuple
+import ctypes
+from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
@@ -114,3 +120,109 @@ def snapshot_node_sharded(local_nodes: Dict[str, torch.Tensor], node_offset: int
 
 def slice_nodes(nodes: Dict[str, torch.Tensor], lo: int, hi: int) -> Dict[str, torch.Tensor]:
     return {k: nodes[k][lo:hi].contiguous() for k in NODE_COLUMNS}
+
+
+# ---------------------------------------------------------------------------------------
+# node-sharded snapshot over peer memory (kp_exchange.cu)
+# ---------------------------------------------------------------------------------------
+class NodeShardedPlacer:
+    """One rank's end of the node-sharded snapshot: owns a ``kp_exchange`` (exchange memory on this GPU,
+    mapped into every peer with CUDA IPC) and a placement workspace.
+
+    ``NodeShardedPlacer(device, max_pods, max_local_nodes)`` inside an initialised process group (one
+    process per GPU) exchanges the IPC handles with ``all_gather_object``; ``NodeShardedPlacer.local_group``
+    builds all ranks of a group inside ONE process (several GPUs of one process, or several ranks emulated
+    on one GPU for tests), linked without IPC.
+
+    ``place`` returns this rank's pod shard ``(lo, hi, idx, score)``; indices are global (list order)."""
+
+    def __init__(self, device, max_pods: int, max_local_nodes: int, rank: Optional[int] = None,
+                 world: Optional[int] = None, connect: bool = True):
+        from . import _lib
+        self._lib = _lib.load()
+        self._check = _lib.check
+        r, w = _world()
+        self.rank = r if rank is None else rank
+        self.world = w if world is None else world
+        self.device = torch.device(device)
+        self.max_pods, self.max_local = max_pods, max_local_nodes
+        self._h = ctypes.c_void_p()
+        self._check(self._lib.kp_exchange_create(self.device.index or 0, self.rank, self.world, max_pods, max_local_nodes,
+                                                 ctypes.byref(self._h)), "kp_exchange_create")
+        self._ws: Optional[torch.Tensor] = None
+        self._n_pods = 0
+        if connect and self.world > 1:
+            buf = (ctypes.c_ubyte * 64)()
+            self._check(self._lib.kp_exchange_handle(self._h, buf), "kp_exchange_handle")
+            handles: List[Optional[bytes]] = [None] * self.world
+            dist.all_gather_object(handles, bytes(buf))
+            blob = b"".join(handles)
+            self._check(self._lib.kp_exchange_connect(self._h, blob), "kp_exchange_connect")
+
+    @classmethod
+    def local_group(cls, devices, max_pods: int, max_local_nodes: int) -> List["NodeShardedPlacer"]:
+        """All ranks of a group in this process: ``devices`` = one device per rank (they may repeat)."""
+        world = len(devices)
+        group = [cls(d, max_pods, max_local_nodes, rank=r, world=world, connect=False) for r, d in enumerate(devices)]
+        arr = (ctypes.c_void_p * world)(*[g._h for g in group])
+        for g in group:
+            g._check(g._lib.kp_exchange_connect_local(g._h, arr), "kp_exchange_connect_local")
+        return group
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.kp_exchange_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    __del__ = close
+
+    def _structs(self, local_nodes, req_cpu_milli, req_mem_bytes, strategy):
+        from . import placement
+        nst, device, n = placement._node_struct(local_nodes)
+        pst, p, strat, per_pod = placement._pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
+        need = placement.snapshot_workspace_bytes(n, p, per_pod)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=device)
+        return nst, pst, n, p, strat, per_pod
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # the three steps, separately (ranks emulated on one device must be driven in lock step)
+    def keys(self, local_nodes, node_offset: int, strategy, per_pod: bool):
+        from . import placement
+        nst, _, _ = placement._node_struct(local_nodes)
+        with torch.cuda.device(self.device):
+            self._check(self._lib.kp_ns_keys(self._h, ctypes.byref(nst), int(node_offset), 0 if per_pod else int(strategy),
+                                             int(per_pod), self._stream()), "kp_ns_keys")
+
+    def scan(self, local_nodes, req_cpu_milli, req_mem_bytes, strategy, filter_mode: int = 1):
+        nst, pst, n, p, strat, per_pod = self._structs(local_nodes, req_cpu_milli, req_mem_bytes, strategy)
+        self._n_pods = p
+        with torch.cuda.device(self.device):
+            self._check(self._lib.kp_ns_place(self._h, ctypes.byref(nst), ctypes.byref(pst), strat, int(filter_mode),
+                                              self._ws.data_ptr(), self._ws.numel(), self._stream()), "kp_ns_place")
+
+    def reduce(self, out=None):
+        lo, hi = shard_bounds(self._n_pods, self.rank, self.world)
+        if out is None:
+            out = (torch.empty(hi - lo, dtype=torch.int64, device=self.device),
+                   torch.empty(hi - lo, dtype=torch.float64, device=self.device))
+        with torch.cuda.device(self.device):
+            self._check(self._lib.kp_ns_reduce(self._h, out[0].data_ptr(), out[1].data_ptr(), self._stream()), "kp_ns_reduce")
+        return lo, hi, out[0], out[1]
+
+    def place(self, local_nodes: Dict[str, torch.Tensor], node_offset: int, req_cpu_milli: torch.Tensor,
+              req_mem_bytes: torch.Tensor, strategy=0, filter_mode: int = 1, out=None):
+        """Every rank: its node slice (CUDA tensors, list order), the slice's global start index, and the SAME pods."""
+        per_pod = isinstance(strategy, torch.Tensor)
+        self.keys(local_nodes, node_offset, strategy, per_pod)
+        self.scan(local_nodes, req_cpu_milli, req_mem_bytes, strategy, filter_mode)
+        return self.reduce(out)
+
+    def check(self):
+        """After synchronising: raise if a kernel of this rank gave up waiting for a peer."""
+        err = ctypes.c_int()
+        self._check(self._lib.kp_exchange_error(self._h, ctypes.byref(err)), "kp_exchange_error")
+        if err.value:
+            raise RuntimeError(self._lib.kp_last_error().decode())
