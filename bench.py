@@ -644,7 +644,162 @@ def session_probe(torch, placement, dev, nodes, pods, meta, steps=30):
 
 
 def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, world, rank, local):
-    raise SystemExit("workload c5node: node-sharded snapshot is not wired into bench.py yet")
+    """Config 5 with the NODES sharded: every rank scores all pods against its contiguous slice of the node list;
+    the per-pod winner is reduced across ranks by the library's own kernels over peer memory (csrc/kp_exchange.cu).
+    Strong scaling: the job (20 000 nodes x 2 000 000 pods) is fixed, the slice shrinks with N."""
+    import ctypes
+    from k8s_llm_scheduler_b200 import dist as kd
+    n, p, n_el = len(nodes), len(pods), eligible_nodes(nodes, meta)
+    lo, hi = kd.shard_bounds(n, rank, world)
+    plo, phi = kd.shard_bounds(p, rank, world)
+    full = placement.nodes_to_device(nodes, dev)
+    mine = kd.slice_nodes(full, lo, hi)
+    rc = torch.as_tensor(pods.req_cpu_milli).to(dev)
+    rm = torch.as_tensor(pods.req_mem_bytes).to(dev)
+    strat = torch.as_tensor(pods.strategy_ids).to(dev) if meta["per_pod"] else meta["strategy"]
+    placer = kd.NodeShardedPlacer(dev, max_pods=p, max_local_nodes=(n + world - 1) // world)
+    out = (torch.empty(phi - plo, dtype=torch.int64, device=dev), torch.empty(phi - plo, dtype=torch.float64, device=dev))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def step():
+        placer.place(mine, lo, rc, rm, strat, meta["filter"], out=out)
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    hbm_peak, sm_max_mhz, peak_src = measured_peaks()
+    peak_meas = issue_peak_pairs_per_s(torch, lib, dev) if rank == 0 else None
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    launches0 = placement.launch_count()
+    evs = []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        if not args.no_flush:
+            flush_buf.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); step(); b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier()
+    launches = placement.launch_count() - launches0
+    placer.check()
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    tot = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    ms_per_step = float(tot.item()) / args.steps
+    value = float(p) * n_el / (ms_per_step * 1e-3)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    dev_idx = out[0][:4096].cpu().numpy()
+
+    # where a step goes: events between the three phases, and around the placement kernel (kp_profile)
+    lib.kp_profile_enable(1)
+    phases, place_ms, plan_ms = [], [], []
+    per_pod = meta["per_pod"]
+    for _ in range(args.steps):
+        if not args.no_flush:
+            flush_buf.zero_()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        e[0].record(); placer.keys(mine, lo, strat, per_pod)
+        e[1].record(); placer.scan(mine, rc, rm, strat, meta["filter"])
+        e[2].record(); placer.reduce(out)
+        e[3].record()
+        fa, fb = ctypes.c_float(), ctypes.c_float()
+        if lib.kp_profile_last_ms(ctypes.byref(fa), ctypes.byref(fb)) == 0:
+            plan_ms.append(fa.value); place_ms.append(fb.value)
+        torch.cuda.synchronize()
+        phases.append([e[i].elapsed_time(e[i + 1]) for i in range(3)])
+    lib.kp_profile_enable(0)
+    barrier()
+
+    # end to end: pinned host tables in (this rank's node slice and all pods), this rank's result shard out
+    hn = {k: v.cpu().pin_memory() for k, v in mine.items()}
+    hp = [torch.as_tensor(pods.req_cpu_milli).pin_memory(), torch.as_tensor(pods.req_mem_bytes).pin_memory()]
+    if per_pod:
+        hp.append(torch.as_tensor(pods.strategy_ids).pin_memory())
+    ho = (torch.empty(phi - plo, dtype=torch.int64).pin_memory(), torch.empty(phi - plo, dtype=torch.float64).pin_memory())
+    dn2 = {k: torch.empty_like(v) for k, v in mine.items()}
+    dp2 = [torch.empty_like(rc), torch.empty_like(rm)] + ([torch.empty_like(strat)] if per_pod else [])
+
+    def e2e_step():
+        for k in dn2:
+            dn2[k].copy_(hn[k], non_blocking=True)
+        for d, h in zip(dp2, hp):
+            d.copy_(h, non_blocking=True)
+        placer.place(dn2, lo, dp2[0], dp2[1], dp2[2] if per_pod else strat, meta["filter"], out=out)
+        ho[0].copy_(out[0], non_blocking=True)
+        ho[1].copy_(out[1], non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    ts = []
+    for _ in range(args.steps):
+        t = time.perf_counter(); e2e_step(); ts.append(time.perf_counter() - t)
+    e2e_s = torch.tensor([sum(ts) / len(ts)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    placer.check()
+    h2d = sum(v.numel() * v.element_size() for v in hn.values()) + sum(h.numel() * h.element_size() for h in hp)
+    d2h = 16 * (phi - plo)
+    e2e_idx = ho[0].numpy().copy()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    from k8s_llm_scheduler_b200.tables import PodTable
+    shard = PodTable.from_columns(pods.req_cpu_milli[plo:phi], pods.req_mem_bytes[plo:phi],
+                                  pods.strategy_ids[plo:phi] if per_pod else None)
+    ok_dev, k_chk = c_oracle_check(nodes, shard, meta, dev_idx)
+    ok_e2e, _ = c_oracle_check(nodes, shard, meta, e2e_idx)
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    clk = (clocks or {}).get("sm_mhz") or sm_max_mhz
+    n_el_local = int(((nodes.ready[lo:hi] != 0) & (nodes.pod_count[lo:hi] < nodes.max_pods[lo:hi])).sum())
+    roofline = None
+    if place_ms:
+        roofline = place_roofline(p, n_el_local, hi - lo, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src, clk,
+                                  peak_meas, hbm_peak, None, per_pod)
+        roofline["note"] = "this rank's placement kernel: all pods x the eligible nodes of its slice"
+    ph = np.array(phases).mean(axis=0)
+    out_line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64 scores, i32 rank compares", "data": "synthetic", "pods_per_sec": p / (ms_per_step * 1e-3),
+        "config": config_block(meta, nodes, pods, world),
+        "run": {"nodes_per_gpu": hi - lo, "sharding": f"node list cut into {world} contiguous slices; every rank scores all {p} pods; "
+                "per-pod arg-max reduced across ranks by the library's kernels over peer memory (CUDA IPC / NVLink): "
+                "32-bit global rank positions pulled by the pod shard's owner, no NCCL and no host on the data path",
+                "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)"},
+        "phase_ms": {"keys_publish": float(ph[0]), "gather_rank_plan_place": float(ph[1]), "reduce_decode": float(ph[2]),
+                     "note": "second, instrumented pass on rank 0; a phase includes waiting for the slowest peer"},
+        "e2e": {"value": float(p) * n_el / float(e2e_s.item()), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+                "d2h_bytes_per_step": 16 * p, "ms_per_step": float(e2e_s.item()) * 1e3,
+                "api": "NodeShardedPlacer.place with pinned host tables copied in and the result shard copied out per step"},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": None,
+        "parity_vs_cpu_sample": ok_dev and ok_e2e,
+        "parity_detail": {"c_oracle_pods_checked": k_chk, "device_pass": ok_dev, "host_api_pass": ok_e2e,
+                          "checked": "first pods of rank 0's result shard against the oracle on the WHOLE node list"},
+    }
+    if world == 1 and not args.no_cpu:
+        cb = cpu_port_run(nodes, pods, meta, args.cpu_seconds)
+        out_line["cpu_baseline"] = {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port",
+                                    "sample": cb["sample"], "pods_per_sec": cb["pods_per_s"]}
+        out_line["parity_vs_cpu_sample"] = out_line["parity_vs_cpu_sample"] and bool(np.array_equal(e2e_idx[:cb["n_sample"]], cb["idx"]))
+    print(json.dumps(out_line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_extras(args, torch, placement, lib, dev, peak_meas):
