@@ -710,7 +710,7 @@ def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, 
         if not args.no_flush:
             flush_buf.zero_()
         e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        e[0].record(); placer.keys(mine, lo, strat, per_pod)
+        e[0].record(); placer.keys(mine, lo, rc, rm, strat, meta["filter"])
         e[1].record(); placer.scan(mine, rc, rm, strat, meta["filter"])
         e[2].record(); placer.reduce(out)
         e[3].record()
@@ -782,7 +782,7 @@ def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, 
                 "per-pod arg-max reduced across ranks by the library's kernels over peer memory (CUDA IPC / NVLink): "
                 "32-bit global rank positions pulled by the pod shard's owner, no NCCL and no host on the data path",
                 "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)"},
-        "phase_ms": {"keys_publish": float(ph[0]), "gather_rank_plan_place": float(ph[1]), "reduce_decode": float(ph[2]),
+        "phase_ms": {"plan_publish": float(ph[0]), "gather_rank_place": float(ph[1]), "reduce_decode": float(ph[2]),
                      "note": "second, instrumented pass on rank 0; a phase includes waiting for the slowest peer"},
         "e2e": {"value": float(p) * n_el / float(e2e_s.item()), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": 16 * p, "ms_per_step": float(e2e_s.item()) * 1e3,

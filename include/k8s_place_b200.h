@@ -178,8 +178,8 @@ int kp_exchange_connect(kp_exchange *ex, const unsigned char *handles /* world x
 int kp_exchange_connect_local(kp_exchange *ex, kp_exchange *const *all /* world exchanges, rank order */);
 void kp_exchange_destroy(kp_exchange *ex);
 int kp_exchange_error(kp_exchange *ex, int *out_error);
-int kp_ns_keys(kp_exchange *ex, const kp_node_table *local_nodes, int64_t node_offset, int strategy,
-               int per_pod_strategy, void *stream);
+int kp_ns_keys(kp_exchange *ex, const kp_node_table *local_nodes, int64_t node_offset, const kp_pod_table *pods,
+               int strategy, int filter_mode, void *workspace, size_t workspace_bytes, void *stream);
 int kp_ns_place(kp_exchange *ex, const kp_node_table *local_nodes, const kp_pod_table *pods, int strategy,
                 int filter_mode, void *workspace, size_t workspace_bytes, void *stream);
 int kp_ns_reduce(kp_exchange *ex, int64_t *out_idx_shard, double *out_score_shard, void *stream);

@@ -211,12 +211,17 @@ struct PlaceTuning {
     // node table with the SAME signature, and the plan kernels are skipped.
     bool reuse_plan = false;
     unsigned long long *plan_sig = nullptr;
+    bool reuse_plan_forced = false;   // reuse even with per-pod strategies: the plan was built by a plan_only call just before
+    bool plan_only = false;           // build the node plan in the workspace and return (no pods are scored)
     // Node-sharded form (kp_exchange.cu): besides index and score the epilogue stores, per pod, the chosen node's
-    // GLOBAL rank position gpos_node[strategy * gpos_stride + local node index] (0xffffffff = no node).
+    // GLOBAL rank position gpos_by_pos[strategy * gpos_stride + local rank position] (0xffffffff = no node).
     uint32_t *out_gpos = nullptr;
-    const uint32_t *gpos_node = nullptr;
+    const uint32_t *gpos_by_pos = nullptr;
     long long gpos_stride = 0;
 };
+// where the plan of a snapshot workspace keeps what the node-sharded exchange publishes
+struct PlanView { const uint32_t *nvalid; const double *score_pos; int npad; };
+PlanView snapshot_plan_view(int64_t n_nodes, int64_t n_pods, bool per_pod, void *workspace);
 // signature the session compares before it sets reuse_plan (0 = this call's plan cannot be reused)
 unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool per_pod, int strategy, int filter_mode);
 int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,

@@ -6,13 +6,14 @@
 // ranks' local winners.  The reduce is done by our own kernels over peer-mapped memory (CUDA IPC), not by a
 // collective library and not through the host:
 //
-//   1. keys     every rank publishes the order keys of its nodes' scores in its exchange buffer and raises
-//               flag 0 in every peer's buffer (st.release.sys).
-//   2. place    every rank pulls all ranks' keys (plain peer loads), counts for each of ITS nodes how many
-//               nodes of the whole cluster sort before it -- the node's GLOBAL rank position, a 32-bit number
-//               that is unique per node and orders exactly like (score desc, index asc) -- and runs the
-//               ordinary snapshot kernels on its slice; their epilogue additionally stores the winner's global
-//               position per pod.  Flag 1 is raised.
+//   1. keys     every rank builds the node plan of its slice (kp_plan.cuh) and publishes, in its exchange buffer,
+//               the order keys of its eligible nodes' scores in best-first order; it raises flag 0 in every
+//               peer's buffer (st.release.sys).
+//   2. place    every rank pulls all ranks' sorted keys (plain peer loads) and finds, by binary search in each
+//               peer's list, how many nodes of the whole cluster sort before each of ITS nodes -- the node's
+//               GLOBAL rank position, a 32-bit number that is unique per node and orders exactly like
+//               (score desc, index asc).  Then the ordinary placement kernel scans the slice; its epilogue
+//               additionally stores the winner's global position per pod.  Flag 1 is raised.
 //   3. reduce   pods are owned in contiguous shards; the owner pulls the W candidate positions of each of its
 //               pods from the peers' buffers, takes the minimum, and fetches index and score from the one rank
 //               that holds the winner.  4 W + 16 bytes cross NVLink per pod, coalesced; nothing is reduced twice.
@@ -35,9 +36,13 @@ constexpr unsigned long long kWaitNs = 4000000000ull;          // 4 s: give up o
 struct ExHeader {                       // start of every rank's buffer
     uint32_t flag[2][kMaxWorld];        // flag[phase][source rank] = epoch reached (written by that rank)
     uint32_t error;                     // set by a kernel of this rank that gave up waiting
-    uint32_t pad0;
+    uint32_t nvalid[kMaxStrategies];    // published: eligible nodes of this rank's slice per strategy
     long long n_local;                  // this rank's slice
     long long node_offset;
+};
+struct ExMeta {                         // pulled copy of every rank's header fields
+    uint32_t nvalid[kMaxWorld][kMaxStrategies];
+    long long node_offset[kMaxWorld];
 };
 
 struct ExLayout {
@@ -48,10 +53,10 @@ static ExLayout ex_layout(int world, int64_t max_pods, int64_t max_local)
 {
     ExLayout L{};
     size_t o = align_up(sizeof(ExHeader));
-    L.off_keys = o;     o = align_up(o + sizeof(uint64_t) * kMaxStrategies * max_local);            // published
-    L.off_gathered = o; o = align_up(o + sizeof(uint64_t) * kMaxStrategies * max_local * world);    // pulled copy of all ranks' keys
-    L.off_gbase = o;    o = align_up(o + sizeof(long long) * 2 * (kMaxWorld + 1));                  // per rank: first slot, node offset
-    L.off_gpos = o;     o = align_up(o + sizeof(uint32_t) * kMaxStrategies * max_local);            // global position per local node
+    L.off_keys = o;     o = align_up(o + sizeof(uint64_t) * kMaxStrategies * max_local);            // published: sorted keys
+    L.off_gathered = o; o = align_up(o + sizeof(uint64_t) * kMaxStrategies * max_local * world);    // pulled copy: [s][rank][pos]
+    L.off_gbase = o;    o = align_up(o + sizeof(ExMeta));
+    L.off_gpos = o;     o = align_up(o + sizeof(uint32_t) * kMaxStrategies * max_local);            // global position per local position
     for (int b = 0; b < 2; ++b) {
         L.off_pod[b] = o;
         o = align_up(o + sizeof(uint32_t) * max_pods);      // candidate global position per pod
@@ -95,13 +100,13 @@ __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v)
 __device__ __forceinline__ unsigned long long ld_sys_u64(const void *p)
 {
     unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
     return v;
 }
 __device__ __forceinline__ uint32_t ld_sys_u32(const void *p)
 {
     uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
 __device__ __forceinline__ unsigned long long global_ns()
@@ -133,40 +138,33 @@ __device__ __forceinline__ bool wait_all_ranks(ExHeader *mine, int phase, int wo
     return s_ok != 0;
 }
 
-// ---- phase 1: publish this slice's score keys -------------------------------------------------------------
-// key = ~order_key(score) (ascending = best first), ~0 = the node can never be chosen -- the same eligibility
-// as the node plan (Ready, score above the -1 sentinel, room for a pod, thresholds not NaN).
-struct NodeCols {
-    const long long *alloc_cpu, *alloc_mem, *pod_count, *max_pods;
-    const uint8_t *ready;
-    const double *cu, *mu;
-    int n;
-};
-
-__global__ void __launch_bounds__(256)
-ns_export_keys_kernel(NodeCols t, int strat_mask, long long node_offset, unsigned char *base, size_t off_keys, long long max_local)
+// ---- phase 1: publish this slice's score keys in best-first order -------------------------------------------
+// key = ~order_key(score): ascending = best first, the order the plan's tables are in.  The plan keeps the fp64
+// score of the node at every rank position; the key is rebuilt from it (round_robin scores are pod counts and
+// order as integers, like the reference's int compare, scheduler.py:544-549).
+__device__ __forceinline__ unsigned long long sort_key_of_score(int s, double score)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) {
-        ExHeader *h = reinterpret_cast<ExHeader *>(base);
-        h->n_local = t.n;
-        h->node_offset = node_offset;
-    }
-    if (i >= t.n) return;
+    return s == 2 ? ~i64_order_key((long long)score) : ~f64_order_key(score);
+}
+
+// one block: writes the keys, then raises flag 0 in every rank's buffer (including its own)
+__global__ void __launch_bounds__(1024)
+ns_publish_kernel(ExPeers peers, int rank, int world, uint32_t epoch, int strat_mask, const uint32_t *__restrict__ plan_nvalid,
+                  const double *__restrict__ score_pos, int npad, long long n_local, long long node_offset, size_t off_keys, long long max_local)
+{
+    unsigned char *base = peers.p[rank];
+    ExHeader *h = reinterpret_cast<ExHeader *>(base);
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(base + off_keys);
-    const double cu = t.cu[i], mu = t.mu[i];
-    const long long pc = t.pod_count[i], mp = t.max_pods[i];
-    const double ta = free_cpu_cores(t.alloc_cpu[i], cu), tb = free_mem_gib(t.alloc_mem[i], mu);
-    const bool ok = t.ready[i] != 0 && pc < mp && ta == ta && tb == tb;
 #pragma unroll
     for (int s = 0; s < kMaxStrategies; ++s) {
-        unsigned long long k = ~0ull;
-        if ((strat_mask & (1 << s)) && ok) {
-            const NodeScore ns = node_score(s, cu, mu, pc, mp);
-            if (ns.key != 0ull) k = ~ns.key;
-        }
-        keys[(size_t)s * max_local + i] = k;
+        const int nv = (strat_mask & (1 << s)) && n_local > 0 ? (int)plan_nvalid[s] : 0;
+        if (threadIdx.x == 0) h->nvalid[s] = (uint32_t)nv;
+        for (int i = threadIdx.x; i < nv; i += blockDim.x) keys[(size_t)s * max_local + i] = sort_key_of_score(s, score_pos[(size_t)s * npad + i]);
     }
+    if (threadIdx.x == 0) { h->n_local = n_local; h->node_offset = node_offset; }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < world) st_release_sys(&reinterpret_cast<ExHeader *>(peers.p[threadIdx.x])->flag[0][rank], epoch);
 }
 
 // raise flag[phase][my rank] = epoch in every rank's buffer (one thread per rank)
@@ -178,97 +176,93 @@ __global__ void ns_signal_kernel(ExPeers peers, int rank, int world, int phase, 
     st_release_sys(&reinterpret_cast<ExHeader *>(peers.p[r])->flag[phase][rank], epoch);
 }
 
-// ---- phase 2a: pull every rank's keys into local memory ----------------------------------------------------
-// gathered[s][slot]: slots of rank r start at gbase[r]; gbase[kMaxWorld + 1 + r] = node offset of rank r.
+// ---- phase 2a: pull every rank's sorted keys into local memory ---------------------------------------------
+// grid (x, world): block row r copies rank r's lists to gathered[s][r][pos]
 __global__ void __launch_bounds__(256)
-ns_gather_keys_kernel(ExPeers peers, int rank, int world, uint32_t epoch, size_t off_keys, size_t off_gathered, size_t off_gbase,
+ns_gather_keys_kernel(ExPeers peers, int rank, int world, uint32_t epoch, size_t off_keys, size_t off_gathered, size_t off_meta,
                       long long max_local)
 {
     unsigned char *base = peers.p[rank];
-    ExHeader *mine = reinterpret_cast<ExHeader *>(base);
-    if (!wait_all_ranks(mine, 0, world, epoch)) return;
-    long long *gbase = reinterpret_cast<long long *>(base + off_gbase);
+    if (!wait_all_ranks(reinterpret_cast<ExHeader *>(base), 0, world, epoch)) return;
+    const int r = blockIdx.y;
+    const ExHeader *h = reinterpret_cast<const ExHeader *>(peers.p[r]);
+    ExMeta *meta = reinterpret_cast<ExMeta *>(base + off_meta);
     unsigned long long *gathered = reinterpret_cast<unsigned long long *>(base + off_gathered);
-    const long long stride_all = max_local * world;
-    long long first = 0;
-    for (int r = 0; r < world; ++r) {
-        const ExHeader *h = reinterpret_cast<const ExHeader *>(peers.p[r]);
-        const long long n_r = (long long)ld_sys_u64(&h->n_local);
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            gbase[r] = first;
-            gbase[kMaxWorld + 1 + r] = (long long)ld_sys_u64(&h->node_offset);
-            if (r == world - 1) gbase[world] = first + n_r;
-        }
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(peers.p[r] + off_keys);
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_r * kMaxStrategies;
-             i += (long long)gridDim.x * blockDim.x) {
-            const int s = (int)(i / n_r);
-            const long long m = i - (long long)s * n_r;
-            gathered[(size_t)s * stride_all + first + m] = ld_sys_u64(src + (size_t)s * max_local + m);
-        }
-        first += n_r;
+    const unsigned long long *src = reinterpret_cast<const unsigned long long *>(peers.p[r] + off_keys);
+#pragma unroll
+    for (int s = 0; s < kMaxStrategies; ++s) {
+        const uint32_t nv = ld_sys_u32(&h->nvalid[s]);
+        if (blockIdx.x == 0 && threadIdx.x == 0) meta->nvalid[r][s] = nv;
+        unsigned long long *dst = gathered + ((size_t)s * world + r) * max_local;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += gridDim.x * blockDim.x)
+            dst[i] = ld_sys_u64(src + (size_t)s * max_local + i);
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) meta->node_offset[r] = (long long)ld_sys_u64(&h->node_offset);
 }
 
-// ---- phase 2b: global rank position of every local node ----------------------------------------------------
-// gpos[s][i] = #{nodes m of the whole cluster : key[m] < key[i], or key[m] == key[i] and m before i in list order}.
-// Lists are concatenated in rank order and slices are contiguous, so slot order IS global list order.
-// A block owns 32 local nodes of one strategy (lane = node); its warps split the slot range; partial counts are
-// added with shared-memory atomics and written once.
-constexpr int kGposWarps = 8;
-
-__global__ void __launch_bounds__(32 * kGposWarps)
-ns_gpos_kernel(const unsigned char *base, int rank, int world, int strat_mask, size_t off_gathered, size_t off_gbase, size_t off_gpos,
-               long long max_local, int n_local)
+// ---- phase 2b: global rank position of every local rank position -------------------------------------------
+// gpos[s][pos] = pos + sum over the other ranks r of #{keys of r that sort before mine}: keys equal to mine count
+// for ranks below me (their nodes come first in list order) and not for ranks above.  One binary search per peer
+// list, all peers side by side (independent load chains).
+__global__ void __launch_bounds__(256)
+ns_gpos_kernel(const unsigned char *base, int rank, int world, int strat_mask, size_t off_gathered, size_t off_meta, size_t off_gpos,
+               long long max_local)
 {
-    __shared__ uint32_t acc[32];
     const int s = blockIdx.y;
     if (!(strat_mask & (1 << s))) return;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const long long *gbase = reinterpret_cast<const long long *>(base + off_gbase);
-    const unsigned long long *K = reinterpret_cast<const unsigned long long *>(base + off_gathered) + (size_t)s * max_local * world;
-    const long long total = gbase[world], my_first = gbase[rank];
-    const int node = blockIdx.x * 32 + lane;
-    if (threadIdx.x < 32) acc[threadIdx.x] = 0;
-    __syncthreads();
-    const bool live = node < n_local;
-    const long long my_slot = my_first + node;
-    const unsigned long long kn = live ? K[my_slot] : 0ull;
-    const long long m0 = total * warp / kGposWarps, m1 = total * (warp + 1) / kGposWarps;
-    uint32_t c = 0;
-#pragma unroll 4
-    for (long long m = m0; m < m1; ++m) {
-        const unsigned long long km = K[m];                      // same address in every lane
-        c += (km < kn) | ((km == kn) & (m < my_slot));
+    const ExMeta *meta = reinterpret_cast<const ExMeta *>(base + off_meta);
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= (int)meta->nvalid[rank][s]) return;
+    const unsigned long long *K = reinterpret_cast<const unsigned long long *>(base + off_gathered) + (size_t)s * world * max_local;
+    const unsigned long long kn = K[(size_t)rank * max_local + pos];
+    int lo[kMaxWorld], nv[kMaxWorld], top = 1;
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+        lo[r] = 0;
+        nv[r] = (r < world && r != rank) ? (int)meta->nvalid[r][s] : 0;
+        top = max(top, nv[r]);
     }
-    if (live && c) atomicAdd(&acc[lane], c);
-    __syncthreads();
-    if (threadIdx.x < 32 && live) {
-        uint32_t *gpos = reinterpret_cast<uint32_t *>(const_cast<unsigned char *>(base) + off_gpos);
-        gpos[(size_t)s * max_local + node] = kn == ~0ull ? 0xffffffffu : acc[lane];
+    for (int step = 1 << (31 - __clz(top)); step > 0; step >>= 1) {
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r) {
+            const int nxt = lo[r] + step;
+            if (nxt <= nv[r]) {                                   // (nv == 0 for ranks that do not take part)
+                const unsigned long long km = K[(size_t)r * max_local + nxt - 1];
+                if (r < rank ? km <= kn : km < kn) lo[r] = nxt;
+            }
+        }
     }
+    uint32_t g = (uint32_t)pos;
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) g += (uint32_t)lo[r];
+    reinterpret_cast<uint32_t *>(const_cast<unsigned char *>(base) + off_gpos)[(size_t)s * max_local + pos] = g;
 }
 
 // ---- phase 3: owner-side reduce over the peers' candidates -------------------------------------------------
 __global__ void __launch_bounds__(256)
-ns_reduce_kernel(ExPeers peers, int rank, int world, uint32_t epoch, size_t off_pod, size_t stride_idx, size_t stride_score, size_t off_gbase,
+ns_reduce_kernel(ExPeers peers, int rank, int world, uint32_t epoch, size_t off_pod, size_t stride_idx, size_t stride_score, size_t off_meta,
                  long long pod_lo, long long pod_hi, long long *__restrict__ out_idx, double *__restrict__ out_score)
 {
     unsigned char *base = peers.p[rank];
     if (!wait_all_ranks(reinterpret_cast<ExHeader *>(base), 1, world, epoch)) return;
-    const long long *gbase = reinterpret_cast<const long long *>(base + off_gbase);
+    const ExMeta *meta = reinterpret_cast<const ExMeta *>(base + off_meta);
     for (long long j = pod_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; j < pod_hi; j += (long long)gridDim.x * blockDim.x) {
+        uint32_t g[kMaxWorld];
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r)                         // all candidates requested before any is looked at
+            g[r] = r < world ? ld_sys_u32(peers.p[r] + off_pod + sizeof(uint32_t) * j) : 0xffffffffu;
         uint32_t best = 0xffffffffu;
         int who = -1;
-        for (int r = 0; r < world; ++r) {
-            const uint32_t g = ld_sys_u32(peers.p[r] + off_pod + sizeof(uint32_t) * j);
-            if (g < best) { best = g; who = r; }
-        }
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r)
+            if (g[r] < best) { best = g[r]; who = r; }
         long long idx = -1;
         double sc = -1.0;
         if (who >= 0) {
-            idx = (long long)ld_sys_u64(peers.p[who] + off_pod + stride_idx + sizeof(long long) * j) + gbase[kMaxWorld + 1 + who];
-            sc = __longlong_as_double((long long)ld_sys_u64(peers.p[who] + off_pod + stride_score + sizeof(double) * j));
+            const unsigned long long li = ld_sys_u64(peers.p[who] + off_pod + stride_idx + sizeof(long long) * j);
+            const unsigned long long ls = ld_sys_u64(peers.p[who] + off_pod + stride_score + sizeof(double) * j);
+            idx = (long long)li + meta->node_offset[who];
+            sc = __longlong_as_double((long long)ls);
         }
         out_idx[j - pod_lo] = idx;
         out_score[j - pod_lo] = sc;
@@ -401,24 +395,42 @@ static int ns_check(const kp_exchange *ex, const char *what)
     return KP_OK;
 }
 
-int kp_ns_keys(kp_exchange *ex, const kp_node_table *nodes, int64_t node_offset, int strategy, int per_pod_strategy, void *stream)
+static int ns_check_tables(const kp_exchange *ex, const kp_node_table *nodes, const kp_pod_table *pods, int filter_mode, const char *what)
+{
+    if (!nodes || !pods || pods->n_pods < 0 || pods->n_pods > ex->max_pods || nodes->n_nodes < 0 || nodes->n_nodes > ex->max_local) {
+        set_error("%s: table sizes exceed the exchange (%lld pods, %lld nodes per rank)", what, (long long)ex->max_pods, (long long)ex->max_local);
+        return KP_ERR_CAPACITY;
+    }
+    if (filter_mode != KP_FILTER_CAPACITY) {
+        set_error("node-sharded placement implements the capacity filter (the Ready-only filter is pod-independent: one arg-max)");
+        return KP_ERR_INVALID_ARG;
+    }
+    return KP_OK;
+}
+
+int kp_ns_keys(kp_exchange *ex, const kp_node_table *nodes, int64_t node_offset, const kp_pod_table *pods, int strategy, int filter_mode,
+               void *workspace, size_t workspace_bytes, void *stream)
 {
     int st = ns_check(ex, "kp_ns_keys");
     if (st != KP_OK) return st;
-    if (!nodes || nodes->n_nodes < 0 || nodes->n_nodes > ex->max_local) {
-        set_error("kp_ns_keys: slice of %lld nodes (exchange holds %lld)", nodes ? (long long)nodes->n_nodes : -1ll, (long long)ex->max_local);
-        return KP_ERR_CAPACITY;
-    }
+    if ((st = ns_check_tables(ex, nodes, pods, filter_mode, "kp_ns_keys")) != KP_OK) return st;
     cudaStream_t sq = (cudaStream_t)stream;
     ex->epoch += 1;
-    const int strat_mask = per_pod_strategy ? 7 : (1 << canon_strategy(strategy));
-    NodeCols t{(const long long *)nodes->alloc_cpu_milli, (const long long *)nodes->alloc_mem_bytes, (const long long *)nodes->pod_count,
-               (const long long *)nodes->max_pods, nodes->ready, nodes->cpu_usage_pct, nodes->mem_usage_pct, (int)nodes->n_nodes};
-    const int blocks = (int)std::max<int64_t>(1, (nodes->n_nodes + 255) / 256);
-    ns_export_keys_kernel<<<blocks, 256, 0, sq>>>(t, strat_mask, node_offset, ex->base, ex->L.off_keys, ex->max_local);
-    KP_LAUNCH_CHECK("ns_export_keys_kernel");
-    ns_signal_kernel<<<1, kMaxWorld, 0, sq>>>(peers_of(ex), ex->rank, ex->world, 0, ex->epoch);
-    KP_LAUNCH_CHECK("ns_signal_kernel");
+    const bool per_pod = pods->strategy_ids != nullptr;
+    const int strat_mask = per_pod ? 7 : (1 << canon_strategy(strategy));
+    const int64_t n = nodes->n_nodes;
+    PlanView pv{nullptr, nullptr, 0};
+    if (n > 0 && pods->n_pods > 0) {
+        // the node plan of this slice, and nothing else yet
+        PlaceTuning tuning;
+        tuning.plan_only = true;
+        st = snapshot_place_device(*nodes, *pods, strategy, filter_mode, nullptr, nullptr, workspace, workspace_bytes, sq, tuning);
+        if (st != KP_OK) return st;
+        pv = snapshot_plan_view(n, pods->n_pods, per_pod, workspace);
+    }
+    ns_publish_kernel<<<1, 1024, 0, sq>>>(peers_of(ex), ex->rank, ex->world, ex->epoch, strat_mask, pv.nvalid, pv.score_pos, pv.npad,
+                                          pv.nvalid ? n : 0, node_offset, ex->L.off_keys, ex->max_local);
+    KP_LAUNCH_CHECK("ns_publish_kernel");
     return KP_OK;
 }
 
@@ -427,36 +439,30 @@ int kp_ns_place(kp_exchange *ex, const kp_node_table *nodes, const kp_pod_table 
 {
     int st = ns_check(ex, "kp_ns_place");
     if (st != KP_OK) return st;
-    if (!nodes || !pods || pods->n_pods < 0 || pods->n_pods > ex->max_pods || nodes->n_nodes > ex->max_local) {
-        set_error("kp_ns_place: table sizes exceed the exchange (%lld pods, %lld nodes)", (long long)ex->max_pods, (long long)ex->max_local);
-        return KP_ERR_CAPACITY;
-    }
-    if (filter_mode != KP_FILTER_CAPACITY) {
-        set_error("node-sharded placement implements the capacity filter (the Ready-only filter is pod-independent: one arg-max)");
-        return KP_ERR_INVALID_ARG;
-    }
+    if ((st = ns_check_tables(ex, nodes, pods, filter_mode, "kp_ns_place")) != KP_OK) return st;
     cudaStream_t sq = (cudaStream_t)stream;
     const bool per_pod = pods->strategy_ids != nullptr;
     const int strat_mask = per_pod ? 7 : (1 << canon_strategy(strategy));
     const ExPeers peers = peers_of(ex);
-    ns_gather_keys_kernel<<<32, 256, 0, sq>>>(peers, ex->rank, ex->world, ex->epoch, ex->L.off_keys, ex->L.off_gathered, ex->L.off_gbase,
-                                             ex->max_local);
+    ns_gather_keys_kernel<<<dim3(4, ex->world), 256, 0, sq>>>(peers, ex->rank, ex->world, ex->epoch, ex->L.off_keys, ex->L.off_gathered,
+                                                             ex->L.off_gbase, ex->max_local);
     KP_LAUNCH_CHECK("ns_gather_keys_kernel");
     const int n = (int)nodes->n_nodes;
     if (n > 0) {
-        ns_gpos_kernel<<<dim3((n + 31) / 32, kMaxStrategies), 32 * kGposWarps, 0, sq>>>(ex->base, ex->rank, ex->world, strat_mask, ex->L.off_gathered,
-                                                                                      ex->L.off_gbase, ex->L.off_gpos, ex->max_local, n);
+        ns_gpos_kernel<<<dim3((n + 255) / 256, kMaxStrategies), 256, 0, sq>>>(ex->base, ex->rank, ex->world, strat_mask, ex->L.off_gathered,
+                                                                              ex->L.off_gbase, ex->L.off_gpos, ex->max_local);
         KP_LAUNCH_CHECK("ns_gpos_kernel");
     }
     ex->n_pods = pods->n_pods;
     unsigned char *pb = ex->base + ex->L.off_pod[ex->epoch & 1u];
     PlaceTuning tuning;
     tuning.out_gpos = reinterpret_cast<uint32_t *>(pb);
-    tuning.gpos_node = reinterpret_cast<const uint32_t *>(ex->base + ex->L.off_gpos);
+    tuning.gpos_by_pos = reinterpret_cast<const uint32_t *>(ex->base + ex->L.off_gpos);
     tuning.gpos_stride = ex->max_local;
+    tuning.reuse_plan = tuning.reuse_plan_forced = true;      // kp_ns_keys built it in this workspace a moment ago
     if (pods->n_pods > 0 && n == 0)                      // an empty slice offers no candidate
         KP_CUDA(cudaMemsetAsync(tuning.out_gpos, 0xff, sizeof(uint32_t) * (size_t)pods->n_pods, sq));
-    if (pods->n_pods > 0) {
+    if (pods->n_pods > 0 && n > 0) {
         st = snapshot_place_device(*nodes, *pods, strategy, filter_mode, reinterpret_cast<int64_t *>(pb + ex->L.pod_stride_idx),
                                    reinterpret_cast<double *>(pb + ex->L.pod_stride_score), workspace, workspace_bytes, sq, tuning);
         if (st != KP_OK) return st;
@@ -485,7 +491,7 @@ int kp_snapshot_place_node_sharded(kp_exchange *ex, const kp_node_table *local_n
                                    int strategy, int filter_mode, int64_t *out_idx_shard, double *out_score_shard, void *workspace,
                                    size_t workspace_bytes, void *stream)
 {
-    int st = kp_ns_keys(ex, local_nodes, node_offset, strategy, pods && pods->strategy_ids != nullptr, stream);
+    int st = kp_ns_keys(ex, local_nodes, node_offset, pods, strategy, filter_mode, workspace, workspace_bytes, stream);
     if (st != KP_OK) return st;
     if ((st = kp_ns_place(ex, local_nodes, pods, strategy, filter_mode, workspace, workspace_bytes, stream)) != KP_OK) return st;
     return kp_ns_reduce(ex, out_idx_shard, out_score_shard, stream);

@@ -53,7 +53,7 @@ struct PlaceParams {
     int small_table_len;               // > 0: small-table plan -- packed form, thresholds sorted WITH duplicates
                                        // (n_nodes of them), table length known on the host: no header reads
     uint32_t *out_gpos;                // node-sharded form: global rank position of the chosen node per pod (NULL = off)
-    const uint32_t *gpos_node;         // [3][gpos_stride] global rank position of every local node
+    const uint32_t *gpos_by_pos;       // [3][gpos_stride] global rank position of every local rank position
     long long gpos_stride;
     long long share_q;                 // place_small_kernel, one strategy: warp g owns share_q pods, the first share_r
     int share_r;                       // warps one more (the split is made on the host: no 64-bit division per warp)
@@ -422,7 +422,7 @@ place_kernel(const PlaceParams p)
         }
         p.out_idx[pod] = idx;
         p.out_score[pod] = sc;
-        if (p.out_gpos) p.out_gpos[pod] = idx >= 0 ? p.gpos_node[(size_t)s * p.gpos_stride + idx] : 0xffffffffu;
+        if (p.out_gpos) p.out_gpos[pod] = best[r] >= 0 ? p.gpos_by_pos[(size_t)s * p.gpos_stride + best[r]] : 0xffffffffu;
     }
     if (p.flow && tid == 0) {                                // flow control off again for the next launch
         __threadfence();
@@ -660,7 +660,7 @@ place_small_kernel(const PlaceParams p)
             }
             p.out_idx[pod] = idx;
             p.out_score[pod] = sc;
-            if (p.out_gpos) p.out_gpos[pod] = idx >= 0 ? p.gpos_node[(size_t)s * p.gpos_stride + idx] : 0xffffffffu;
+            if (p.out_gpos) p.out_gpos[pod] = mine < kSmallNone ? p.gpos_by_pos[(size_t)s * p.gpos_stride + mine] : 0xffffffffu;
         }
     }
 }

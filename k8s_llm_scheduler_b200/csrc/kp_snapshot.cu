@@ -42,6 +42,7 @@ namespace kp {
 // ---------------------------------------------------------------------------------------
 constexpr int kArgmaxMaxBlocks = 256;
 constexpr int kSmallPad = 1536;
+constexpr int64_t kSmallMaxPods = 1 << 19;
 constexpr int kMaxChunkPods = 2048;
 
 struct SnapLayout {
@@ -117,6 +118,14 @@ unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool
     const SnapLayout L = make_layout(n_nodes, n_pods, false);
     return 0x8000000000000000ull | ((unsigned long long)canon_strategy(strategy) << 60) |
            ((unsigned long long)(L.off_keys & 0xfffffffffffull) << 16) | (unsigned long long)(n_nodes & 0xffff);
+}
+
+PlanView snapshot_plan_view(int64_t n_nodes, int64_t n_pods, bool per_pod, void *workspace)
+{
+    const SnapLayout L = make_layout(n_nodes, n_pods, per_pod);
+    unsigned char *w = static_cast<unsigned char *>(workspace);
+    return PlanView{reinterpret_cast<const SnapHeader *>(w + L.off_header)->nvalid, reinterpret_cast<const double *>(w + L.off_score_pos),
+                    (int)L.npad};
 }
 
 static NodePtrs node_ptrs(const kp_node_table &t)
@@ -602,7 +611,9 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     // small tables: the nodes-in-registers kernel (kp_place.cuh); its per-pod strategy groups are 32 slots wide
     // (pinned host pod rows read in place keep the paced place_kernel: the order in which the rows cross the
     // host link matters more there than the instruction count)
-    bool use_small = !big && !(tuning.flow && flow_window > 0 && !per_pod);
+    // and large pod counts / per-pod strategies keep it too: with thousands of pods per warp its fixed costs vanish
+    // and its tile loop is a little tighter (profiles/r02_slice_probe.txt)
+    bool use_small = !big && !per_pod && P <= kSmallMaxPods && !(tuning.flow && flow_window > 0);
     if (const char *v = getenv("KP_SMALL_OLD")) if (v[0] == '1') use_small = false;   // experiments only
     const int chunk_pods = use_small ? 32 : kPlaceCfgs[cfg].chunk;
     const int64_t n_chunks = (P + chunk_pods - 1) / chunk_pods + (per_pod ? kMaxStrategies - 1 : 0);
@@ -640,7 +651,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e0, stream));
     const unsigned long long sig = snapshot_plan_signature(n, P, per_pod, strategy, filter_mode);
     if (tuning.plan_sig) *tuning.plan_sig = sig;
-    if (tuning.reuse_plan && sig != 0ull) {
+    if (tuning.reuse_plan && (sig != 0ull || tuning.reuse_plan_forced)) {
         // the workspace holds this table's plan: only the per-call merge counters of the segmented form are reset
         if (big && L.zero_bytes > L.off_chunk_done)
             KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.zero_bytes - L.off_chunk_done, stream));
@@ -697,6 +708,8 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         KP_LAUNCH_CHECK("scatter_tables_kernel");
     }
 
+    if (tuning.plan_only) return KP_OK;
+
     // ---- pods ----
     if (per_pod) {
         const int gb = (int)((P + kGroupItems - 1) / kGroupItems);
@@ -729,7 +742,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     pp.out_idx = (long long *)out_idx;
     pp.out_score = out_score;
     pp.out_gpos = tuning.out_gpos;
-    pp.gpos_node = tuning.gpos_node;
+    pp.gpos_by_pos = tuning.gpos_by_pos;
     pp.gpos_stride = tuning.gpos_stride;
     // pacing applies to the kernels that fetch a CTA's requests up front (node splits, one strategy)
     const bool paced = tuning.flow && flow_window > 0 && !per_pod && !big && !use_small && kPlaceCfgs[cfg].nsplit > 1;

@@ -170,11 +170,16 @@ class NodeShardedPlacer:
         return group
 
     def close(self):
-        if getattr(self, "_h", None) and self._h.value:
-            self._lib.kp_exchange_destroy(self._h)
-            self._h = ctypes.c_void_p()
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self._h = None
+            self._lib.kp_exchange_destroy(h)
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 -- interpreter shutdown: modules may already be gone
+            pass
 
     def _structs(self, local_nodes, req_cpu_milli, req_mem_bytes, strategy):
         from . import placement
@@ -189,12 +194,11 @@ class NodeShardedPlacer:
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # the three steps, separately (ranks emulated on one device must be driven in lock step)
-    def keys(self, local_nodes, node_offset: int, strategy, per_pod: bool):
-        from . import placement
-        nst, _, _ = placement._node_struct(local_nodes)
+    def keys(self, local_nodes, node_offset: int, req_cpu_milli, req_mem_bytes, strategy, filter_mode: int = 1):
+        nst, pst, n, p, strat, per_pod = self._structs(local_nodes, req_cpu_milli, req_mem_bytes, strategy)
         with torch.cuda.device(self.device):
-            self._check(self._lib.kp_ns_keys(self._h, ctypes.byref(nst), int(node_offset), 0 if per_pod else int(strategy),
-                                             int(per_pod), self._stream()), "kp_ns_keys")
+            self._check(self._lib.kp_ns_keys(self._h, ctypes.byref(nst), int(node_offset), ctypes.byref(pst), strat, int(filter_mode),
+                                             self._ws.data_ptr(), self._ws.numel(), self._stream()), "kp_ns_keys")
 
     def scan(self, local_nodes, req_cpu_milli, req_mem_bytes, strategy, filter_mode: int = 1):
         nst, pst, n, p, strat, per_pod = self._structs(local_nodes, req_cpu_milli, req_mem_bytes, strategy)
@@ -215,8 +219,7 @@ class NodeShardedPlacer:
     def place(self, local_nodes: Dict[str, torch.Tensor], node_offset: int, req_cpu_milli: torch.Tensor,
               req_mem_bytes: torch.Tensor, strategy=0, filter_mode: int = 1, out=None):
         """Every rank: its node slice (CUDA tensors, list order), the slice's global start index, and the SAME pods."""
-        per_pod = isinstance(strategy, torch.Tensor)
-        self.keys(local_nodes, node_offset, strategy, per_pod)
+        self.keys(local_nodes, node_offset, req_cpu_milli, req_mem_bytes, strategy, filter_mode)
         self.scan(local_nodes, req_cpu_milli, req_mem_bytes, strategy, filter_mode)
         return self.reduce(out)
 

@@ -26,7 +26,7 @@ def run_emulated(nodes: NodeTable, pods: PodTable, world: int, strategy, per_pod
     strat = torch.as_tensor(pods.strategy_ids).to(dev) if per_pod else strategy
     for _ in range(rounds):                                    # several snapshots in a row: epochs, alternating buffers
         for g, (a, _) in zip(group, cuts):
-            g.keys(slices[g.rank], a, strat, per_pod)
+            g.keys(slices[g.rank], a, rc, rm, strat, 1)
         for g in group:
             g.scan(slices[g.rank], rc, rm, strat, 1)
         parts = [g.reduce() for g in group]
