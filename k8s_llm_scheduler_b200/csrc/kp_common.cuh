@@ -270,6 +270,9 @@ size_t sort_temp_bytes(int64_t n);
 int sort_pairs_u64(void *temp, size_t temp_bytes, const unsigned long long *keys_in, unsigned long long *keys_out,
                    const uint32_t *vals_in, uint32_t *vals_out, int n, cudaStream_t stream);
 int inclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream);
+int exclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream);
+int sort_pairs_u32_desc(void *temp, size_t temp_bytes, const uint32_t *keys_in, uint32_t *keys_out, const uint32_t *vals_in,
+                        uint32_t *vals_out, int64_t n, cudaStream_t stream);
 // diagnostics (kp_profile_enable): events around the node plan and the placement kernel
 struct ProfileEvents { bool enabled; bool valid; cudaEvent_t e0, e1, e2; };
 ProfileEvents &profile_events();

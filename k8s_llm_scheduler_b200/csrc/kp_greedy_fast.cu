@@ -22,6 +22,19 @@
 //    peer's shared memory and completes a transaction on the peer's mbarrier) and then waits
 //    on its own mbarrier only -- no cluster barrier on the per-pod path.
 //
+//  * EXACT BATCHING of a pod-independent prefix (one strategy, resource_balanced / least_loaded).  While every
+//    pod fits every state a node can still reach, a decision does not depend on the pod: the winner is the best
+//    (score, index) key among the nodes' current states, and a commit replaces that node's state by the next one
+//    of its trajectory, whose score is lower.  The sequence of chosen nodes is therefore the merge of the nodes'
+//    state streams by (score desc, index asc) -- ONE descending sort of all reachable (node, state) entries by the
+//    same 32-bit key the loop compares -- and pod j of the prefix simply gets entry j (or no node once the entries
+//    run out: the cluster is full).  The prefix ends at the first pod that does not fit the tightest reachable
+//    state; from there the sequential loop continues on the advanced node states.  Config 3 (every pod fits every
+//    node with room) is one such prefix from the first pod to the last: a sort for the whole GPU instead of a
+//    million dependent steps on one SM.  Preconditions (monotone streams, every reachable state choosable, entry
+//    count within the workspace) are checked on the device; pairs are not evaluated at all on this path, which
+//    bench.py reports separately from the pair rate of the scanning kernels.
+//
 // Whether the preconditions hold is decided on the device (ok flag); the fp64 kernel is always
 // launched behind this path and returns at once when the flag says the work is done.
 #include <algorithm>
@@ -260,6 +273,148 @@ fast_pods_kernel(FastIn in, const FastHeader *__restrict__ hdr, const double *__
 }
 
 // ---------------------------------------------------------------------------------------
+// 2b. exact batching of the pod-independent prefix
+// ---------------------------------------------------------------------------------------
+constexpr long long kBatchMinPods = 16384;      // host: calls with fewer pods skip the attempt
+constexpr unsigned long long kBatchMinRun = 4096;   // device: a shorter prefix is left to the loop
+
+struct BatchHeader {
+    uint32_t ok;                     // streams monotone, reachable states choosable, entry count within the buffers
+    uint32_t wmin;                   // field-wise minimum threshold word over every reachable choosable state
+    unsigned long long jstar;        // first pod that does not fit wmin (n_pods if none)
+    unsigned long long total;        // number of (node, state) entries
+    unsigned long long cap;          // entries the buffers hold
+};
+
+// pods decided by the sorted prefix (0: batching not used); the same predicate in every kernel that needs it
+__device__ __forceinline__ unsigned long long batch_n_done(const FastHeader *hdr, const BatchHeader *b)
+{
+    if (!b || !hdr->ok || !b->ok || b->total > b->cap || b->jstar < kBatchMinRun) return 0ull;
+    return b->jstar;
+}
+
+// One block.  Per choosable node: entry count = max_pods - pod_count; per shape: the lowest pod count any of its
+// choosable nodes starts from (every trajectory state above it is reachable).  Then every reachable state is
+// checked: it must be choosable, its key must not rise along the stream, and its threshold word joins wmin.
+__global__ void __launch_bounds__(1024, 1)
+batch_check_kernel(FastIn in, const FastHeader *__restrict__ hdr, const uint32_t *__restrict__ shape_id, const uint32_t *__restrict__ entry_w,
+                   const uint32_t *__restrict__ entry_key, int total, uint32_t *__restrict__ cnt, BatchHeader *b, unsigned long long cap)
+{
+    __shared__ unsigned s_minpc[kFastMaxShapes];
+    __shared__ unsigned s_wmin_lo, s_wmin_hi, s_bad;
+    __shared__ unsigned long long s_total;
+    const int tid = threadIdx.x;
+    if (tid < kFastMaxShapes) s_minpc[tid] = 0xffffffffu;
+    if (tid == 0) { s_wmin_lo = 0xffffu; s_wmin_hi = 0xffffu; s_bad = 0u; s_total = 0ull; }
+    __syncthreads();
+    const bool fast_ok = hdr->ok != 0;
+    const uint32_t *key = entry_key + (size_t)in.uniform_strategy * total;
+    unsigned wlo = 0xffffu, whi = 0xffffu, bad = 0u;
+    unsigned long long mine_total = 0ull;
+    for (int i = tid; i < in.n; i += 1024) {
+        uint32_t c = 0u;
+        const uint32_t sh = shape_id[i];
+        if (fast_ok && sh != kNoEntry && key[i] != 0u) {                  // choosable now
+            const long long pc = in.pod_count0[i], mp = in.max_pods[i];
+            c = (uint32_t)(mp - pc);
+            atomicMin(&s_minpc[sh & 0x7fu], (unsigned)pc);
+            const uint32_t w = entry_w[i];
+            wlo = min(wlo, w & 0xffffu); whi = min(whi, w >> 16);
+            if (pc + 1 < mp) {                                            // the stream must not rise at its first commit
+                const uint32_t nxt = key[in.n + hdr->traj_base[sh & 0x7fu] + (uint32_t)pc + 1u];
+                if (nxt > key[i]) bad = 1u;
+            }
+        }
+        cnt[i] = c;
+        mine_total += c;
+    }
+    __syncthreads();                                                       // s_minpc complete
+    if (fast_ok) {
+        const int ns = (int)hdr->n_shapes;
+        for (int t = tid; t < (int)hdr->traj_total; t += 1024) {
+            int sh = 0;
+            while (sh + 1 < ns && hdr->traj_base[sh + 1] <= (uint32_t)t) ++sh;
+            const unsigned pc = (unsigned)t - hdr->traj_base[sh];
+            const unsigned mp = (unsigned)hdr->shape_mp[sh];
+            if (s_minpc[sh] == 0xffffffffu || pc <= s_minpc[sh] || pc >= mp) continue;   // not reachable, or full
+            const uint32_t k = key[in.n + t];
+            if (k == 0u) bad = 1u;                                         // a state that can never be chosen ends a stream early
+            if (pc > s_minpc[sh] + 1u && k > key[in.n + t - 1]) bad = 1u;  // keys must not rise along the trajectory
+            const uint32_t w = entry_w[in.n + t];
+            wlo = min(wlo, w & 0xffffu); whi = min(whi, w >> 16);
+        }
+    }
+    atomicMin(&s_wmin_lo, wlo);
+    atomicMin(&s_wmin_hi, whi);
+    if (bad) s_bad = 1u;
+    atomicAdd(&s_total, mine_total);
+    __syncthreads();
+    if (tid == 0) {
+        b->ok = (fast_ok && !s_bad) ? 1u : 0u;
+        b->wmin = (s_wmin_hi << 16) | s_wmin_lo;
+        b->jstar = (unsigned long long)in.n_pods;
+        b->total = s_total;
+        b->cap = cap;
+    }
+}
+
+// first pod whose request does not fit the tightest reachable state
+__global__ void __launch_bounds__(256)
+batch_violation_kernel(FastIn in, const FastHeader *__restrict__ hdr, const uint32_t *__restrict__ xs, BatchHeader *b)
+{
+    if (!hdr->ok || !b->ok) return;
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    bool viol = false;
+    if (j < in.n_pods) viol = ((~(b->wmin - xs[j])) & kFastGuards) != 0u;
+    const unsigned m = __ballot_sync(0xffffffffu, viol);
+    if (m && (threadIdx.x & 31) == __ffs(m) - 1) atomicMin(&b->jstar, (unsigned long long)j);
+}
+
+// one warp per node: its entries (initial state, then the trajectory states up to max_pods - 1) with the loop's own key
+__global__ void __launch_bounds__(256)
+batch_entries_kernel(FastIn in, const FastHeader *__restrict__ hdr, const BatchHeader *__restrict__ b, const uint32_t *__restrict__ shape_id,
+                     const uint32_t *__restrict__ entry_key, int total, int idx_bits, const uint32_t *__restrict__ cnt,
+                     const uint32_t *__restrict__ off, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    if (batch_n_done(hdr, b) == 0ull) return;
+    const int node = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (node >= in.n) return;
+    const uint32_t c = cnt[node];
+    if (c == 0u) return;
+    const uint32_t *key = entry_key + (size_t)in.uniform_strategy * total;
+    const uint32_t idx_mask = (1u << idx_bits) - 1u;
+    const uint32_t low = idx_mask - (uint32_t)node;
+    const uint32_t t0 = (uint32_t)in.n + hdr->traj_base[shape_id[node] & 0x7fu] + (uint32_t)in.pod_count0[node];   // entry of state k is t0 + k
+    const uint32_t o = off[node];
+    for (uint32_t k = lane; k < c; k += 32) {
+        const uint32_t e = k == 0u ? (uint32_t)node : t0 + k;
+        keys[o + k] = (key[e] << idx_bits) | low;
+        vals[o + k] = e;
+    }
+}
+
+// pod j of the prefix takes sorted entry j; behind the last entry the cluster is full
+__global__ void __launch_bounds__(256)
+batch_assign_kernel(FastIn in, const FastHeader *__restrict__ hdr, const BatchHeader *__restrict__ b, const uint32_t *__restrict__ keys,
+                    const uint32_t *__restrict__ vals, int idx_bits, long long *__restrict__ out_idx, uint32_t *__restrict__ out_entry,
+                    uint32_t *__restrict__ commits)
+{
+    const unsigned long long done = batch_n_done(hdr, b);
+    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= done) return;
+    if (j < b->total) {
+        const uint32_t idx_mask = (1u << idx_bits) - 1u;
+        const int node = (int)(idx_mask - (keys[j] & idx_mask));
+        out_idx[j] = node;
+        out_entry[j] = vals[j];
+        atomicAdd(&commits[node], 1u);
+    } else {
+        out_idx[j] = -1;
+        out_entry[j] = kNoEntry;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // 3. the greedy loop
 // ---------------------------------------------------------------------------------------
 struct FastRun {
@@ -273,6 +428,8 @@ struct FastRun {
     long long *out_pc;             // final pod counts (may be NULL)
     double *out_cu, *out_mu;
     int total, idx_bits, nodes_per_cta;
+    const BatchHeader *batch;      // exact batching of the prefix (NULL = not attempted)
+    const uint32_t *commits;       // [n] commits the prefix made to every node
 };
 
 // dynamic shared memory: traj_w[kFastMaxTraj] | traj_key[KS][kFastMaxTraj] | c_t[nodes_per_cta]
@@ -378,6 +535,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
     const int us = in.uniform_strategy;
     const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
     const int cta_base = crank * r.nodes_per_cta;
+    const long long n_done = (long long)batch_n_done(r.hdr, r.batch);   // pods the sorted prefix has already decided
 
     if (tid <= kFastMaxShapes) s_tbase[tid] = r.hdr->traj_base[tid];
     for (int i = tid; i < kFastMaxTraj; i += kFastThreads) {
@@ -394,16 +552,22 @@ fast_greedy_kernel(FastIn in, FastRun r)
 #pragma unroll
         for (int q = 0; q < KS; ++q) key[q][k] = 0u;
         if (local < r.nodes_per_cta && n < in.n) {
-            w[k] = r.entry_w[n];
-#pragma unroll
-            for (int q = 0; q < KS; ++q) {
-                const uint32_t kr = r.entry_key[(size_t)(MULTI ? q : us) * total + n];
-                key[q][k] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
-            }
             // trajectory index of the state with this node's pod count (its NEXT state is one further);
             // nodes that can never be chosen have no shape and are never committed to
             const uint32_t sh = r.shape_id[n];
-            c_t[local] = sh == kNoEntry ? 0u : (r.hdr->traj_base[sh & 0x7fu] + (uint32_t)in.pod_count0[n]) & 0x7fffffffu;
+            uint32_t ct = sh == kNoEntry ? 0u : (r.hdr->traj_base[sh & 0x7fu] + (uint32_t)in.pod_count0[n]) & 0x7fffffffu;
+            // the state this node is in when the loop starts: its initial entry, or -- after a batched prefix that
+            // committed to it -- the trajectory state that many pods further
+            const uint32_t adv = n_done ? r.commits[n] : 0u;
+            uint32_t e = (uint32_t)n;
+            if (adv) { ct = (ct + adv) | 0x80000000u; e = (uint32_t)in.n + (ct & 0x7fffffffu); }
+            c_t[local] = ct;
+            w[k] = r.entry_w[e];
+#pragma unroll
+            for (int q = 0; q < KS; ++q) {
+                const uint32_t kr = r.entry_key[(size_t)(MULTI ? q : us) * total + e];
+                key[q][k] = kr ? (kr << r.idx_bits) | (idx_mask - (uint32_t)n) : 0u;
+            }
         }
     }
     uint32_t wmin = 0u, kbest = 0u;                                    // uniform strategy only (one key per node)
@@ -417,7 +581,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
     __syncthreads();
     if (CLUSTER) cluster_barrier();                                    // every CTA's mbarriers exist before any peer signals them
 
-    for (long long base = 0; base < in.n_pods; base += kFastPodBatch) {
+    for (long long base = n_done; base < in.n_pods; base += kFastPodBatch) {
         const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
         __syncthreads();
         for (int i = tid; i < cnt; i += kFastThreads) {
@@ -540,6 +704,9 @@ struct FastLayout {
     int64_t total;
     size_t off_hdr, off_shape, off_iota, off_keys, off_score, off_kout, off_vout, off_flag, off_incl, off_rank,
         off_uniq, off_w, off_key32, off_xs, off_entry, off_tmp, tmp_bytes, bytes;
+    // exact batching (only for calls with at least kBatchMinPods pods): entry buffers for up to batch_cap entries
+    size_t off_bhdr, off_bcnt, off_boff, off_bcommits, off_bkeys[2], off_bvals[2];
+    int64_t batch_cap;
 };
 
 static FastLayout fast_layout(int64_t n, int64_t p)
@@ -563,7 +730,16 @@ static FastLayout fast_layout(int64_t n, int64_t p)
     L.off_key32 = o; o = align_up(o + sizeof(uint32_t) * kMaxStrategies * T);
     L.off_xs = o;    o = align_up(o + sizeof(uint32_t) * p);
     L.off_entry = o; o = align_up(o + sizeof(uint32_t) * p);
-    L.tmp_bytes = sort_temp_bytes(L.total);
+    L.batch_cap = p >= kBatchMinPods ? 2 * p : 0;                     // more reachable states than twice the pods: the loop does it
+    L.off_bhdr = o;     o = align_up(o + sizeof(BatchHeader));
+    L.off_bcnt = o;     o = align_up(o + sizeof(uint32_t) * (L.batch_cap ? n : 0));
+    L.off_boff = o;     o = align_up(o + sizeof(uint32_t) * (L.batch_cap ? n : 0));
+    L.off_bcommits = o; o = align_up(o + sizeof(uint32_t) * (L.batch_cap ? n : 0));
+    for (int b = 0; b < 2; ++b) {
+        L.off_bkeys[b] = o; o = align_up(o + sizeof(uint32_t) * L.batch_cap);
+        L.off_bvals[b] = o; o = align_up(o + sizeof(uint32_t) * L.batch_cap);
+    }
+    L.tmp_bytes = std::max(sort_temp_bytes(L.total), L.batch_cap ? sort_temp_bytes(L.batch_cap) : (size_t)0);
     L.off_tmp = o;   o = align_up(o + L.tmp_bytes);
     L.bytes = o;
     return L;
@@ -735,8 +911,35 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
     fast_pods_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, uniq, uniq + total, xs);
     KP_LAUNCH_CHECK("fast_pods_kernel");
 
+    // exact batching of the pod-independent prefix (one strategy whose scores fall with every commit)
+    BatchHeader *bh = nullptr;
+    uint32_t *commits = nullptr;
+    if (L.batch_cap > 0 && !multi && in.uniform_strategy != 2 && n < (1 << 24)) {
+        bh = reinterpret_cast<BatchHeader *>(w + L.off_bhdr);
+        uint32_t *cnt = reinterpret_cast<uint32_t *>(w + L.off_bcnt), *off = reinterpret_cast<uint32_t *>(w + L.off_boff);
+        commits = reinterpret_cast<uint32_t *>(w + L.off_bcommits);
+        uint32_t *bk0 = reinterpret_cast<uint32_t *>(w + L.off_bkeys[0]), *bk1 = reinterpret_cast<uint32_t *>(w + L.off_bkeys[1]);
+        uint32_t *bv0 = reinterpret_cast<uint32_t *>(w + L.off_bvals[0]), *bv1 = reinterpret_cast<uint32_t *>(w + L.off_bvals[1]);
+        KP_CUDA(cudaMemsetAsync(commits, 0, sizeof(uint32_t) * (size_t)n, stream));
+        KP_CUDA(cudaMemsetAsync(bk0, 0, sizeof(uint32_t) * (size_t)L.batch_cap, stream));          // unused slots sort last
+        batch_check_kernel<<<1, 1024, 0, stream>>>(in, hdr, shape_id, entry_w, key32, total, cnt, bh, (unsigned long long)L.batch_cap);
+        KP_LAUNCH_CHECK("batch_check_kernel");
+        batch_violation_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, xs, bh);
+        KP_LAUNCH_CHECK("batch_violation_kernel");
+        int st = exclusive_sum_u32(tmp, L.tmp_bytes, cnt, off, (int)n, stream);
+        if (st != KP_OK) return st;
+        batch_entries_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, stream>>>(in, hdr, bh, shape_id, key32, total, idx_bits, cnt, off, bk0, bv0);
+        KP_LAUNCH_CHECK("batch_entries_kernel");
+        st = sort_pairs_u32_desc(tmp, L.tmp_bytes, bk0, bk1, bv0, bv1, L.batch_cap, stream);
+        if (st != KP_OK) return st;
+        batch_assign_kernel<<<(int)((p + 255) / 256), 256, 0, stream>>>(in, hdr, bh, bk1, bv1, idx_bits, (long long *)out_idx, out_entry, commits);
+        KP_LAUNCH_CHECK("batch_assign_kernel");
+    }
+
     FastRun r{};
     r.hdr = hdr;
+    r.batch = bh;
+    r.commits = commits;
     r.shape_id = shape_id;
     r.entry_w = entry_w;
     r.entry_key = key32;

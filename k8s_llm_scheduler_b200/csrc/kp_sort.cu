@@ -35,6 +35,23 @@ int sort_pairs_u64(void *temp, size_t temp_bytes, const unsigned long long *keys
     return KP_OK;
 }
 
+// descending 32-bit keys with 32-bit values (the batched greedy prefix: state entries by (score rank, node index))
+int sort_pairs_u32_desc(void *temp, size_t temp_bytes, const uint32_t *keys_in, uint32_t *keys_out, const uint32_t *vals_in,
+                        uint32_t *vals_out, int64_t n, cudaStream_t stream)
+{
+    if (n <= 0) return KP_OK;
+    KP_CUDA(cub::DeviceRadixSort::SortPairsDescending(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, 32, stream));
+    count_launch(3);
+    return KP_OK;
+}
+
+int exclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream)
+{
+    KP_CUDA(cub::DeviceScan::ExclusiveSum(temp, temp_bytes, in, out, n, stream));
+    count_launch(2);
+    return KP_OK;
+}
+
 int inclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream)
 {
     KP_CUDA(cub::DeviceScan::InclusiveSum(temp, temp_bytes, in, out, n, stream));

@@ -192,6 +192,34 @@ def test_fast_path_falls_back_when_preconditions_fail():
     _check_greedy(nodes, pods, 0, 1, what="huge max_pods")
 
 
+@pytest.mark.parametrize("strategy", [0, 1])
+def test_batched_prefix_and_hand_over_to_the_loop(strategy):
+    """Exact batching (kp_greedy_fast.cu): while every pod fits every reachable node state the decisions are one
+    sort; the first pod that does not ends the prefix and the sequential loop continues on the advanced states.
+    The violating pod is placed at several depths (before the minimum run length, inside the run, after the
+    cluster has filled up); every variant must equal the oracle pod for pod, state for state."""
+    nodes, base = synth.config3(600, 40_000, seed=90 + strategy)           # 600 x ~82 free slots: fills around pod 49 000
+    for where in (None, 100, 5_000, 22_222, 39_999):
+        pods = PodTable.from_columns(base.req_cpu_milli.copy(), base.req_mem_bytes.copy())
+        if where is not None:
+            pods.req_cpu_milli[where] = 17_000                             # fits an empty node (32 cores x 0.5+), not a loaded one
+            pods.req_cpu_milli[where + 1 if where + 1 < len(pods) else where] = 40_000   # fits nothing
+        _check_greedy(nodes, pods, strategy, 1, what=f"violation at {where}")
+    nodes, pods = synth.config3(300, 60_000, seed=93)                      # more pods than free slots: the entries run out
+    _check_greedy(nodes, pods, strategy, 1, what="entries run out inside the prefix")
+    # usage that does not follow scheduler.py:150-151: a node's score may RISE at its first commit -> no batching
+    nodes, pods = synth.config3(500, 30_000, seed=94)
+    rng = np.random.Generator(np.random.PCG64(95))
+    nodes.cpu_usage_pct[:] = np.round(rng.random(500) * 90, 2)
+    nodes.mem_usage_pct[:] = np.round(rng.random(500) * 90, 2)
+    _check_greedy(nodes, pods, strategy, 1, what="custom usage")
+    # heterogeneous shapes, all pods small enough for the tightest state of the smallest shape
+    nodes, pods = synth.config5(3000, 50_000, seed=96, infeasible=0.0)
+    pods.req_cpu_milli[:] = np.minimum(pods.req_cpu_milli, 1_900)
+    pods.req_mem_bytes[:] = np.minimum(pods.req_mem_bytes, 7 << 30)
+    _check_greedy(nodes, pods, strategy, 1, what="heterogeneous shapes")
+
+
 def test_full_size_config3_greedy():
     """BASELINE config 3 at full size (5k nodes x 1M pods, resource_balanced, sequential commit):
     conservation properties at full size; exact parity with the oracle on the first 30k pods (a
