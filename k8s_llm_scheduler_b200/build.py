@@ -81,6 +81,36 @@ def build_pyobj(force: bool = False) -> Path:
     return out
 
 
+TORCH_EXT_NAME = "libk8s_place_torch.so"
+TORCH_EXT_PATH = PKG_DIR / TORCH_EXT_NAME
+
+
+def build_torch_ext(force: bool = False) -> Path:
+    """g++ build of the PyTorch-extension form of the ops (csrc/kp_torch_ext.cpp: TORCH_LIBRARY(k8s_place, ...)),
+    in-tree and linked against libk8s_place_b200.so next to it (rpath $ORIGIN).  No nvcc: the file holds no kernels."""
+    import torch
+    from torch.utils import cpp_extension as ce
+    src = CSRC / "kp_torch_ext.cpp"
+    deps = [src, PKG_DIR.parent / "include" / "k8s_place_b200.h"]
+    if not force and TORCH_EXT_PATH.exists() and all(TORCH_EXT_PATH.stat().st_mtime >= d.stat().st_mtime for d in deps):
+        return TORCH_EXT_PATH
+    build_library()
+    cxx = os.environ.get("CXX") or shutil.which("g++") or shutil.which("c++")
+    if not cxx:
+        raise RuntimeError("no C++ compiler for the PyTorch extension")
+    cuda_home = Path(find_nvcc()).resolve().parents[1]
+    inc = [f"-I{p}" for p in ce.include_paths()] + [f"-I{cuda_home / 'include'}"]
+    libdir = ce.library_paths()[0]
+    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           *inc, str(src), "-o", str(TORCH_EXT_PATH), f"-L{PKG_DIR}", f"-l:{LIB_NAME}", f"-L{libdir}",
+           "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{libdir}"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"{cxx} failed:\n{res.stdout}\n{res.stderr}")
+    return TORCH_EXT_PATH
+
+
 if __name__ == "__main__":
     print(build_library(force=True, verbose=True))
     print(build_pyobj(force=True))
+    print(build_torch_ext(force=True))

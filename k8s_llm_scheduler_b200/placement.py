@@ -1,9 +1,11 @@
-"""Placement ops over CUDA tensors, and the host-buffer session -- thin callers of the C ABI.
+"""Placement ops over CUDA tensors, and the host-buffer session.
 
-``snapshot_place`` / ``greedy_place`` / ``node_scores`` take int64 / float64 CUDA tensors
-(the PyTorch-facing form named by the north star) and launch on torch's current stream.
-``Session`` takes host numpy arrays (or pinned torch tensors) and is what the
-reference-facing adapter uses.  PyTorch is plumbing here: device memory and streams.
+``snapshot_place`` / ``greedy_place`` / ``node_scores`` take int64 / float64 CUDA tensors and launch on
+torch's current stream.  They are registered PyTorch operators -- ``torch.ops.k8s_place.*`` (csrc/kp_torch_ext.cpp,
+``TORCH_LIBRARY(k8s_place, ...)``, CUDA dispatch key only), the extension form the north star names -- which call
+the C ABI of libk8s_place_b200.so; the functions here are their Python signatures (a dict of node columns instead
+of seven positional tensors).  ``Session`` takes host numpy arrays (or pinned torch tensors) through ctypes and is
+what the reference-facing adapter uses.  PyTorch is plumbing here: device memory, streams, the dispatcher.
 Nothing in this module computes a placement on the CPU.
 """
 from __future__ import annotations
@@ -22,6 +24,25 @@ from .tables import NODE_COLUMNS, NodeTable, PodTable
 _NODE_DTYPES = {"alloc_cpu_milli": torch.int64, "alloc_mem_bytes": torch.int64,
                 "pod_count": torch.int64, "max_pods": torch.int64, "ready": torch.uint8,
                 "cpu_usage_pct": torch.float64, "mem_usage_pct": torch.float64}
+
+
+_OPS = [None]
+
+
+def ops():
+    """``torch.ops.k8s_place`` with the extension library loaded (raises if it has not been built: no fallback)."""
+    if _OPS[0] is None:
+        from .build import TORCH_EXT_PATH
+        _lib.load()                                   # the C-ABI library the extension links against
+        if not TORCH_EXT_PATH.exists():
+            raise ImportError(f"{TORCH_EXT_PATH} not found: build it with `python -m k8s_llm_scheduler_b200.build`")
+        torch.ops.load_library(str(TORCH_EXT_PATH))
+        _OPS[0] = torch.ops.k8s_place
+    return _OPS[0]
+
+
+def _cols(nodes: Dict[str, torch.Tensor]):
+    return tuple(nodes[k] for k in NODE_COLUMNS)
 
 
 def _dev_col(t: torch.Tensor, name: str, dtype: torch.dtype, device: torch.device, n: int):
@@ -76,6 +97,12 @@ def _workspace(nbytes: int, device, workspace: Optional[torch.Tensor]) -> torch.
     return workspace
 
 
+def _strategy_args(strategy):
+    if isinstance(strategy, torch.Tensor):
+        return strategy, 0
+    return None, int(strategy)
+
+
 def snapshot_workspace_bytes(n_nodes: int, n_pods: int, per_pod_strategy: bool) -> int:
     return int(_lib.load().kp_snapshot_workspace_bytes(n_nodes, n_pods, int(per_pod_strategy)))
 
@@ -92,23 +119,16 @@ def snapshot_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
 
     Returns (node_idx int64[P], score float64[P]); idx -1 / score -1.0 = no node.
     """
-    lib = _lib.load()
-    nst, device, n = _node_struct(nodes)
-    pst, p, strat, per_pod = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
+    sid, strat = _strategy_args(strategy)
+    op = ops()
+    if out is None and workspace is None:
+        return op.snapshot_place(*_cols(nodes), req_cpu_milli, req_mem_bytes, sid, strat, int(filter_mode))
+    device, n, p = req_cpu_milli.device, nodes["pod_count"].numel(), req_cpu_milli.numel()
     if out is None:
-        out_idx = torch.empty(p, dtype=torch.int64, device=device)
-        out_score = torch.empty(p, dtype=torch.float64, device=device)
-    else:
-        out_idx, out_score = out
-        _dev_col(out_idx, "out_idx", torch.int64, device, p)
-        _dev_col(out_score, "out_score", torch.float64, device, p)
-    ws = _workspace(snapshot_workspace_bytes(n, p, per_pod), device, workspace)
-    with torch.cuda.device(device):
-        stream = torch.cuda.current_stream(device).cuda_stream
-        check(lib.kp_snapshot_place(byref(nst), byref(pst), strat, int(filter_mode),
-                                    out_idx.data_ptr(), out_score.data_ptr(), ws.data_ptr(),
-                                    ws.numel(), c_void_p(stream)), "kp_snapshot_place")
-    return out_idx, out_score
+        out = (torch.empty(p, dtype=torch.int64, device=device), torch.empty(p, dtype=torch.float64, device=device))
+    ws = _workspace(snapshot_workspace_bytes(n, p, sid is not None), device, workspace)
+    op.snapshot_place_out(*_cols(nodes), req_cpu_milli, req_mem_bytes, sid, strat, int(filter_mode), out[0], out[1], ws)
+    return out[0], out[1]
 
 
 def greedy_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
@@ -119,38 +139,13 @@ def greedy_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
     Returns (node_idx, score, final_pod_count, final_cpu_usage_pct, final_mem_usage_pct).
     The input node tensors are not modified.
     """
-    lib = _lib.load()
-    nst, device, n = _node_struct(nodes)
-    pst, p, strat, _ = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
-    out_idx = torch.empty(p, dtype=torch.int64, device=device)
-    out_score = torch.empty(p, dtype=torch.float64, device=device)
-    out_pc = torch.empty(n, dtype=torch.int64, device=device)
-    out_cu = torch.empty(n, dtype=torch.float64, device=device)
-    out_mu = torch.empty(n, dtype=torch.float64, device=device)
-    ws = _workspace(greedy_workspace_bytes(n, p), device, workspace)
-    with torch.cuda.device(device):
-        stream = torch.cuda.current_stream(device).cuda_stream
-        check(lib.kp_greedy_place(byref(nst), byref(pst), strat, int(filter_mode),
-                                  out_idx.data_ptr(), out_score.data_ptr(), out_pc.data_ptr(),
-                                  out_cu.data_ptr(), out_mu.data_ptr(), ws.data_ptr(), ws.numel(),
-                                  c_void_p(stream)), "kp_greedy_place")
-    return out_idx, out_score, out_pc, out_cu, out_mu
+    sid, strat = _strategy_args(strategy)
+    return ops().greedy_place(*_cols(nodes), req_cpu_milli, req_mem_bytes, sid, strat, int(filter_mode), workspace)
 
 
 def node_scores(nodes: Dict[str, torch.Tensor], strategy: int = 0, filter_mode: int = FILTER_CAPACITY):
     """Per-node score, free cpu cores, free memory GiB, eligibility (scheduler.py:537-545, :232-233)."""
-    lib = _lib.load()
-    nst, device, n = _node_struct(nodes)
-    score = torch.empty(n, dtype=torch.float64, device=device)
-    fc = torch.empty(n, dtype=torch.float64, device=device)
-    fm = torch.empty(n, dtype=torch.float64, device=device)
-    el = torch.empty(n, dtype=torch.uint8, device=device)
-    with torch.cuda.device(device):
-        stream = torch.cuda.current_stream(device).cuda_stream
-        check(lib.kp_node_scores(byref(nst), int(strategy), int(filter_mode), score.data_ptr(),
-                                 fc.data_ptr(), fm.data_ptr(), el.data_ptr(), c_void_p(stream)),
-              "kp_node_scores")
-    return score, fc, fm, el
+    return ops().node_scores(*_cols(nodes), int(strategy), int(filter_mode))
 
 
 def launch_count() -> int:
