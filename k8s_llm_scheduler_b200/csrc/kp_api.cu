@@ -1,6 +1,7 @@
 // C ABI of the placement library (declared in include/k8s_place_b200.h).
 // Validation, error strings, device queries and the host-pointer "session" that owns its
 // device buffers.  No exceptions cross this boundary; every entry point returns a status.
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -106,10 +107,15 @@ struct kp_session {
     // node plan kept in d_ws for the resident table (kp_session_set_nodes + snapshots with nodes == NULL):
     // signature of the last snapshot's plan, 0 = none; cleared whenever the table or the workspace changes hands
     unsigned long long plan_sig = 0;
+    // large uploads are pipelined: pod columns go up in chunks on copy_stream while earlier chunks are scored
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t chunk_ready[2] = {nullptr};
 };
 
 namespace {
 
+constexpr int kPipeMaxChunks = 2;
+constexpr int64_t kPipeChunkMinPods = 1 << 19;   // below two pieces of this size one copy + one launch is as good
 constexpr unsigned kFlowWindowCtas = 64;      // request rows of this many CTAs in flight on the host link
 constexpr size_t kStageMaxBytes = 1u << 20;   // node tables up to ~18 k rows travel as one copy
 
@@ -438,6 +444,8 @@ int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_sessio
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_out, 2 * pcol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_state, 3 * ncol + kAlign);
     if (e == cudaSuccess) e = cudaMalloc(&s->d_ws, s->ws_bytes + kAlign);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);
+    for (int c = 0; e == cudaSuccess && c < kPipeMaxChunks; ++c) e = cudaEventCreateWithFlags(&s->chunk_ready[c], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_flow, kAlign);
     if (e == cudaSuccess) e = cudaMemset(s->d_flow, 0, kAlign);
     if (e == cudaSuccess) {
@@ -466,6 +474,8 @@ void kp_session_destroy(kp_session *s)
     cudaFree(s->d_ws);
     cudaFree(s->d_flow);
     if (s->h_stage) cudaFreeHost(s->h_stage);
+    for (int c = 0; c < kPipeMaxChunks; ++c) if (s->chunk_ready[c]) cudaEventDestroy(s->chunk_ready[c]);
+    if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -535,20 +545,57 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
             out_in_place = true;
         }
     }
-    if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return fail_drained(s, st);
-    PlaceTuning tuning;
-    if (in_place) {
-        tuning.flow = s->d_flow;
-        tuning.flow_window = kFlowWindowCtas;
+    // Many pods, one strategy: the pod columns go up in TWO pieces on a second stream -- a small first one, so that
+    // scoring starts early, and the rest, which travels while the first is scored (against the same node plan).
+    // Scoring a pod costs about n_nodes / 3500 times what copying it costs, which sizes the first piece; more,
+    // equal pieces would only multiply the placement kernel's start-up and tail.
+    const int64_t P = pods->n_pods;
+    const bool pipelined = !in_place && pods->strategy_ids == nullptr && filter_mode == KP_FILTER_CAPACITY && P <= s->max_pods &&
+                           P >= 2 * kPipeChunkMinPods;
+    const int nchunks = pipelined ? 2 : 0;
+    int64_t cut[3] = {0, 0, P};
+    if (pipelined) {
+        const double f = std::min(0.5, std::max(1.0 / 16, 3500.0 / (3500.0 + (double)dn.n_nodes)));
+        cut[1] = std::max<int64_t>(kPipeChunkMinPods, (int64_t)(f * (double)P));
     }
-    // resident table, same strategy / filter / layout as the snapshot before: its node plan is still in d_ws
     unsigned long long sig = 0;
-    tuning.plan_sig = &sig;
-    tuning.reuse_plan = s->plan_sig != 0 &&
-                        s->plan_sig == snapshot_plan_signature(dn.n_nodes, dp.n_pods, dp.strategy_ids != nullptr, strategy, filter_mode);
+    const unsigned long long want_sig = snapshot_plan_signature(dn.n_nodes, P, pods->strategy_ids != nullptr, strategy, filter_mode);
+    const bool resident_plan = s->plan_sig != 0 && s->plan_sig == want_sig;
     s->plan_sig = 0;
-    st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream, tuning);
-    if (st != KP_OK) return fail_drained(s, st);
+    if (nchunks >= 2) {
+        const int64_t *h_rc = pods->req_cpu_milli, *h_rm = pods->req_mem_bytes;
+        int64_t *g_rc = reinterpret_cast<int64_t *>(s->d_pods), *g_rm = reinterpret_cast<int64_t *>(s->d_pods + pcol);
+        for (int c = 0; c < nchunks; ++c) {
+            const int64_t lo = cut[c], hi = cut[c + 1];
+            const size_t bytes = sizeof(int64_t) * (size_t)(hi - lo);
+            KP_CUDA(cudaMemcpyAsync(g_rc + lo, h_rc + lo, bytes, cudaMemcpyHostToDevice, s->copy_stream));
+            KP_CUDA(cudaMemcpyAsync(g_rm + lo, h_rm + lo, bytes, cudaMemcpyHostToDevice, s->copy_stream));
+            KP_CUDA(cudaEventRecord(s->chunk_ready[c], s->copy_stream));
+        }
+        s->h2d += 2 * (int64_t)b8;
+        for (int c = 0; c < nchunks; ++c) {
+            const int64_t lo = cut[c], hi = cut[c + 1];
+            KP_CUDA(cudaStreamWaitEvent(s->stream, s->chunk_ready[c], 0));
+            kp_pod_table part{hi - lo, g_rc + lo, g_rm + lo, nullptr};
+            PlaceTuning tuning;
+            tuning.plan_sig = &sig;
+            tuning.reuse_plan = c > 0 || resident_plan;
+            st = snapshot_place_device(dn, part, strategy, filter_mode, d_idx + lo, d_score + lo, s->d_ws, s->ws_bytes, s->stream, tuning);
+            if (st != KP_OK) { cudaStreamSynchronize(s->copy_stream); return fail_drained(s, st); }
+        }
+    } else {
+        if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return fail_drained(s, st);
+        PlaceTuning tuning;
+        if (in_place) {
+            tuning.flow = s->d_flow;
+            tuning.flow_window = kFlowWindowCtas;
+        }
+        // resident table, same strategy / filter as the snapshot before: its node plan is still in d_ws
+        tuning.plan_sig = &sig;
+        tuning.reuse_plan = resident_plan;
+        st = snapshot_place_device(dn, dp, strategy, filter_mode, d_idx, d_score, s->d_ws, s->ws_bytes, s->stream, tuning);
+        if (st != KP_OK) return fail_drained(s, st);
+    }
     s->plan_sig = sig;
     if (b8) {
         if (!out_in_place) {

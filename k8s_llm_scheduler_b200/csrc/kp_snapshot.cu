@@ -50,7 +50,9 @@ struct SnapLayout {
     int64_t npad;        // n rounded up to a multiple of 4, plus slack for 16-byte copies
     int64_t slots;       // pod slots incl. per-strategy chunk padding
     int64_t chunks;      // pod chunks at the smallest chunk size (32)
-    size_t off_header, off_chunk_done, zero_bytes;            // zeroed together (large-table plan)
+    size_t off_header, off_chunk_done, chunk_done_bytes;      // both zeroed by the large-table plan; the per-pod arrays
+                                                              // (chunk_done, perm, best) sit BEHIND the plan, whose offsets
+                                                              // therefore depend on the node count alone
     size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_perm;
     size_t off_pos, off_kout, off_vout, off_iota, off_sorted, off_flag, off_incl, off_sort_tmp, off_best;   // large tables
     size_t sort_tmp_bytes, total;
@@ -69,8 +71,6 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     const bool big = n > kSmallMaxNodes;                 // multi-kernel plan, node segments possible
     size_t o = 0;
     L.off_header = o;     o = align_up(o + sizeof(SnapHeader));
-    L.off_chunk_done = o; o = align_up(o + sizeof(uint32_t) * (big ? L.chunks : 0));
-    L.zero_bytes = o;
     L.off_keys = o;    o = align_up(o + sizeof(uint64_t) * kKeyArrays * n);
     L.off_score = o;   o = align_up(o + sizeof(double) * kMaxStrategies * n);
     L.off_score_pos = o; o = align_up(o + sizeof(double) * kMaxStrategies * L.npad);
@@ -79,7 +79,6 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
     L.off_packed = o;  o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_partial = o; o = align_up(o + (sizeof(uint64_t) + sizeof(uint32_t) * 2) * kMaxStrategies * kArgmaxMaxBlocks);
-    L.off_perm = o;    o = align_up(o + sizeof(uint32_t) * (per_pod ? L.slots : 0));
     const int64_t nb = big ? n : 0, npb = big ? L.npad : 0;
     L.sort_tmp_bytes = big ? align_up(sort_temp_bytes(n)) : 0;            // per sorted array (they run concurrently)
     L.off_pos = o;      o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
@@ -90,6 +89,8 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_flag = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
     L.off_incl = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
     L.off_sort_tmp = o; o = align_up(o + L.sort_tmp_bytes * (kMaxStrategies + 2));
+    L.off_chunk_done = o; L.chunk_done_bytes = sizeof(uint32_t) * (big ? L.chunks : 0); o = align_up(o + L.chunk_done_bytes);
+    L.off_perm = o;     o = align_up(o + sizeof(uint32_t) * (per_pod ? L.slots : 0));
     L.off_best = o;     o = align_up(o + sizeof(uint32_t) * (big ? L.slots : 0));
     L.total = o;
     return L;
@@ -109,9 +110,9 @@ bool snapshot_single_pass(int64_t n_nodes, bool per_pod)
     return n_nodes <= kSmallMaxNodes && !per_pod;
 }
 
-// What a node plan depends on besides the node table: which strategy tables were built, the filter, and where
-// the arrays sit in the workspace (for large tables the layout moves with the pod count).  Plans with per-pod
-// strategies are not reused: their header carries per-call pod group counters.
+// What a node plan depends on besides the node table: which strategy table was built and the filter (the plan's
+// place in the workspace depends on the node count alone).  Plans with per-pod strategies are not reused: their
+// header carries per-call pod group counters.
 unsigned long long snapshot_plan_signature(int64_t n_nodes, int64_t n_pods, bool per_pod, int strategy, int filter_mode)
 {
     if (per_pod || filter_mode != KP_FILTER_CAPACITY || n_nodes <= 0) return 0ull;
@@ -653,15 +654,15 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     if (tuning.plan_sig) *tuning.plan_sig = sig;
     if (tuning.reuse_plan && (sig != 0ull || tuning.reuse_plan_forced)) {
         // the workspace holds this table's plan: only the per-call merge counters of the segmented form are reset
-        if (big && L.zero_bytes > L.off_chunk_done)
-            KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.zero_bytes - L.off_chunk_done, stream));
+        if (L.chunk_done_bytes) KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.chunk_done_bytes, stream));
     } else if (!big) {
         // no sort, no memset, one launch: every node counts its own sorted positions
         const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
         plan_count_kernel<<<groups * kCountCluster, kCountThreads, 0, stream>>>(t, strat_mask, po);
         KP_LAUNCH_CHECK("plan_count_kernel");
     } else {
-        KP_CUDA(cudaMemsetAsync(w, 0, L.zero_bytes, stream));
+        KP_CUDA(cudaMemsetAsync(hdr, 0, sizeof(SnapHeader), stream));
+        if (L.chunk_done_bytes) KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.chunk_done_bytes, stream));
         const int nb = (int)((n + 255) / 256);
         uint32_t *iota = reinterpret_cast<uint32_t *>(w + L.off_iota);
         unsigned long long *kout = reinterpret_cast<unsigned long long *>(w + L.off_kout);

@@ -17,6 +17,10 @@
 #include <c10/cuda/CUDAStream.h>
 #include <torch/library.h>
 
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
 #include <tuple>
 
 #include "../../include/k8s_place_b200.h"
@@ -25,13 +29,26 @@ namespace {
 
 using at::Tensor;
 
+// error text is formatted here with snprintf and handed to TORCH_CHECK as one string
+[[noreturn]] void fail(const char *fmt, ...)
+{
+    char buf[640];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    TORCH_CHECK(false, std::string(buf));
+    abort();
+}
+
 const void *col(const Tensor &t, const char *name, at::ScalarType dtype, const c10::Device &dev, int64_t n)
 {
-    TORCH_CHECK(t.is_cuda(), name, ": expected a CUDA tensor");
-    TORCH_CHECK(t.device() == dev, name, ": on ", t.device(), ", expected ", dev);
-    TORCH_CHECK(t.scalar_type() == dtype, name, ": dtype ", t.scalar_type(), ", expected ", dtype);
-    TORCH_CHECK(t.dim() == 1 && t.numel() == n, name, ": expected shape (", n, ",)");
-    TORCH_CHECK(t.is_contiguous(), name, ": must be contiguous");
+    if (!t.is_cuda()) fail("%s: expected a CUDA tensor", name);
+    if (t.device() != dev) fail("%s: on %s, expected %s", name, t.device().str().c_str(), dev.str().c_str());
+    if (t.scalar_type() != dtype) fail("%s: dtype %s, expected %s", name, c10::toString(t.scalar_type()), c10::toString(dtype));
+    if (t.dim() != 1 || t.numel() != n) fail("%s: expected shape (%lld,), got %lld element(s) in %d dimension(s)", name, (long long)n,
+                                              (long long)t.numel(), (int)t.dim());
+    if (!t.is_contiguous()) fail("%s: must be contiguous", name);
     return t.data_ptr();
 }
 
@@ -45,7 +62,7 @@ struct Tables {
 kp_node_table node_table(const Tensor &ac, const Tensor &am, const Tensor &pc, const Tensor &mp, const Tensor &ready, const Tensor &cu,
                          const Tensor &mu)
 {
-    TORCH_CHECK(pc.is_cuda(), "pod_count: expected a CUDA tensor");
+    if (!pc.is_cuda()) fail("pod_count: expected a CUDA tensor");
     const c10::Device dev = pc.device();
     const int64_t n = pc.numel();
     kp_node_table t{};
@@ -74,7 +91,7 @@ Tables tables(const Tensor &ac, const Tensor &am, const Tensor &pc, const Tensor
 
 void check(int status, const char *where)
 {
-    TORCH_CHECK(status == KP_OK, where, ": status ", status, " (", kp_status_string(status), ": ", kp_last_error(), ")");
+    if (status != KP_OK) fail("%s: status %d (%s: %s)", where, status, kp_status_string(status), kp_last_error());
 }
 
 void snapshot_place_out(const Tensor &ac, const Tensor &am, const Tensor &pc, const Tensor &mp, const Tensor &ready, const Tensor &cu,
@@ -84,8 +101,8 @@ void snapshot_place_out(const Tensor &ac, const Tensor &am, const Tensor &pc, co
     const Tables t = tables(ac, am, pc, mp, ready, cu, mu, rc, rm, sid);
     col(out_idx, "out_idx", at::kLong, t.dev, t.pods.n_pods);
     col(out_score, "out_score", at::kDouble, t.dev, t.pods.n_pods);
-    TORCH_CHECK(workspace.is_cuda() && workspace.device() == t.dev && workspace.scalar_type() == at::kByte && workspace.is_contiguous(),
-                "workspace: expected a contiguous uint8 tensor on ", t.dev);
+    if (!(workspace.is_cuda() && workspace.device() == t.dev && workspace.scalar_type() == at::kByte && workspace.is_contiguous()))
+        fail("workspace: expected a contiguous uint8 tensor on %s", t.dev.str().c_str());
     const c10::cuda::CUDAGuard guard(t.dev);
     check(kp_snapshot_place(&t.nodes, &t.pods, (int)strategy, (int)filter_mode, out_idx.data_ptr<int64_t>(), out_score.data_ptr<double>(),
                             workspace.data_ptr(), (size_t)workspace.numel(), c10::cuda::getCurrentCUDAStream(t.dev.index()).stream()),
@@ -116,8 +133,8 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> greedy_place(const Tensor &ac
     Tensor out_pc = at::empty({n}, pc.options()), out_cu = at::empty({n}, cu.options()), out_mu = at::empty({n}, mu.options());
     const int64_t need = (int64_t)kp_greedy_workspace_bytes(n, p);
     Tensor ws = workspace.has_value() ? *workspace : at::empty({need < 256 ? 256 : need}, rc.options().dtype(at::kByte));
-    TORCH_CHECK(ws.is_cuda() && ws.device() == t.dev && ws.scalar_type() == at::kByte && ws.is_contiguous() && ws.numel() >= need,
-                "workspace: expected a contiguous uint8 tensor on ", t.dev, " with at least ", need, " bytes");
+    if (!(ws.is_cuda() && ws.device() == t.dev && ws.scalar_type() == at::kByte && ws.is_contiguous() && ws.numel() >= need))
+        fail("workspace: expected a contiguous uint8 tensor on %s with at least %lld bytes", t.dev.str().c_str(), (long long)need);
     const c10::cuda::CUDAGuard guard(t.dev);
     check(kp_greedy_place(&t.nodes, &t.pods, (int)strategy, (int)filter_mode, out_idx.data_ptr<int64_t>(), out_score.data_ptr<double>(),
                           out_pc.data_ptr<int64_t>(), out_cu.data_ptr<double>(), out_mu.data_ptr<double>(), ws.data_ptr(), (size_t)ws.numel(),

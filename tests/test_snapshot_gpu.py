@@ -287,7 +287,7 @@ def test_session_resident_table_reuses_its_node_plan(n):
         first = check(nodes, a, 0)
         again = check(nodes, a, 0)
         assert again < first and again == 1                    # only the placement kernel ran
-        assert check(nodes, b, 0) == (1 if n <= 8192 else first)   # large tables: the layout moves with the pod count
+        assert check(nodes, b, 0) == 1                         # another pod count: the plan's place depends on the nodes alone
         assert check(nodes, b, 1) == first                     # another strategy: its table is not in the plan
         assert check(nodes, b, 1) == 1
         assert check(nodes, a, 1, mode=0) >= 1                 # the reference's own filter has no plan
@@ -300,10 +300,39 @@ def test_session_resident_table_reuses_its_node_plan(n):
         assert check(nodes, a, 1) == first
         s.set_nodes(other)                                     # a new table
         assert check(other, a, 1) == first
-        assert check(other, b, 1) == (1 if n <= 8192 else first)
+        assert check(other, b, 1) == 1
         gi, _ = s.snapshot(nodes, a, 1, 1)                     # table passed with the call: planned afresh
         assert_same_idx(gi, oracle_snapshot(nodes, a, 1, 1)[0])
     assert lib is not None
+
+
+@pytest.mark.parametrize("n,pinned", [(3000, False), (9000, True)])
+def test_session_uploads_many_pods_in_chunks_behind_the_scoring(n, pinned):
+    """More than a million pods with one strategy: the session sends the pod columns in chunks on a second stream
+    and scores each chunk as it lands, all against the plan of the first chunk.  Same answers as one call."""
+    import torch
+    from k8s_llm_scheduler_b200.placement import Session
+    p = 1_150_001
+    nodes, pods = synth.config5(n, p, seed=60 + n)
+    uniform = PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes)
+    want = device_snapshot(nodes, uniform, 0, 1)
+    head = PodTable.from_columns(pods.req_cpu_milli[:40_000], pods.req_mem_bytes[:40_000])
+    oi, os_ = oracle_snapshot(nodes, head, 0, 1)
+    assert_same_idx(want[0][:40_000], oi)
+    with Session(0, max_nodes=n, max_pods=p) as s:
+        if pinned:
+            hp = (torch.as_tensor(pods.req_cpu_milli).pin_memory(), torch.as_tensor(pods.req_mem_bytes).pin_memory(), None)
+            out = (torch.empty(p, dtype=torch.int64).pin_memory(), torch.empty(p, dtype=torch.float64).pin_memory())
+            for _ in range(2):
+                out[0].fill_(-7)
+                s.snapshot(nodes, hp, 0, 1, out=out)
+                assert_same_idx(out[0].numpy(), want[0])
+                assert_same_f64(out[1].numpy(), want[1])
+        else:
+            gi, gs = s.snapshot(nodes, uniform, 0, 1)
+            assert_same_idx(gi, want[0])
+            assert_same_f64(gs, want[1])
+        assert s.last_copy_bytes() == (6 * 8 * n + n + 16 * p, 16 * p)
 
 
 def test_session_inputs_that_need_conversion_stay_alive_for_the_call():
