@@ -115,7 +115,7 @@ struct kp_session {
 namespace {
 
 constexpr int kPipeMaxChunks = 2;
-constexpr int64_t kPipeChunkMinPods = 1 << 19;   // below two pieces of this size one copy + one launch is as good
+constexpr int64_t kPipeChunkMinPodsDefault = 1 << 19;   // below two pieces of this size one copy + one launch is as good
 constexpr unsigned kFlowWindowCtas = 64;      // request rows of this many CTAs in flight on the host link
 constexpr size_t kStageMaxBytes = 1u << 20;   // node tables up to ~18 k rows travel as one copy
 
@@ -549,6 +549,8 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     // scoring starts early, and the rest, which travels while the first is scored (against the same node plan).
     // Scoring a pod costs about n_nodes / 3500 times what copying it costs, which sizes the first piece; more,
     // equal pieces would only multiply the placement kernel's start-up and tail.
+    int64_t kPipeChunkMinPods = kPipeChunkMinPodsDefault;
+    if (const char *v = getenv("KP_PIPE_MIN")) kPipeChunkMinPods = std::max<int64_t>(1024, atoll(v));   // experiments only
     const int64_t P = pods->n_pods;
     const bool pipelined = !in_place && pods->strategy_ids == nullptr && filter_mode == KP_FILTER_CAPACITY && P <= s->max_pods &&
                            P >= 2 * kPipeChunkMinPods;
