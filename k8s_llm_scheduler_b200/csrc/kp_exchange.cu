@@ -360,6 +360,20 @@ int kp_exchange_connect_local(kp_exchange *ex, kp_exchange *const *all)
         }
         ex->peer[r] = all[r]->base;
     }
+    // exchanges on other devices of this process: plain peer access instead of IPC
+    int prev = -1;
+    cudaGetDevice(&prev);
+    KP_CUDA(cudaSetDevice(ex->device));
+    for (int r = 0; r < ex->world; ++r) {
+        if (all[r]->device == ex->device) continue;
+        const cudaError_t e = cudaDeviceEnablePeerAccess(all[r]->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+            if (prev >= 0) cudaSetDevice(prev);
+            return cuda_fail(e, "cudaDeviceEnablePeerAccess (peer access between the GPUs is required)");
+        }
+        cudaGetLastError();
+    }
+    if (prev >= 0) cudaSetDevice(prev);
     ex->connected = true;
     return KP_OK;
 }

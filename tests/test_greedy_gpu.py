@@ -284,3 +284,27 @@ def test_tables_beyond_the_fast_path_capacity_use_the_fp64_kernel():
     nodes, pods = synth.config5(90_000, 2100, seed=39)
     _check_greedy(nodes, pods, 0, 1, per_pod=True, what="90k per-pod")
     _check_greedy(nodes, pods, 1, 1, what="90k uniform (cluster of 8)")
+
+
+def test_greedy_on_a_second_device_of_the_same_process(monkeypatch):
+    """Opt-in shared-memory sizes are a per-device attribute: the second GPU a process uses must get them too
+    (fp64 kernel with more than 48 KB of cold state, fast path with its trajectory tables)."""
+    import torch
+    from k8s_llm_scheduler_b200 import placement
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    nodes, pods = synth.config5(4000, 5000, seed=41)
+    want = oracle_greedy(nodes, pods, 0, 1)
+    want_pp = oracle_greedy(nodes, pods, 0, 1, per_pod=True)
+    for no_fast in ("0", "1"):
+        monkeypatch.setenv("KP_GREEDY_NO_FAST", no_fast)
+        for dev in ("cuda:0", "cuda:1"):
+            dn = placement.nodes_to_device(nodes, dev)
+            rc, rm = torch.as_tensor(pods.req_cpu_milli).to(dev), torch.as_tensor(pods.req_mem_bytes).to(dev)
+            with torch.cuda.device(dev):
+                g = placement.greedy_place(dn, rc, rm, 0, 1)
+                gp = placement.greedy_place(dn, rc, rm, torch.as_tensor(pods.strategy_ids).to(dev), 1)
+                torch.cuda.synchronize()
+            assert_same_idx(g[0].cpu().numpy(), want[0], f"{dev} no_fast={no_fast}")
+            assert np.array_equal(g[2].cpu().numpy(), want[2])
+            assert_same_idx(gp[0].cpu().numpy(), want_pp[0], f"{dev} no_fast={no_fast} per-pod")

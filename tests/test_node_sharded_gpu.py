@@ -79,3 +79,45 @@ def test_uneven_and_empty_slices():
     few = PodTable.from_columns(pods.req_cpu_milli[:3], pods.req_mem_bytes[:3])
     gi, _ = run_emulated(nodes, few, 5, 1, False)
     assert_same_idx(gi, oracle_snapshot(nodes, few, 1, 1)[0])
+
+
+def test_two_real_gpus_in_one_process():
+    """The same exchange with each rank on its own device (peer access inside one process): kernels of different
+    ranks now really run at the same time and wait for each other's flags."""
+    import torch
+    from k8s_llm_scheduler_b200 import dist as kd, placement
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    nodes, pods = synth.config5(6000, 80_000, seed=88)
+    n, p = len(nodes), len(pods)
+    devs = [torch.device("cuda:0"), torch.device("cuda:1")]
+    cuts = [kd.shard_bounds(n, r, 2) for r in range(2)]
+    group = kd.NodeShardedPlacer.local_group(devs, max_pods=p, max_local_nodes=max(b - a for a, b in cuts))
+    # every buffer exists before the first kernel that waits for a peer is launched (an allocation may have to
+    # wait for running kernels)
+    args, outs = [], []
+    for g, dev, (a, b) in zip(group, devs, cuts):
+        full = placement.nodes_to_device(nodes, dev)
+        args.append((kd.slice_nodes(full, a, b), a, torch.as_tensor(pods.req_cpu_milli).to(dev),
+                     torch.as_tensor(pods.req_mem_bytes).to(dev), torch.as_tensor(pods.strategy_ids).to(dev)))
+        lo, hi = kd.shard_bounds(p, g.rank, 2)
+        outs.append((torch.empty(hi - lo, dtype=torch.int64, device=dev), torch.empty(hi - lo, dtype=torch.float64, device=dev)))
+        with torch.cuda.device(dev):
+            g._structs(args[-1][0], args[-1][2], args[-1][3], args[-1][4])        # workspace allocated up front
+    for dev in devs:
+        torch.cuda.synchronize(dev)
+    parts = []
+    for rounds in range(3):
+        parts = []
+        for g, dev, arg, out in zip(group, devs, args, outs):
+            with torch.cuda.device(dev):
+                parts.append(g.place(*arg, 1, out=out))
+        for dev in devs:
+            torch.cuda.synchronize(dev)
+    for g in group:
+        g.check()
+    idx = np.concatenate([q[2].cpu().numpy() for q in parts])
+    score = np.concatenate([q[3].cpu().numpy() for q in parts])
+    oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
+    assert_same_idx(idx, oi)
+    assert_same_f64(score, os_)
