@@ -425,7 +425,7 @@ def run_ours(args):
     # timed region (device time, per-step CUDA events on the launching stream); no
     # instrumentation inside the steps, so the kernels chain with dependent launches
     steps = args.steps if snapshot else max(1, min(args.steps, 3))
-    warmup = args.warmup if snapshot else 1
+    warmup = args.warmup if snapshot else min(args.warmup, 3)
     for _ in range(warmup):
         step()
     torch.cuda.synchronize()
@@ -550,6 +550,7 @@ def run_ours(args):
                 "rank0_ms_min_median": [min(e2e_each) * 1e3, statistics.median(e2e_each) * 1e3],
                 "host_numa": NUMA_NOTE.get("note")},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+        "step_ms_rank0": [round(x, 4) for x in step_ms],
         "cpu_baseline": cpu_baseline, "parity_vs_cpu_sample": parity,
         "parity_detail": {"c_oracle_pods_checked": k_chk, "device_pass": ok_dev, "host_api_pass": ok_e2e,
                           "python_port_sample": None if cpu_baseline is None else "first pods of the cpu_baseline sample"},
@@ -809,7 +810,7 @@ def run_extras(args, torch, placement, lib, dev, peak_meas):
     hbm_peak, sm_max_mhz, peak_src = measured_peaks()
     sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    for name, steps in (("c2", 20), ("c4shard", 3), ("c5", 3), ("c3", 1), ("c5greedy", 1)):
+    for name, steps in (("c2", 20), ("c4shard", 3), ("c5", 3), ("c3", 3), ("c5greedy", 1)):
         if name == args.workload:
             continue
         try:
@@ -827,7 +828,7 @@ def run_extras(args, torch, placement, lib, dev, peak_meas):
             else:
                 ws = torch.empty(placement.greedy_workspace_bytes(n, p), dtype=torch.uint8, device=dev)
                 fn = lambda: res.__setitem__("out", placement.greedy_place(dn, rc, rm, strat, meta["filter"], workspace=ws))  # noqa: E731
-            for _ in range(3 if snapshot else 1):
+            for _ in range(3):
                 fn()
             torch.cuda.synchronize()
             ms, place, plan = [], [], []

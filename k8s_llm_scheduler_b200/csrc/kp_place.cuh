@@ -33,7 +33,7 @@ namespace kp {
 #endif
 #ifndef KP_UPDATE_MODE
 #define KP_UPDATE_MODE 1      // candidate update: 0 = SEL (ALU pipe), 1 = alternate per pod, 2 = guarded IMAD (FMA pipe)
-#endif
+#endif                        // 3 = IMAD that reads the candidate (best * 0 + pos: one vector source), 4 = alternate SEL / that IMAD
 constexpr int kTileBytes = KP_TILE_BYTES;              // per shared-memory tile buffer
 constexpr int kTileNodesPacked = kTileBytes / 4;       // 1024
 constexpr int kTileNodesWide = kTileBytes / 8;         // 512
@@ -120,13 +120,29 @@ __device__ __forceinline__ void swar_update_alu(int &best, uint32_t x, uint32_t 
         "  @!p mov.s32 %0, %3; }"
         : "+r"(best) : "r"(w), "r"(x), "r"(pos));
 }
-__device__ __forceinline__ constexpr bool update_on_fma(int r)
+// packed test + update on the FMA pipe, second form: best = best * zero + pos (zero and pos are warp-uniform,
+// so the instruction has one vector-register source; nothing to decode afterwards)
+__device__ __forceinline__ void swar_update_self(int &best, uint32_t x, uint32_t w, int pos, int zero)
+{
+    asm volatile(
+        "{ .reg .pred p; .reg .b32 t, d;\n"
+        "  sub.u32 t, %1, %2;\n"
+        "  lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0;\n"
+        "  @!p mad.lo.s32 %0, %0, %4, %3; }"
+        : "+r"(best) : "r"(w), "r"(x), "r"(pos), "r"(zero));
+}
+__device__ __forceinline__ constexpr bool update_on_fma(int r)             // the x-encoded form (decoded after the scan)
 {
     return KP_UPDATE_MODE == 2 || (KP_UPDATE_MODE == 1 && (r & 1));
+}
+__device__ __forceinline__ constexpr bool update_self(int r)
+{
+    return KP_UPDATE_MODE == 3 || (KP_UPDATE_MODE == 4 && (r & 1));
 }
 __device__ __forceinline__ void swar_step(int &best, uint32_t x, uint32_t w, int pos, int one, int r)
 {
     if (update_on_fma(r)) swar_update(best, x, w, pos, one);
+    else if (update_self(r)) swar_update_self(best, x, w, pos, one - 1);
     else swar_update_alu(best, x, w, pos);
 }
 

@@ -23,6 +23,13 @@ __device__ __forceinline__ void upd_f(int &best_enc, uint32_t x, uint32_t w, int
     asm volatile("{ .reg .pred p; .reg .b32 t, d; sub.u32 t, %1, %2; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0; @!p mad.lo.s32 %0, %3, %4, %2; }"
                  : "+r"(best_enc) : "r"(w), "r"(x), "r"(pos), "r"(one));
 }
+// G: like F, but the update reads `best` (best = best * zero + pos): pos and zero are warp-uniform, so the
+// instruction has ONE vector-register source
+__device__ __forceinline__ void upd_g(int &best, uint32_t x, uint32_t w, int pos, int zero)
+{
+    asm volatile("{ .reg .pred p; .reg .b32 t, d; sub.u32 t, %1, %2; lop3.b32.or d|p, t, 0x80008000, 0, 0x0c, 0; @!p mad.lo.s32 %0, %0, %4, %3; }"
+                 : "+r"(best) : "r"(w), "r"(x), "r"(pos), "r"(zero));
+}
 __device__ __forceinline__ void upd_h(int &best, uint32_t x, uint32_t w, int pos)
 {
     asm volatile("{ .reg .pred p, q; setp.ge.f16x2 p|q, %1, %2; @p selp.s32 %0, %3, %0, q; }"
@@ -46,7 +53,7 @@ __global__ void __launch_bounds__(THREADS) bench_kernel(int iters, int *__restri
     for (int i = threadIdx.x; i < TILE; i += THREADS) {
         const uint32_t v = (uint32_t)i * 2246822519u;
         const uint32_t ra = (v >> 5) % 2000u, rb = (v >> 18) % 2000u;
-        if (V == 'F') s_pk[i] = ((rb | 0x8000u) << 16) | (ra | 0x8000u);
+        if (V == 'F' || V == 'G') s_pk[i] = ((rb | 0x8000u) << 16) | (ra | 0x8000u);
         else {
             const __half2 h = __halves2half2(__ushort2half_rn((unsigned short)ra), __ushort2half_rn((unsigned short)rb));
             s_pk[i] = *reinterpret_cast<const uint32_t *>(&h);
@@ -60,7 +67,7 @@ __global__ void __launch_bounds__(THREADS) bench_kernel(int iters, int *__restri
     for (int r = 0; r < R; ++r) {
         const uint32_t h = (uint32_t)(gtid * R + r) * 2654435761u;
         const uint32_t ra = (h >> 3) % 2000u, rb = (h >> 17) % 2000u;
-        if (V == 'F') x[r] = (rb << 16) | ra;
+        if (V == 'F' || V == 'G') x[r] = (rb << 16) | ra;
         else {
             const __half2 hh = __halves2half2(__ushort2half_rn((unsigned short)ra), __ushort2half_rn((unsigned short)rb));
             x[r] = *reinterpret_cast<const uint32_t *>(&hh);
@@ -78,6 +85,7 @@ __global__ void __launch_bounds__(THREADS) bench_kernel(int iters, int *__restri
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     if (V == 'F') upd_f(best[r], x[r], w[k], 4 * i + k, one);
+                    if (V == 'G') upd_g(best[r], x[r], w[k], 4 * i + k, zero);
                     if (V == 'H') upd_h(best[r], x[r], w[k], 4 * i + k);
                     if (V == 'I') upd_i(best[r], x[r], w[k], 4 * i + k, zero);
                     if (V == 'J') upd_j(best[r], x[r], w[k], 4 * i + k, zero);
@@ -132,10 +140,14 @@ int main()
     const int iters = 24;
     for (int occ : {2, 4}) {
         run<'F', 8>("F  SWAR IMAD.IADD + LOP3.P + @P IMAD (3/pair)", sms, occ, iters);
+        run<'G', 8>("G  SWAR, update best = best*zero + pos (1 vector source)", sms, occ, iters);
         run<'H', 8>("H  HSETP2 P,Q + @P SEL ..,Q (2/pair)", sms, occ, iters);
         run<'I', 8>("I  HSETP2 + PLOP3 + @P IMAD (3/pair)", sms, occ, iters);
         run<'J', 8>("J  HSET2 mask + ISETP + @P IMAD (3/pair)", sms, occ, iters);
     }
+    run<'G', 16>("G  SWAR, update best = best*zero + pos", sms, 2, iters);
+    run<'G', 16>("G  SWAR, update best = best*zero + pos", sms, 3, iters);
+    run<'F', 16>("F  SWAR IMAD.IADD + LOP3.P + @P IMAD", sms, 3, iters);
     run<'H', 4>("H  HSETP2 P,Q + @P SEL ..,Q (2/pair)", sms, 4, iters);
     run<'H', 16>("H  HSETP2 P,Q + @P SEL ..,Q (2/pair)", sms, 2, iters);
     return 0;
