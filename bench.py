@@ -116,13 +116,28 @@ def eligible_nodes(nodes, meta) -> int:
     return int(ok.sum())
 
 
+def pods_scanned(nodes, pods, meta) -> int:
+    """Pods the placement kernel actually scans the table for.  With per-pod strategies the grouping pass answers
+    pods that exceed the largest free-cpu / free-memory threshold of the table ("no node") without a scan; `value`
+    still counts every pod x eligible node (the work the reference loop does), and the line carries the evaluated
+    rate beside it (evaluated and effective pairs are reported apart)."""
+    if not meta["per_pod"] or meta["mode"] != "snapshot" or meta["filter"] != 1:
+        return len(pods)
+    with np.errstate(invalid="ignore"):
+        fc = (nodes.alloc_cpu_milli / 1000.0) * (100.0 - nodes.cpu_usage_pct) / 100.0
+        fm = (nodes.alloc_mem_bytes / 1024.0 / 1024.0 / 1024.0) * (100.0 - nodes.mem_usage_pct) / 100.0
+    fc, fm = np.where(np.isnan(fc), np.inf, fc), np.where(np.isnan(fm), np.inf, fm)
+    dead = (pods.req_cpu_milli / 1000.0 > fc.max()) | (pods.req_mem_bytes / 1024.0 / 1024.0 / 1024.0 > fm.max())
+    return int(len(pods) - dead.sum())
+
+
 def config_block(meta, nodes, pods, world: int, extra=None):
     """`config` of the JSON line; identical in both arms apart from the run-specific tail."""
     cfg = {"workload": meta["desc"], "baseline_config": meta["config"], "nodes": len(nodes), "pods": len(pods),
            "nodes_eligible": eligible_nodes(nodes, meta),
            "strategy": "per-pod mix" if meta["per_pod"] else STRATEGY_NAMES[meta["strategy"]],
            "filter": "capacity" if meta["filter"] == 1 else "ready", "mode": meta["mode"],
-           "pairs_counted": "pods x eligible nodes"}
+           "pairs_counted": "pods x eligible nodes", "pods_scanned": pods_scanned(nodes, pods, meta)}
     cfg.update(extra or {})
     return cfg
 
@@ -513,8 +528,8 @@ def run_ours(args):
     clk = (clocks or {}).get("sm_mhz") or sm_max_mhz
     roofline = None
     if place_ms:
-        roofline = place_roofline(p, n_el, n, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src, clk, peak_meas,
-                                  hbm_peak, load_traffic(args.workload if world == 1 else f"{args.workload}/{world}"),
+        roofline = place_roofline(pods_scanned(nodes, pods, meta), n_el, n, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src,
+                                  clk, peak_meas, hbm_peak, load_traffic(args.workload if world == 1 else f"{args.workload}/{world}"),
                                   meta["per_pod"])
 
     # parity: every line carries a C-oracle check of this rank's first decisions (device pass AND host-API pass);
@@ -540,6 +555,7 @@ def run_ours(args):
         "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling_of(meta),
         "vs_baseline": None, "dtype": "f64 scores, i32 rank compares", "data": "synthetic",
         "pods_per_sec": pods_per_step / (ms_per_step * 1e-3),
+        "pairs_per_sec_evaluated": value * pods_scanned(nodes, all_pods, meta) / max(1, len(all_pods)),
         "config": config_block(meta, nodes, all_pods, world),
         "run": {"pods_per_gpu": p, "sharding": sharding,
                 "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB write)"},
@@ -770,14 +786,17 @@ def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, 
     n_el_local = int(((nodes.ready[lo:hi] != 0) & (nodes.pod_count[lo:hi] < nodes.max_pods[lo:hi])).sum())
     roofline = None
     if place_ms:
-        roofline = place_roofline(p, n_el_local, hi - lo, place_ms, plan_ms, step_ms, sm_count, sm_max_mhz, peak_src, clk,
-                                  peak_meas, hbm_peak, None, per_pod)
+        from k8s_llm_scheduler_b200.tables import NODE_COLUMNS as _NC, NodeTable as _NT
+        slice_table = _NT.from_columns(**{k: getattr(nodes, k)[lo:hi] for k in _NC})      # this rank rejects against ITS largest thresholds
+        roofline = place_roofline(pods_scanned(slice_table, pods, meta), n_el_local, hi - lo, place_ms, plan_ms, step_ms, sm_count,
+                                  sm_max_mhz, peak_src, clk, peak_meas, hbm_peak, None, per_pod)
         roofline["note"] = "this rank's placement kernel: all pods x the eligible nodes of its slice"
     ph = np.array(phases).mean(axis=0)
     out_line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64 scores, i32 rank compares", "data": "synthetic", "pods_per_sec": p / (ms_per_step * 1e-3),
+        "pairs_per_sec_evaluated": value * pods_scanned(nodes, pods, meta) / max(1, p),
         "config": config_block(meta, nodes, pods, world),
         "run": {"nodes_per_gpu": hi - lo, "sharding": f"node list cut into {world} contiguous slices; every rank scores all {p} pods; "
                 "per-pod arg-max reduced across ranks by the library's kernels over peer memory (CUDA IPC / NVLink): "
@@ -850,11 +869,12 @@ def run_extras(args, torch, placement, lib, dev, peak_meas):
                 lib.kp_profile_enable(0)
             t = statistics.mean(ms) * 1e-3
             ok, k = c_oracle_check(nodes, pods, meta, res["out"][0][:4096].cpu().numpy())
-            e = {"workload": meta["desc"], "baseline_config": meta["config"], "nodes_eligible": n_el,
-                 "ms_per_step": t * 1e3, "pairs_per_sec": p * n_el / t, "pods_per_sec": p / t,
+            scanned = pods_scanned(nodes, pods, meta)
+            e = {"workload": meta["desc"], "baseline_config": meta["config"], "nodes_eligible": n_el, "pods_scanned": scanned,
+                 "ms_per_step": t * 1e3, "pairs_per_sec": p * n_el / t, "pairs_per_sec_evaluated": scanned * n_el / t, "pods_per_sec": p / t,
                  "parity_vs_cpu_sample": ok, "c_oracle_pods_checked": k}
             if place:
-                e["roofline"] = place_roofline(p, n_el, n, place, plan, ms, sm_count, sm_max_mhz, peak_src, sm_max_mhz,
+                e["roofline"] = place_roofline(scanned, n_el, n, place, plan, ms, sm_count, sm_max_mhz, peak_src, sm_max_mhz,
                                                peak_meas, hbm_peak, load_traffic(name), meta["per_pod"])
             if not snapshot:
                 e["greedy"] = greedy_report(torch, placement, dn, rc, rm, strat, meta, res["out"], ws)

@@ -145,19 +145,51 @@ static NodePtrs node_ptrs(const kp_node_table &t)
 constexpr int kGroupPerThread = 8;
 constexpr int kGroupItems = 256 * kGroupPerThread;
 
+// Pods that exceed the LARGEST free-cpu or free-memory threshold of the table fit no node whatever the strategy
+// (their threshold rank is past every node's): they are answered here ("no node") and never enter a strategy
+// group, so the placement kernel does not scan the table for them.  Exact: the test is the kernel's own
+// request > threshold compare against the last entry of the sorted threshold arrays (which hold every node's
+// thresholds, NaN parked at +inf -- a table with such a node simply rejects nobody early).
+struct GroupPods {
+    const long long *sid, *req_cpu, *req_mem;
+    long long n_pods;
+    const double *uniq;            // [2][npad] sorted thresholds
+    int npad, small_n;             // small_n > 0: arrays keep duplicates and hold small_n entries; else hdr->distinct
+    long long *out_idx;
+    double *out_score;
+    uint32_t *out_gpos;            // node-sharded form (may be NULL)
+};
+constexpr int kGroupDead = kMaxStrategies;
+
+__device__ __forceinline__ void group_limits(const GroupPods &g, const SnapHeader *hdr, double &ta_max, double &tb_max)
+{
+    const int da = g.small_n > 0 ? g.small_n : (int)hdr->distinct[0], db = g.small_n > 0 ? g.small_n : (int)hdr->distinct[1];
+    const double ninf = __longlong_as_double((long long)0xfff0000000000000ull);
+    ta_max = da > 0 ? g.uniq[da - 1] : ninf;
+    tb_max = db > 0 ? g.uniq[(size_t)g.npad + db - 1] : ninf;
+}
+__device__ __forceinline__ int group_of(const GroupPods &g, long long j, double ta_max, double tb_max)
+{
+    if (req_cores(g.req_cpu[j]) > ta_max || req_gib(g.req_mem[j]) > tb_max) return kGroupDead;
+    return canon_strategy(g.sid[j]);
+}
+
 __global__ void __launch_bounds__(256)
-group_count_kernel(const long long *__restrict__ sid, long long n_pods, SnapHeader *hdr)
+group_count_kernel(GroupPods gp, SnapHeader *hdr)
 {
     __shared__ unsigned s_cnt[kMaxStrategies];
     if (threadIdx.x < kMaxStrategies) s_cnt[threadIdx.x] = 0u;
     __syncthreads();
+    const long long n_pods = gp.n_pods;
+    double ta_max, tb_max;
+    group_limits(gp, hdr, ta_max, tb_max);
     const long long base = (long long)blockIdx.x * kGroupItems;
     unsigned c[kMaxStrategies] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
         if (j < n_pods) {
-            const int g = canon_strategy(sid[j]);
+            const int g = group_of(gp, j, ta_max, tb_max);
 #pragma unroll
             for (int s = 0; s < kMaxStrategies; ++s) c[s] += g == s;
         }
@@ -171,9 +203,11 @@ group_count_kernel(const long long *__restrict__ sid, long long n_pods, SnapHead
     if (threadIdx.x < kMaxStrategies && s_cnt[threadIdx.x]) atomicAdd(&hdr->group_count[threadIdx.x], s_cnt[threadIdx.x]);
 }
 __global__ void __launch_bounds__(256)
-group_assign_kernel(const long long *__restrict__ sid, long long n_pods, int chunk_pods,
-                    SnapHeader *hdr, uint32_t *__restrict__ perm)
+group_assign_kernel(GroupPods gp, int chunk_pods, SnapHeader *hdr, uint32_t *__restrict__ perm)
 {
+    const long long n_pods = gp.n_pods;
+    double ta_max, tb_max;
+    group_limits(gp, hdr, ta_max, tb_max);
     __shared__ unsigned s_cnt[kMaxStrategies], s_cur[kMaxStrategies];
     __shared__ long long s_base[kMaxStrategies];
     if (threadIdx.x < kMaxStrategies) { s_cnt[threadIdx.x] = 0u; s_cur[threadIdx.x] = 0u; }
@@ -185,7 +219,12 @@ group_assign_kernel(const long long *__restrict__ sid, long long n_pods, int chu
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
-        g[i] = j < n_pods ? canon_strategy(sid[j]) : -1;
+        g[i] = j < n_pods ? group_of(gp, j, ta_max, tb_max) : -1;
+        if (g[i] == kGroupDead) {                                 // fits nothing: answered here, never scanned
+            gp.out_idx[j] = -1;
+            gp.out_score[j] = -1.0;
+            if (gp.out_gpos) gp.out_gpos[j] = 0xffffffffu;
+        }
 #pragma unroll
         for (int s = 0; s < kMaxStrategies; ++s) c[s] += g[i] == s;
     }
@@ -714,9 +753,11 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     // ---- pods ----
     if (per_pod) {
         const int gb = (int)((P + kGroupItems - 1) / kGroupItems);
-        group_count_kernel<<<gb, 256, 0, stream>>>((const long long *)pods.strategy_ids, P, hdr);
+        GroupPods gp{(const long long *)pods.strategy_ids, (const long long *)pods.req_cpu_milli, (const long long *)pods.req_mem_bytes, P,
+                     po.uniq, (int)L.npad, big ? 0 : (int)n, (long long *)out_idx, out_score, tuning.out_gpos};
+        group_count_kernel<<<gb, 256, 0, stream>>>(gp, hdr);
         KP_LAUNCH_CHECK("group_count_kernel");
-        group_assign_kernel<<<gb, 256, 0, stream>>>((const long long *)pods.strategy_ids, P, chunk_pods, hdr, perm);
+        group_assign_kernel<<<gb, 256, 0, stream>>>(gp, chunk_pods, hdr, perm);
         KP_LAUNCH_CHECK("group_assign_kernel");
     }
     if (nseg > 1) KP_CUDA(cudaMemsetAsync(best_pos, 0xff, sizeof(uint32_t) * n_chunks * chunk_pods, stream));
