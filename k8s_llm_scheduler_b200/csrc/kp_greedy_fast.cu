@@ -59,6 +59,7 @@ struct FastHeader {
     uint32_t traj_total;
     uint32_t distinct[2];
     uint32_t score_ranks[kMaxStrategies];
+    uint32_t wmax_lo, wmax_hi;  // largest threshold rank field (rank + 1) of any state that exists: a pod beyond it fits nothing, ever
     uint32_t traj_base[kFastMaxShapes + 1];
     long long shape_cpu[kFastMaxShapes], shape_mem[kFastMaxShapes], shape_mp[kFastMaxShapes];
 };
@@ -133,6 +134,8 @@ fast_shapes_kernel(FastIn in, FastHeader *hdr, uint32_t *__restrict__ shape_id)
         hdr->traj_base[cnt] = total;
         hdr->n_shapes = (uint32_t)cnt;
         hdr->traj_total = total;
+        hdr->wmax_lo = 0u;
+        hdr->wmax_hi = 0u;
         hdr->ok = (!s_overflow && !any_bad && total <= (uint32_t)kFastMaxTraj) ? 1u : 0u;
     }
 }
@@ -239,6 +242,15 @@ fast_pack_kernel(FastIn in, FastHeader *hdr, const uint32_t *__restrict__ rank_t
         for (int s = 0; s < kMaxStrategies; ++s)
             if ((in.strat_mask & (1 << s)) && (hdr->score_ranks[s] + 1u) >= (1u << (32 - idx_bits))) ok = false;
         hdr->ok = ok ? 1u : 0u;
+    }
+    // field-wise maximum over the states that exist (node rows and trajectory states; the unused tail of the
+    // trajectory table carries +inf thresholds and must not count)
+    const bool exists = i < total && (i < in.n || (uint32_t)(i - in.n) < hdr->traj_total);
+    const uint32_t mlo = __reduce_max_sync(0xffffffffu, exists ? rank_t0[i] + 1u : 0u);
+    const uint32_t mhi = __reduce_max_sync(0xffffffffu, exists ? rank_t1[i] + 1u : 0u);
+    if ((threadIdx.x & 31) == 0) {
+        if (mlo) atomicMax(&hdr->wmax_lo, mlo);
+        if (mhi) atomicMax(&hdr->wmax_hi, mhi);
     }
     if (i >= total) return;
     entry_w[i] = (((rank_t1[i] + 1u) | 0x8000u) << 16) | ((rank_t0[i] + 1u) | 0x8000u);
@@ -536,6 +548,7 @@ fast_greedy_kernel(FastIn in, FastRun r)
     const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
     const int cta_base = crank * r.nodes_per_cta;
     const long long n_done = (long long)batch_n_done(r.hdr, r.batch);   // pods the sorted prefix has already decided
+    const uint32_t wmax_lo = r.hdr->wmax_lo, wmax_hi = r.hdr->wmax_hi;
 
     if (tid <= kFastMaxShapes) s_tbase[tid] = r.hdr->traj_base[tid];
     for (int i = tid; i < kFastMaxTraj; i += kFastThreads) {
@@ -592,6 +605,14 @@ fast_greedy_kernel(FastIn in, FastRun r)
         uint32_t x = s_x[0];
         int s = s_sid[0];
         for (int j = 0; j < cnt; ++j) {
+            if ((x & 0xffffu) > wmax_lo || (x >> 16) > wmax_hi) {
+                // larger than every state that exists: no scan, no reduction, no exchange (every CTA of a cluster
+                // takes this branch for the same pods)
+                if (crank == 0 && tid == 0) { r.out_idx[base + j] = -1; r.out_entry[base + j] = kNoEntry; }
+                x = s_x[j + 1];
+                s = s_sid[j + 1];
+                continue;
+            }
             uint32_t best;
             if (!MULTI) {
                 const bool all_fit = ((~(wmin - x)) & kFastGuards) == 0u;
