@@ -66,7 +66,11 @@ def test_reference_decisions_ready_filter(golden_dir):
 
 @pytest.mark.parametrize("n,p", [(1, 1), (3, 5), (7, 257), (100, 3000), (1000, 2049), (4096, 700),
                                  (4097, 1500), (5000, 300), (9001, 4099), (8192, 600), (8193, 600),
-                                 (20000, 1000)])
+                                 (20000, 1000),
+                                 # register-slice boundaries of place_small_kernel (56 words x 32 lanes per slice, word
+                                 # counts in steps of 8) with pod counts off every group / pass size
+                                 (255, 31), (256, 33), (257, 1001), (1792, 1001), (1793, 33), (2048, 4100), (3585, 31),
+                                 (7169, 129), (8191, 3)])
 def test_random_clusters_capacity_filter(n, p):
     nodes, pods = synth.config5(n, p, seed=1000 + n)
     for sid in (0, 1, 2):
