@@ -127,6 +127,16 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
                       int filter_mode, int64_t *out_node_idx, double *out_score,
                       void *workspace, size_t workspace_bytes, void *stream);
 
+/* Same decisions for MORE pods against the SAME node table: the workspace still holds the node plan that an
+ * earlier kp_snapshot_place call (same node table contents, same strategy, capacity filter, no per-pod strategy
+ * ids) left there, and only the placement kernel runs -- the reference's per-pod loop re-reads one cluster table
+ * for every pod (scheduler.py:690-729), so does a caller that scores pod batches as they arrive.  The caller
+ * vouches for "same table, same workspace"; nothing can check it.  KP_ERR_INVALID_ARG for the Ready-only filter
+ * or per-pod strategy ids (their plans are not reusable). */
+int kp_snapshot_place_again(const kp_node_table *nodes, const kp_pod_table *pods, int strategy, int filter_mode,
+                            int64_t *out_node_idx, double *out_score, void *workspace, size_t workspace_bytes,
+                            void *stream);
+
 /* ---- snapshot placement without a workspace, device pointers -------------------------
  * No counterpart in the reference: this entry point exists for hosts that cannot give
  * kp_snapshot_place a workspace because they cannot allocate device memory at the time

@@ -59,6 +59,8 @@ SYMBOLS = {
     "kp_snapshot_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "kp_snapshot_place": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "kp_snapshot_place_again": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
+                                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "kp_snapshot_place_noalloc": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
                                           c_void_p, c_void_p, c_void_p]),
     "kp_exchange_create": (c_int, [c_int, c_int, c_int, c_int64, c_int64, POINTER(c_void_p)]),

@@ -333,6 +333,26 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
                                  workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+int kp_snapshot_place_again(const kp_node_table *nodes, const kp_pod_table *pods, int strategy, int filter_mode,
+                            int64_t *out_node_idx, double *out_score, void *workspace, size_t workspace_bytes, void *stream)
+{
+    int st = check_tables(nodes, pods);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) {
+        set_error("output pointer is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    if (snapshot_plan_signature(nodes->n_nodes, pods->n_pods, pods->strategy_ids != nullptr, strategy, filter_mode) == 0ull) {
+        set_error("kp_snapshot_place_again: only the capacity filter with one strategy keeps a reusable node plan");
+        return KP_ERR_INVALID_ARG;
+    }
+    PlaceTuning tuning;
+    tuning.reuse_plan = true;
+    return snapshot_place_device(*nodes, *pods, strategy, filter_mode, out_node_idx, out_score, workspace, workspace_bytes,
+                                 (cudaStream_t)stream, tuning);
+}
+
 int kp_snapshot_place_noalloc(const kp_node_table *nodes, const kp_pod_table *pods, int strategy,
                               int filter_mode, int64_t *out_node_idx, double *out_score, void *stream)
 {

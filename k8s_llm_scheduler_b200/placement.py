@@ -131,6 +131,23 @@ def snapshot_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
     return out[0], out[1]
 
 
+def snapshot_place_again(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor, req_mem_bytes: torch.Tensor,
+                         strategy: int, workspace: torch.Tensor, out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+    """More pods against the SAME node table: ``workspace`` still holds the node plan of an earlier
+    ``snapshot_place(nodes, ..., strategy, FILTER_CAPACITY, workspace=workspace)`` call, so only the placement kernel
+    runs (kp_snapshot_place_again; the caller vouches for "same table, same workspace")."""
+    lib = _lib.load()
+    nst, device, n = _node_struct(nodes)
+    pst, p, strat, per_pod = _pod_struct(req_cpu_milli, req_mem_bytes, int(strategy), device)
+    if out is None:
+        out = (torch.empty(p, dtype=torch.int64, device=device), torch.empty(p, dtype=torch.float64, device=device))
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        check(lib.kp_snapshot_place_again(byref(nst), byref(pst), strat, FILTER_CAPACITY, out[0].data_ptr(), out[1].data_ptr(),
+                                          workspace.data_ptr(), workspace.numel(), c_void_p(stream)), "kp_snapshot_place_again")
+    return out[0], out[1]
+
+
 def greedy_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
                  req_mem_bytes: torch.Tensor, strategy: Union[int, torch.Tensor] = 0,
                  filter_mode: int = FILTER_CAPACITY, workspace: Optional[torch.Tensor] = None):

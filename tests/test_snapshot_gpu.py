@@ -339,6 +339,32 @@ def test_session_uploads_many_pods_in_chunks_behind_the_scoring(n, pinned):
         assert s.last_copy_bytes() == (6 * 8 * n + n + 16 * p, 16 * p)
 
 
+@pytest.mark.parametrize("n", [700, 5000, 11_000])
+def test_place_again_reuses_the_plan_in_the_workspace(n):
+    """kp_snapshot_place_again: other pods against the same node table, only the placement kernel runs."""
+    import torch
+    from k8s_llm_scheduler_b200 import placement, PlacementError
+    nodes, pods = synth.config5(n, 24_000, seed=70 + n)
+    dn = placement.nodes_to_device(nodes, "cuda:0")
+    rc, rm = torch.as_tensor(pods.req_cpu_milli).cuda(), torch.as_tensor(pods.req_mem_bytes).cuda()
+    ws = torch.empty(placement.snapshot_workspace_bytes(n, 24_000, False), dtype=torch.uint8, device="cuda")
+    placement.snapshot_place(dn, rc[:9000].contiguous(), rm[:9000].contiguous(), 1, 1, workspace=ws)
+    before = placement.launch_count()
+    gi, gs = placement.snapshot_place_again(dn, rc[9000:].contiguous(), rm[9000:].contiguous(), 1, ws)
+    torch.cuda.synchronize()
+    assert placement.launch_count() - before == 1
+    rest = PodTable.from_columns(pods.req_cpu_milli[9000:], pods.req_mem_bytes[9000:])
+    oi, os_ = oracle_snapshot(nodes, rest, 1, 1)
+    assert_same_idx(gi.cpu().numpy(), oi)
+    assert_same_f64(gs.cpu().numpy(), os_)
+    with pytest.raises(PlacementError):                            # per-pod strategy plans are not reusable
+        lib = placement._lib.load()
+        nst, device, _ = placement._node_struct(dn)
+        pst, p, strat, _ = placement._pod_struct(rc, rm, torch.as_tensor(pods.strategy_ids).cuda(), device)
+        placement.check(lib.kp_snapshot_place_again(ctypes.byref(nst), ctypes.byref(pst), 0, 1, gi.data_ptr(), gs.data_ptr(),
+                                                    ws.data_ptr(), ws.numel(), None), "kp_snapshot_place_again")
+
+
 def test_session_inputs_that_need_conversion_stay_alive_for_the_call():
     """Columns of the 'wrong' dtype or layout (bool ready, int32 counts, Python lists, strided views, float
     tensors) are converted to temporaries; the temporaries must live until kp_session_snapshot has returned."""
