@@ -177,7 +177,7 @@ int kp_snapshot_place_noalloc(const kp_node_table *nodes, const kp_pod_table *po
  * kp_snapshot_place_node_sharded = kp_ns_keys + kp_ns_place + kp_ns_reduce, all stream-ordered and
  * asynchronous; every rank must make the same calls in the same order.  (The three steps are separate so
  * that ranks emulated on ONE device can be driven in lock step: a kernel there must never wait for a
- * kernel that has not been launched yet.)  A rank that waits more than 4 s for a peer gives up and sets
+ * kernel that has not been launched yet.)  A rank that waits more than 15 s for a peer gives up and sets
  * the error word that kp_exchange_error reads (after synchronising): the results are then invalid.
  * Workspace: kp_snapshot_workspace_bytes(local n_nodes, n_pods, per_pod_strategy).
  */

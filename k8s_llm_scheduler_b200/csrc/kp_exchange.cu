@@ -31,7 +31,7 @@
 namespace kp {
 
 constexpr int kMaxWorld = 16;
-constexpr unsigned long long kWaitNs = 4000000000ull;          // 4 s: give up on a peer
+constexpr unsigned long long kWaitNs = 15000000000ull;         // 15 s: give up on a peer (a rank may still be loading its CUDA modules)
 
 struct ExHeader {                       // start of every rank's buffer
     uint32_t flag[2][kMaxWorld];        // flag[phase][source rank] = epoch reached (written by that rank)
