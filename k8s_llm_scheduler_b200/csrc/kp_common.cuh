@@ -270,6 +270,13 @@ size_t sort_temp_bytes(int64_t n);
 int sort_pairs_u64(void *temp, size_t temp_bytes, const unsigned long long *keys_in, unsigned long long *keys_out,
                    const uint32_t *vals_in, uint32_t *vals_out, int n, cudaStream_t stream);
 int inclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream);
+// kp_ranksort.cu: hand-written sort of several key arrays at once (chunk sort + rank by merge counting), for up to
+// kRankSortMax entries per array
+constexpr int kRankSortMax = 65536;
+struct RankSortArrays { int idx[8]; int count; };
+size_t rank_sort_scratch_bytes(int64_t n, int arrays);
+int rank_sort_pairs_u64(void *scratch, size_t scratch_bytes, const unsigned long long *keys_in, size_t in_stride, const RankSortArrays &which,
+                        int n, unsigned long long *kout, uint32_t *vout, size_t out_stride, cudaStream_t stream);
 int exclusive_sum_u32(void *temp, size_t temp_bytes, const uint32_t *in, uint32_t *out, int n, cudaStream_t stream);
 int sort_pairs_u32_desc(void *temp, size_t temp_bytes, const uint32_t *keys_in, uint32_t *keys_out, const uint32_t *vals_in,
                         uint32_t *vals_out, int64_t n, cudaStream_t stream);

@@ -741,8 +741,8 @@ static FastLayout fast_layout(int64_t n, int64_t p)
     L.off_iota = o;  o = align_up(o + sizeof(uint32_t) * T);
     L.off_keys = o;  o = align_up(o + sizeof(uint64_t) * 5 * T);
     L.off_score = o; o = align_up(o + sizeof(double) * kMaxStrategies * T);
-    L.off_kout = o;  o = align_up(o + sizeof(uint64_t) * T);
-    L.off_vout = o;  o = align_up(o + sizeof(uint32_t) * T);
+    L.off_kout = o;  o = align_up(o + sizeof(uint64_t) * 5 * T);      // sorted keys / source entries of the five key arrays
+    L.off_vout = o;  o = align_up(o + sizeof(uint32_t) * 5 * T);
     L.off_flag = o;  o = align_up(o + sizeof(uint32_t) * T);
     L.off_incl = o;  o = align_up(o + sizeof(uint32_t) * T);
     L.off_rank = o;  o = align_up(o + sizeof(uint32_t) * 5 * T);
@@ -761,6 +761,7 @@ static FastLayout fast_layout(int64_t n, int64_t p)
         L.off_bvals[b] = o; o = align_up(o + sizeof(uint32_t) * L.batch_cap);
     }
     L.tmp_bytes = std::max(sort_temp_bytes(L.total), L.batch_cap ? sort_temp_bytes(L.batch_cap) : (size_t)0);
+    if (L.total <= kRankSortMax) L.tmp_bytes = std::max(L.tmp_bytes, rank_sort_scratch_bytes(L.total, 5));
     L.off_tmp = o;   o = align_up(o + L.tmp_bytes);
     L.bytes = o;
     return L;
@@ -913,15 +914,27 @@ int greedy_fast_device(const kp_node_table &nodes, const kp_pod_table &pods, int
     const int gb = (total + 255) / 256;
     fast_entries_kernel<<<gb, 256, 0, stream>>>(in, hdr, e, iota);
     KP_LAUNCH_CHECK("fast_entries_kernel");
-    for (int a = 0; a < 5; ++a) {                                     // 0..2 score orders, 3..4 thresholds
-        if (a < kMaxStrategies && !(in.strat_mask & (1 << a))) continue;
-        int st = sort_pairs_u64(tmp, L.tmp_bytes, keys + (size_t)a * total, kout, iota, vout, total, stream);
+    // sorted order of the five key arrays (0..2 score orders, 3..4 thresholds): all of them in two launches of our own
+    // for tables up to kRankSortMax entries (kp_ranksort.cu), one library radix sort per array beyond
+    if (total <= kRankSortMax) {
+        RankSortArrays which{};
+        for (int a = 0; a < 5; ++a)
+            if (a >= kMaxStrategies || (in.strat_mask & (1 << a))) which.idx[which.count++] = a;
+        const int st = rank_sort_pairs_u64(tmp, L.tmp_bytes, keys, (size_t)total, which, total, kout, vout, (size_t)total, stream);
         if (st != KP_OK) return st;
-        fast_flags_kernel<<<gb, 256, 0, stream>>>(kout, total, flag);
+    }
+    for (int a = 0; a < 5; ++a) {
+        if (a < kMaxStrategies && !(in.strat_mask & (1 << a))) continue;
+        unsigned long long *ko = kout + (size_t)a * total;
+        uint32_t *vo = vout + (size_t)a * total;
+        int st = KP_OK;
+        if (total > kRankSortMax) st = sort_pairs_u64(tmp, L.tmp_bytes, keys + (size_t)a * total, ko, iota, vo, total, stream);
+        if (st != KP_OK) return st;
+        fast_flags_kernel<<<gb, 256, 0, stream>>>(ko, total, flag);
         KP_LAUNCH_CHECK("fast_flags_kernel");
         st = inclusive_sum_u32(tmp, L.tmp_bytes, flag, incl, total, stream);
         if (st != KP_OK) return st;
-        fast_rank_kernel<<<gb, 256, 0, stream>>>(kout, vout, flag, incl, total, rank + (size_t)a * total,
+        fast_rank_kernel<<<gb, 256, 0, stream>>>(ko, vo, flag, incl, total, rank + (size_t)a * total,
                                                  a >= kMaxStrategies ? uniq + (size_t)(a - kMaxStrategies) * total : nullptr,
                                                  a >= kMaxStrategies ? &hdr->distinct[a - kMaxStrategies] : &hdr->score_ranks[a]);
         KP_LAUNCH_CHECK("fast_rank_kernel");

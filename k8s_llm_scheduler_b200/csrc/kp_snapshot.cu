@@ -715,6 +715,15 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         for (int s = 0; s < kMaxStrategies; ++s) if (strat_mask & (1 << s)) list.idx[list.count++] = s;
         list.idx[list.count++] = 3;
         list.idx[list.count++] = 4;
+        if (n <= kRankSortMax) {
+            // every key array in two launches of our own (kp_ranksort.cu); the radix sort of the library needs ten
+            // latency-bound launches per array at these sizes
+            RankSortArrays which{};
+            for (int q = 0; q < list.count; ++q) which.idx[which.count++] = list.idx[q];
+            const int st = rank_sort_pairs_u64(tmp, L.sort_tmp_bytes * (kMaxStrategies + 2), keys, (size_t)n, which, (int)n, kout, vout, (size_t)n,
+                                               stream);
+            if (st != KP_OK) return st;
+        } else {
         // the sorts are independent and latency-bound (tens of thousands of keys, ~9 launches each):
         // all but the first run on side streams, forked from and joined back into the caller's stream
         SideStreams *side = side_streams();
@@ -736,6 +745,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
             }
         }
         if (side_lock.owns_lock()) side_lock.unlock();
+        }
         post_sort_kernel<<<dim3(nb, list.count), 256, 0, stream>>>(kout, vout, (int)n, (int)L.npad, list, pos, sorted, flag);
         KP_LAUNCH_CHECK("post_sort_kernel");
         for (int tq = 0; tq < 2; ++tq) {

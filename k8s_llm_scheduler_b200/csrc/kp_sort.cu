@@ -1,4 +1,6 @@
-// Library sorts / scans for the node plan of LARGE tables (more than 8192 nodes).
+// Library sorts / scans of the plans: prefix scans, the 32-bit entry sort of the batched greedy prefix, and the
+// key-array sorts of tables beyond kRankSortMax entries (up to that size kp_ranksort.cu sorts them with our own
+// two kernels).
 //
 // The plan of a large table orders up to five 64-bit key arrays of n nodes (three strategy
 // orders, two threshold orders).  That is a plain key-value radix sort, not part of the hot
