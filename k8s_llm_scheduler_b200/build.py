@@ -31,31 +31,77 @@ def find_nvcc() -> str:
     raise RuntimeError("nvcc not found (set NVCC=/path/to/nvcc)")
 
 
-def _stale() -> bool:
-    if not LIB_PATH.exists():
-        return True
-    built = LIB_PATH.stat().st_mtime
-    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + \
-        [PKG_DIR.parent / "include" / "k8s_place_b200.h"]
-    return any(d.stat().st_mtime > built for d in deps)
+def _digest(paths, extra: str = "") -> str:
+    """Content hash of a target's inputs.  A built file is current iff the hash stored next to it matches: file
+    times say nothing after the tree has been copied to another machine (the GPU box), where a time-based check
+    made every rank of a multi-process run rebuild -- and overwrite -- the library at the same moment."""
+    import hashlib
+    h = hashlib.sha256(extra.encode())
+    for p in sorted(paths):
+        h.update(p.name.encode())
+        h.update(p.read_bytes())
+    return h.hexdigest()
+
+
+def _current(target: Path, digest: str) -> bool:
+    stamp = target.with_name(target.name + ".srchash")
+    return target.exists() and stamp.exists() and stamp.read_text().strip() == digest
+
+
+def _stamp(target: Path, digest: str) -> None:
+    stamp = target.with_name(target.name + ".srchash")
+    tmp = stamp.with_name(stamp.name + f".{os.getpid()}")
+    tmp.write_text(digest + "\n")
+    os.replace(tmp, stamp)
+
+
+class _BuildLock:
+    """One builder at a time per tree (several ranks may start together); the others wait and then find the
+    target current."""
+
+    def __enter__(self):
+        import fcntl
+        self.f = open(PKG_DIR / ".build.lock", "w")
+        fcntl.flock(self.f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+        fcntl.flock(self.f, fcntl.LOCK_UN)
+        self.f.close()
+
+
+def _library_digest() -> str:
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [PKG_DIR.parent / "include" / "k8s_place_b200.h"]
+    return _digest(deps, " ".join(NVCC_FLAGS + SOURCES))
 
 
 def build_library(force: bool = False, verbose: bool = False) -> Path:
-    """Compile the CUDA library if it is missing or older than its sources."""
-    if not force and not _stale():
-        return LIB_PATH
+    """Compile the CUDA library if it is missing or was built from other sources (content hash, see _digest)."""
     extra = os.environ.get("KP_NVCC_EXTRA", "").split()          # experiments only (e.g. -DKP_UPDATE_MODE=1)
     out = Path(os.environ.get("KP_LIB_OUT", str(LIB_PATH)))
-    cmd = [find_nvcc(), *NVCC_FLAGS, *extra, "-o", str(out), *[str(CSRC / s) for s in SOURCES]]
-    if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
-        print(" ".join(cmd))
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
-    if verbose:
-        print(res.stderr)
+    variant = bool(extra) or out != LIB_PATH
+    digest = _library_digest()
+    if not force and not variant and _current(LIB_PATH, digest):
+        return LIB_PATH
+    with _BuildLock():
+        if not force and not variant and _current(LIB_PATH, digest):     # another process built it while we waited
+            return LIB_PATH
+        tmp = out.with_name(out.name + f".{os.getpid()}.tmp")
+        cmd = [find_nvcc(), *NVCC_FLAGS, *extra, "-o", str(tmp), *[str(CSRC / s) for s in SOURCES]]
+        if verbose:
+            cmd.insert(1, "-Xptxas")
+            cmd.insert(2, "-v")
+            print(" ".join(cmd))
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            tmp.unlink(missing_ok=True)
+            raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
+        os.replace(tmp, out)                                          # readers never see a half-written library
+        if not variant:
+            _stamp(LIB_PATH, digest)
+        if verbose:
+            print(res.stderr)
     return LIB_PATH
 
 
@@ -69,15 +115,23 @@ def build_pyobj(force: bool = False) -> Path:
     (csrc/kp_pyobj.c); optional: tables.py keeps the same conversions in Python."""
     import sysconfig
     out, src = pyobj_path(), CSRC / "kp_pyobj.c"
-    if not force and out.exists() and out.stat().st_mtime >= src.stat().st_mtime:
+    digest = _digest([src], sysconfig.get_config_var("EXT_SUFFIX") or "")
+    if not force and _current(out, digest):
         return out
     cc = os.environ.get("CC") or shutil.which("gcc") or shutil.which("cc")
     if not cc:
         raise RuntimeError("no C compiler for the record-walker extension")
-    cmd = [cc, "-O2", "-shared", "-fPIC", "-I", sysconfig.get_paths()["include"], str(src), "-o", str(out), "-lm"]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError(f"{cc} failed:\n{res.stdout}\n{res.stderr}")
+    with _BuildLock():
+        if not force and _current(out, digest):
+            return out
+        tmp = out.with_name(out.name + f".{os.getpid()}.tmp")
+        cmd = [cc, "-O2", "-shared", "-fPIC", "-I", sysconfig.get_paths()["include"], str(src), "-o", str(tmp), "-lm"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            tmp.unlink(missing_ok=True)
+            raise RuntimeError(f"{cc} failed:\n{res.stdout}\n{res.stderr}")
+        os.replace(tmp, out)
+        _stamp(out, digest)
     return out
 
 
@@ -91,8 +145,8 @@ def build_torch_ext(force: bool = False) -> Path:
     import torch
     from torch.utils import cpp_extension as ce
     src = CSRC / "kp_torch_ext.cpp"
-    deps = [src, PKG_DIR.parent / "include" / "k8s_place_b200.h"]
-    if not force and TORCH_EXT_PATH.exists() and all(TORCH_EXT_PATH.stat().st_mtime >= d.stat().st_mtime for d in deps):
+    digest = _digest([src, PKG_DIR.parent / "include" / "k8s_place_b200.h"], torch.__version__)
+    if not force and _current(TORCH_EXT_PATH, digest):
         return TORCH_EXT_PATH
     build_library()
     cxx = os.environ.get("CXX") or shutil.which("g++") or shutil.which("c++")
@@ -101,12 +155,19 @@ def build_torch_ext(force: bool = False) -> Path:
     cuda_home = Path(find_nvcc()).resolve().parents[1]
     inc = [f"-I{p}" for p in ce.include_paths()] + [f"-I{cuda_home / 'include'}"]
     libdir = ce.library_paths()[0]
-    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
-           *inc, str(src), "-o", str(TORCH_EXT_PATH), f"-L{PKG_DIR}", f"-l:{LIB_NAME}", f"-L{libdir}",
-           "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{libdir}"]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError(f"{cxx} failed:\n{res.stdout}\n{res.stderr}")
+    with _BuildLock():
+        if not force and _current(TORCH_EXT_PATH, digest):
+            return TORCH_EXT_PATH
+        tmp = TORCH_EXT_PATH.with_name(TORCH_EXT_NAME + f".{os.getpid()}.tmp")
+        cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+               *inc, str(src), "-o", str(tmp), f"-L{PKG_DIR}", f"-l:{LIB_NAME}", f"-L{libdir}",
+               "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{libdir}"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            tmp.unlink(missing_ok=True)
+            raise RuntimeError(f"{cxx} failed:\n{res.stdout}\n{res.stderr}")
+        os.replace(tmp, TORCH_EXT_PATH)
+        _stamp(TORCH_EXT_PATH, digest)
     return TORCH_EXT_PATH
 
 

@@ -80,3 +80,26 @@ def test_argument_validation_needs_no_gpu(lib):
 def test_missing_library_fails_loudly(tmp_path):
     with pytest.raises(ImportError, match="no CPU fallback"):
         _lib.load(tmp_path / "libk8s_place_b200.so")
+
+
+def test_rebuild_is_decided_by_content_not_by_file_times(lib):
+    """After the tree has been copied to another machine file times mean nothing: a library whose stored source hash
+    matches is current whatever the mtimes say (a time-based check once made all ranks of a torchrun job rebuild, and
+    overwrite, the library at the same moment)."""
+    import os
+    import time
+    from k8s_llm_scheduler_b200 import build as B
+    assert B._current(LIB_PATH, B._library_digest())
+    src = B.CSRC / "kp_api.cu"
+    before = LIB_PATH.stat().st_mtime_ns
+    os.utime(src, None)                                   # source now "newer" than the library
+    t = time.perf_counter()
+    assert build_library() == LIB_PATH
+    assert LIB_PATH.stat().st_mtime_ns == before and time.perf_counter() - t < 5.0      # no compiler run
+    stamp = LIB_PATH.with_name(LIB_PATH.name + ".srchash")
+    good = stamp.read_text()
+    try:
+        stamp.write_text("0" * 64 + "\n")
+        assert not B._current(LIB_PATH, B._library_digest())
+    finally:
+        stamp.write_text(good)
