@@ -213,7 +213,6 @@ struct PlaceTuning {
     unsigned long long *plan_sig = nullptr;
     bool reuse_plan_forced = false;   // reuse even with per-pod strategies: the plan was built by a plan_only call just before
     bool plan_only = false;           // build the node plan in the workspace and return (no pods are scored)
-    bool no_small_segments = false;   // small tables are never cut into node segments (no per-pod merge buffers in the layout)
     // Node-sharded form (kp_exchange.cu): besides index and score the epilogue stores, per pod, the chosen node's
     // GLOBAL rank position gpos_by_pos[strategy * gpos_stride + local rank position] (0xffffffff = no node).
     uint32_t *out_gpos = nullptr;

@@ -58,12 +58,7 @@ struct SnapLayout {
     size_t sort_tmp_bytes, total;
 };
 
-// Node segments (grid.y of place_kernel) need two per-pod merge buffers.  Large tables always have them; small
-// tables get them from kSegMinPods pods on, where cutting a small table into its 1024-node tiles is what keeps the
-// pod chunks from quantising into whole waves (a 2 500-node slice x 2 M pods is 2.2 waves of 16-pods-per-lane CTAs).
-constexpr int64_t kSegMinPods = 1 << 18;
-
-static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod, bool small_segments = true)
+static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
 {
     SnapLayout L{};
     L.n = n;
@@ -94,10 +89,9 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod, bool small_seg
     L.off_flag = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
     L.off_incl = o;     o = align_up(o + sizeof(uint32_t) * 2 * npb);
     L.off_sort_tmp = o; o = align_up(o + L.sort_tmp_bytes * (kMaxStrategies + 2));
-    const bool seg = big || (small_segments && p >= kSegMinPods);
-    L.off_chunk_done = o; L.chunk_done_bytes = sizeof(uint32_t) * (seg ? L.chunks : 0); o = align_up(o + L.chunk_done_bytes);
+    L.off_chunk_done = o; L.chunk_done_bytes = sizeof(uint32_t) * (big ? L.chunks : 0); o = align_up(o + L.chunk_done_bytes);
     L.off_perm = o;     o = align_up(o + sizeof(uint32_t) * (per_pod ? L.slots : 0));
-    L.off_best = o;     o = align_up(o + sizeof(uint32_t) * (seg ? L.slots : 0));
+    L.off_best = o;     o = align_up(o + sizeof(uint32_t) * (big ? L.slots : 0));
     L.total = o;
     return L;
 }
@@ -602,7 +596,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     if (const char *v = getenv("KP_PLACE_RESIDENT")) resident_cap = atoi(v);        // experiments only
     if (const char *v = getenv("KP_FLOW_WINDOW")) flow_window = (unsigned)atoi(v);  // experiments only
     const bool per_pod = pods.strategy_ids != nullptr;
-    const SnapLayout L = make_layout(n, P, per_pod, !tuning.no_small_segments);
+    const SnapLayout L = make_layout(n, P, per_pod);
     if (!ws || ws_bytes < L.total || (reinterpret_cast<uintptr_t>(ws) & (kAlign - 1))) {
         set_error("snapshot workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", L.total,
                   ws_bytes, ws);
@@ -640,11 +634,8 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     // multi-kernel plan), then by carrying fewer pods per CTA.
     const int sms = sm_count_cached();
     const bool big = n > kSmallMaxNodes;
-    // (small tables: only the tiles that hold table entries, not the padding behind them; never when the pod rows are
-    // read in place from host memory -- every segment would fetch them again)
-    const bool small_seg = !big && L.chunk_done_bytes > 0 && !(tuning.flow && flow_window > 0);
-    const int ntiles_wide = (int)(((big ? L.npad : (n + 3) / 4 * 4) + kTileNodesWide - 1) / kTileNodesWide);
-    const int max_nseg = (big || small_seg) ? ntiles_wide : 1;
+    const int ntiles_wide = (int)((L.npad + kTileNodesWide - 1) / kTileNodesWide);
+    const int max_nseg = big ? ntiles_wide : 1;
     int cfg = kFallbackCfg;
     // The top of the ladder carries 16 pods per lane: the per-iteration overhead of the inner loop (one LDS.128,
     // four position adds, loop control: 11 instructions) is then spread over 64 pairs instead of 32, and 16
@@ -780,7 +771,6 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
         KP_LAUNCH_CHECK("group_assign_kernel");
     }
     if (nseg > 1) KP_CUDA(cudaMemsetAsync(best_pos, 0xff, sizeof(uint32_t) * n_chunks * chunk_pods, stream));
-    if (nseg > 1 && !big) KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.chunk_done_bytes, stream));   // (the large-table plan zeroes it)
     PlaceParams pp{};
     pp.req_cpu = (const long long *)pods.req_cpu_milli;
     pp.req_mem = (const long long *)pods.req_mem_bytes;
@@ -853,7 +843,7 @@ int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods,
                   (long long)pods.n_pods, (long long)kNoAllocMaxPods);
         return KP_ERR_CAPACITY;
     }
-    if (make_layout(nodes.n_nodes, pods.n_pods, per_pod, false).total > kNoAllocScratchBytes) {
+    if (make_layout(nodes.n_nodes, pods.n_pods, per_pod).total > kNoAllocScratchBytes) {
         set_error("kp_snapshot_place_noalloc: internal scratch too small for this call");
         return KP_ERR_CAPACITY;
     }
@@ -869,10 +859,8 @@ int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods,
     }
     // the array keeps the previous call's contents; snapshot_place_device rewrites every
     // counter, merge buffer and table entry (including padding) it later reads
-    PlaceTuning tuning;
-    tuning.no_small_segments = true;           // per-pod merge buffers would make the scratch grow with the pod count
     return snapshot_place_device(nodes, pods, strategy, filter_mode, out_idx, out_score,
-                                 scratch_addr[dev], kNoAllocScratchBytes, stream, tuning);
+                                 scratch_addr[dev], kNoAllocScratchBytes, stream);
 }
 
 }  // namespace kp

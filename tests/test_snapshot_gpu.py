@@ -115,6 +115,18 @@ def test_config5_reduced_mixed_strategies():
     assert 0.27 < (gi < 0).mean() < 0.33
 
 
+@pytest.mark.parametrize("n,p", [(2500, 600_000), (8192, 270_000), (1025, 300_001), (3000, 262_144), (900, 530_000)])
+def test_small_tables_with_many_pods(n, p):
+    """One rank's share of a node-sharded cluster: a small table under hundreds of thousands of pods, uniform strategy
+    (both placement kernels, either side of 2^19 pods) and per-pod strategies."""
+    nodes, pods = synth.config5(n, p, seed=77 + n)
+    for sid, per_pod in ((0, False), (1, False), (0, True)):
+        gi, gs = device_snapshot(nodes, pods, sid, 1, per_pod=per_pod)
+        oi, os_ = oracle_snapshot(nodes, pods, sid, 1, per_pod=per_pod)
+        assert_same_idx(gi, oi, f"n={n} p={p} strategy={sid} per_pod={per_pod}")
+        assert_same_f64(gs, os_)
+
+
 def test_all_equal_nodes_first_wins():
     nodes = synth.all_equal_nodes(6000)
     nodes.ready[:5] = 0
