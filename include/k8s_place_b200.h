@@ -252,6 +252,15 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
                       int strategy, int filter_mode, int64_t *out_node_idx, double *out_score,
                       int64_t *out_pod_count, double *out_cpu_usage_pct,
                       double *out_mem_usage_pct);
+/* ONE decision for ONE pod -- the reference's own call shape: HuggingFaceClient._fallback_decision(node_metrics,
+ * reason) is called once per pending pod (scheduler.py:598 -> :521-559) with the node list it was just handed.
+ * `nodes` is host memory (required).  Under KP_FILTER_READY the request arguments and the two allocatable columns
+ * are not read (pass 0 and any valid arrays).  Tables of up to 2048 rows never leave the host: the columns are
+ * gathered into the session's pinned staging buffer, ONE single-CTA kernel reads them across the host link, and the
+ * answer comes back through a pinned word the call polls -- no copies, no stream synchronisation; larger tables go
+ * through kp_session_snapshot with a one-pod table.  *out_node_idx = -1, *out_score = -1.0: no node can win. */
+int kp_session_decide(kp_session *s, const kp_node_table *nodes, int strategy, int filter_mode,
+                      int64_t req_cpu_milli, int64_t req_mem_bytes, int64_t *out_node_idx, double *out_score);
 /* Bytes moved host->device and device->host by the last session call. */
 int kp_session_last_copy_bytes(const kp_session *s, int64_t *h2d, int64_t *d2h);
 

@@ -18,11 +18,30 @@ from typing import Any, Callable, List, Mapping, Optional, Sequence
 
 import numpy as np
 
-from ._lib import FILTER_CAPACITY, FILTER_READY, PlacementError
+from ._lib import FILTER_CAPACITY, FILTER_READY, KpNodeTable, PlacementError
 from .placement import Session
-from .tables import NodeTable, PodTable, SchedulingDecision, strategy_id
+from .tables import NODE_COLUMNS, NodeTable, PodTable, SchedulingDecision, _record_walker, strategy_id
 
 logger = logging.getLogger(__name__)
+
+
+class _ColumnBuffers:
+    """Node-table columns kept across calls: the C record walker (csrc/kp_pyobj.c) fills rows [0, n) in place and the
+    ready-made KpNodeTable points at them -- a decision allocates no arrays and rebuilds no ctypes structure."""
+    _DTYPES = {"alloc_cpu_milli": np.int64, "alloc_mem_bytes": np.int64, "pod_count": np.int64, "max_pods": np.int64,
+               "ready": np.uint8, "cpu_usage_pct": np.float64, "mem_usage_pct": np.float64}
+
+    def __init__(self, capacity: int):
+        self.capacity = capacity
+        self.arrays = [np.zeros(capacity, self._DTYPES[k]) for k in NODE_COLUMNS]
+        self.struct = KpNodeTable()
+        for k, a in zip(NODE_COLUMNS, self.arrays):
+            setattr(self.struct, k, a.ctypes.data)
+
+    def fill(self, walker, node_metrics, mode: int) -> KpNodeTable:
+        walker.node_metrics_to_columns(node_metrics, *self.arrays, mode | 4)      # + 4: buffers larger than the list
+        self.struct.n_nodes = len(node_metrics)
+        return self.struct
 
 
 class FallbackPlacer:
@@ -34,14 +53,19 @@ class FallbackPlacer:
         self.config = config if config is not None else {}
         self.decision_cls = decision_cls
         self.session = Session(device=device, max_nodes=max_nodes, max_pods=max_pods)
-        # one-decision calls: the single (dummy) request and the result live in pinned host memory, so the
-        # kernels read / write them in place and the call needs no pod or result copies
-        import torch
-        self._one_pod = (torch.zeros(1, dtype=torch.int64).pin_memory(), torch.zeros(1, dtype=torch.int64).pin_memory(), None)
-        self._one_out = (torch.empty(1, dtype=torch.int64).pin_memory(), torch.empty(1, dtype=torch.float64).pin_memory())
+        # one-decision calls go through kp_session_decide (one kernel, no copies, no stream synchronisation for
+        # small tables); the node columns are written into buffers kept across calls
+        self._cols = _ColumnBuffers(min(max_nodes, 1 << 16))
 
     def strategy(self) -> str:
         return self.config.get("fallback", {}).get("strategy", "resource_balanced")
+
+    def _node_columns(self, node_metrics, ready_only: bool):
+        """The node table of one decision: the kept column buffers when the C walker is there and the list fits."""
+        walker = _record_walker()
+        if walker is not None and len(node_metrics) <= self._cols.capacity:
+            return self._cols.fill(walker, node_metrics, 2 if ready_only else 1)
+        return NodeTable.from_node_metrics(node_metrics, ready_only=ready_only)
 
     # ---- same shape as the reference method (minus self) ----
     def fallback_decision(self, node_metrics: Sequence[Any], reason: str):
@@ -51,9 +75,7 @@ class FallbackPlacer:
         try:
             # Ready-only filter: available_cpu / available_memory are dead inputs (the reference never reads
             # them, scheduler.py:531-549) and are not even looked at
-            table = NodeTable.from_node_metrics(node_metrics, ready_only=True)
-            idx, _ = self.session.snapshot(table, self._one_pod, strategy_id(strategy), FILTER_READY, out=self._one_out)
-            i = int(idx[0])
+            i, _ = self.session.decide(self._node_columns(node_metrics, ready_only=True), strategy_id(strategy), FILTER_READY)
             if i >= 0:                                              # scheduler.py:551-557
                 return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
                                          reasoning=f"Fallback ({strategy}): {reason}",
@@ -68,10 +90,9 @@ class FallbackPlacer:
             return self.decision_cls("", 0.0, "No nodes available", True)
         strategy = self.strategy()
         try:
-            table = NodeTable.from_node_metrics(node_metrics)
             pods = PodTable.from_pod_specs([pod_spec])
-            idx, _ = self.session.snapshot(table, pods, strategy_id(strategy), FILTER_CAPACITY)
-            i = int(idx[0])
+            i, _ = self.session.decide(self._node_columns(node_metrics, ready_only=False), strategy_id(strategy), FILTER_CAPACITY,
+                                       int(pods.req_cpu_milli[0]), int(pods.req_mem_bytes[0]))
             if i >= 0:
                 return self.decision_cls(selected_node=node_metrics[i].name, confidence=0.4,
                                          reasoning=f"Fallback ({strategy}): {reason}",

@@ -16,7 +16,7 @@ PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
 LIB_NAME = "libk8s_place_b200.so"
 LIB_PATH = PKG_DIR / LIB_NAME
-SOURCES = ["kp_api.cu", "kp_snapshot.cu", "kp_greedy.cu", "kp_greedy_fast.cu", "kp_sort.cu", "kp_ranksort.cu", "kp_ingest.cu", "kp_cachekey.cu", "kp_diag.cu", "kp_exchange.cu"]
+SOURCES = ["kp_api.cu", "kp_snapshot.cu", "kp_greedy.cu", "kp_greedy_fast.cu", "kp_sort.cu", "kp_ranksort.cu", "kp_ingest.cu", "kp_cachekey.cu", "kp_diag.cu", "kp_exchange.cu", "kp_decide.cu"]
 NVCC_FLAGS = [
     "-shared", "-Xcompiler", "-fPIC", "-O3", "-std=c++17",
     "-gencode", "arch=compute_100a,code=sm_100a",

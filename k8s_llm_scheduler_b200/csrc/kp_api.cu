@@ -110,6 +110,9 @@ struct kp_session {
     // large uploads are pipelined: pod columns go up in chunks on copy_stream while earlier chunks are scored
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t chunk_ready[2] = {nullptr};
+    // kp_session_decide: answer slot in pinned host memory (the kernel stores, the host polls) and its call counter
+    DecideSlot *h_slot = nullptr;
+    unsigned long long decide_seq = 0;
 };
 
 namespace {
@@ -473,6 +476,8 @@ int kp_session_create(int device, int64_t max_nodes, int64_t max_pods, kp_sessio
         s->stage_bytes = want < kStageMaxBytes ? want : kStageMaxBytes;
         if (s->stage_bytes) e = cudaHostAlloc((void **)&s->h_stage, s->stage_bytes, cudaHostAllocDefault);
     }
+    if (e == cudaSuccess) e = cudaHostAlloc((void **)&s->h_slot, sizeof(DecideSlot), cudaHostAllocDefault);
+    if (e == cudaSuccess) memset(s->h_slot, 0, sizeof(DecideSlot));
     if (const char *v = getenv("KP_SESSION_DIRECT")) s->direct = atoi(v) & 3;   // experiments only
     if (e != cudaSuccess) {
         kp_session_destroy(s);
@@ -494,6 +499,7 @@ void kp_session_destroy(kp_session *s)
     cudaFree(s->d_ws);
     cudaFree(s->d_flow);
     if (s->h_stage) cudaFreeHost(s->h_stage);
+    if (s->h_slot) cudaFreeHost(s->h_slot);
     for (int c = 0; c < kPipeMaxChunks; ++c) if (s->chunk_ready[c]) cudaEventDestroy(s->chunk_ready[c]);
     if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -627,6 +633,62 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
         s->d2h += 2 * (int64_t)b8;
     }
     KP_CUDA(cudaStreamSynchronize(s->stream));
+    return KP_OK;
+}
+
+// One decision for one pod: the reference's own call shape (scheduler.py:598 -> :521-559).  Small tables are scored
+// where they lie (columns gathered into the pinned staging buffer, read across the host link by ONE kernel that also
+// writes the answer into pinned memory); the host polls the answer's sequence word instead of synchronising.
+int kp_session_decide(kp_session *s, const kp_node_table *nodes, int strategy, int filter_mode, int64_t req_cpu_milli,
+                      int64_t req_mem_bytes, int64_t *out_node_idx, double *out_score)
+{
+    if (!s || !nodes || !out_node_idx || !out_score) { set_error("session / nodes / output is NULL"); return KP_ERR_INVALID_ARG; }
+    int st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    const int64_t n = nodes->n_nodes;
+    const size_t b8 = sizeof(int64_t) * (size_t)(n > 0 ? n : 0);
+    const size_t col = align_up(b8);
+    if (n < 0 || n > kDecideMaxNodes || n > s->max_nodes || !s->h_stage || 6 * col + (size_t)n > s->stage_bytes) {
+        // larger tables: the batched path with a one-pod table
+        const int64_t rc = req_cpu_milli, rm = req_mem_bytes;
+        const kp_pod_table one{1, &rc, &rm, nullptr};
+        return kp_session_snapshot(s, nodes, &one, strategy, filter_mode, out_node_idx, out_score);
+    }
+    kp_pod_table none{};
+    if ((st = check_tables(nodes, &none)) != KP_OK) return st;
+    DeviceGuard guard(s->device);
+    s->h2d = s->d2h = 0;
+    const void *src[6] = {nodes->alloc_cpu_milli, nodes->alloc_mem_bytes, nodes->pod_count,
+                          nodes->max_pods, nodes->cpu_usage_pct, nodes->mem_usage_pct};
+    for (int c = 0; c < 6; ++c) memcpy(s->h_stage + c * col, src[c], b8);
+    if (n > 0) memcpy(s->h_stage + 6 * col, nodes->ready, (size_t)n);
+    kp_node_table t{};
+    t.n_nodes = n;
+    t.alloc_cpu_milli = reinterpret_cast<const int64_t *>(s->h_stage + 0 * col);
+    t.alloc_mem_bytes = reinterpret_cast<const int64_t *>(s->h_stage + 1 * col);
+    t.pod_count = reinterpret_cast<const int64_t *>(s->h_stage + 2 * col);
+    t.max_pods = reinterpret_cast<const int64_t *>(s->h_stage + 3 * col);
+    t.cpu_usage_pct = reinterpret_cast<const double *>(s->h_stage + 4 * col);
+    t.mem_usage_pct = reinterpret_cast<const double *>(s->h_stage + 5 * col);
+    t.ready = s->h_stage + 6 * col;
+    const unsigned long long seq = ++s->decide_seq;
+    if ((st = decide_device(t, strategy, filter_mode, req_cpu_milli, req_mem_bytes, s->h_slot, seq, s->stream)) != KP_OK) return st;
+    s->h2d += 6 * (int64_t)b8 + n;
+    s->d2h += 2 * (int64_t)sizeof(int64_t);
+    // the answer arrives as a release store at system scope: poll it (a few microseconds), and only if it stays away
+    // fall back on the stream -- which also reports a launch that failed
+    volatile unsigned long long *flag = &s->h_slot->seq;
+    bool seen = false;
+    for (int spin = 0; spin < (1 << 22); ++spin) {
+        if (__atomic_load_n(flag, __ATOMIC_ACQUIRE) == seq) { seen = true; break; }
+        __builtin_ia32_pause();
+    }
+    if (!seen) {
+        KP_CUDA(cudaStreamSynchronize(s->stream));
+        if (__atomic_load_n(flag, __ATOMIC_ACQUIRE) != seq) { set_error("decide: the kernel finished without an answer"); return KP_ERR_CUDA; }
+    }
+    *out_node_idx = s->h_slot->idx;
+    *out_score = s->h_slot->score;
     return KP_OK;
 }
 

@@ -255,6 +255,12 @@ int cache_keys_device(const uint8_t *prefix, const int64_t *prefix_off, int64_t 
                       int64_t nodes_len, uint8_t *out, cudaStream_t stream);
 int sm_count_cached();
 // kp_diag.cu: measured issue peak of the snapshot inner loop
+// one decision for one pod (kp_decide.cu): the answer slot lives in pinned host memory
+constexpr int kDecideMaxNodes = 2048;
+struct DecideSlot { long long idx; double score; unsigned long long seq; unsigned long long pad; };
+int decide_device(const kp_node_table &nodes, int strategy, int filter_mode, long long req_cpu_milli, long long req_mem_bytes,
+                  DecideSlot *slot, unsigned long long seq, cudaStream_t stream);
+
 int issue_peak_device(void *scratch, size_t scratch_bytes, double min_ms, cudaStream_t stream, double *pairs_per_sec);
 // Ordinal of the current device, clamped to [0, kMaxDevices): index of per-device once-flags.  Function
 // attributes (opt-in shared memory sizes) belong to a device's context, so such flags are kept per device.

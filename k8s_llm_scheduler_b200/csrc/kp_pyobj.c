@@ -124,26 +124,33 @@ static int is_ready(PyObject *conditions)
     return ready;
 }
 
-static int writable(PyObject *obj, Py_buffer *view, Py_ssize_t itemsize, Py_ssize_t n, const char *what)
+static int writable_at_least(PyObject *obj, Py_buffer *view, Py_ssize_t itemsize, Py_ssize_t n, const char *what, int larger_ok)
 {
     if (PyObject_GetBuffer(obj, view, PyBUF_WRITABLE | PyBUF_C_CONTIGUOUS) < 0) return -1;
-    if (view->len != itemsize * n) {
+    if (larger_ok ? view->len < itemsize * n : view->len != itemsize * n) {
         PyBuffer_Release(view);
         PyErr_Format(PyExc_ValueError, "%s: buffer of %zd bytes, expected %zd", what, view->len, itemsize * n);
         return -1;
     }
     return 0;
 }
+static int writable(PyObject *obj, Py_buffer *view, Py_ssize_t itemsize, Py_ssize_t n, const char *what)
+{
+    return writable_at_least(obj, view, itemsize, n, what, 0);
+}
 
 /* node_metrics_to_columns(nodes, cpu_milli, mem_bytes, pod_count, max_pods, ready, cpu_usage, mem_usage, mode)
  * mode 0: allocatable rounded to the nearest wire integer, 1: must be exact, 2: allocatable columns not read at all
  * (zeros) -- the reference's own decision (scheduler.py:531-549) never looks at available_cpu / available_memory,
- * so under the Ready-only filter whatever they hold (inf, nan, 1e300, ...) must not matter. */
+ * so under the Ready-only filter whatever they hold (inf, nan, 1e300, ...) must not matter.
+ * mode + 4: the buffers may be LARGER than the list (column buffers kept across calls; rows [0, n) are written). */
 static PyObject *node_metrics_to_columns(PyObject *self, PyObject *args)
 {
     PyObject *nodes, *o[7];
     int mode;
     if (!PyArg_ParseTuple(args, "OOOOOOOOi", &nodes, &o[0], &o[1], &o[2], &o[3], &o[4], &o[5], &o[6], &mode)) return NULL;
+    const int larger_ok = (mode & 4) != 0;
+    mode &= 3;
     const int exact = mode == 1, skip_alloc = mode == 2;
     PyObject *seq = PySequence_Fast(nodes, "node_metrics must be a sequence");
     if (!seq) return NULL;
@@ -153,7 +160,7 @@ static PyObject *node_metrics_to_columns(PyObject *self, PyObject *args)
     static const char *names[7] = {"alloc_cpu_milli", "alloc_mem_bytes", "pod_count", "max_pods", "ready", "cpu_usage_pct", "mem_usage_pct"};
     int got = 0, ok = 1;
     for (; got < 7; ++got)
-        if (writable(o[got], &v[got], size[got], n, names[got]) < 0) { ok = 0; break; }
+        if (writable_at_least(o[got], &v[got], size[got], n, names[got], larger_ok) < 0) { ok = 0; break; }
     if (ok) {
         int64_t *milli = v[0].buf, *bytes = v[1].buf, *pc = v[2].buf, *mp = v[3].buf;
         uint8_t *ready = v[4].buf;

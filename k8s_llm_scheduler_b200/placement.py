@@ -195,6 +195,8 @@ class Session:
         self.device, self.max_nodes, self.max_pods = device, max_nodes, max_pods
         self._resident = -1
         self._memo = {}
+        self._d_idx, self._d_score = c_int64(-1), ctypes.c_double(-1.0)      # decide(): answer cells, made once
+        self._d_idx_ref, self._d_score_ref = byref(self._d_idx), byref(self._d_score)
         check(self._lib.kp_session_create(device, max_nodes, max_pods, byref(self._h)),
               "kp_session_create")
 
@@ -311,6 +313,18 @@ class Session:
         if nst is not None:
             self._resident = nst.n_nodes
         return out
+
+    def decide(self, nodes, strategy: int = 0, filter_mode: int = FILTER_READY, req_cpu_milli: int = 0,
+               req_mem_bytes: int = 0) -> Tuple[int, float]:
+        """ONE decision for ONE pod (kp_session_decide; the reference's call shape, scheduler.py:521-559):
+        (node index or -1, score).  ``nodes``: a NodeTable / column dict, or a ready-made KpNodeTable whose
+        arrays the caller keeps alive (adapter.FallbackPlacer keeps one over its column buffers)."""
+        nst = nodes if type(nodes) is KpNodeTable else self._node_struct_memo(nodes)
+        if type(nst) is tuple:
+            nst, _keep = nst
+        check(self._lib.kp_session_decide(self._h, byref(nst), strategy, filter_mode, req_cpu_milli, req_mem_bytes,
+                                          self._d_idx_ref, self._d_score_ref), "kp_session_decide")
+        return self._d_idx.value, self._d_score.value
 
     def greedy(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY):
         """Returns (idx, score, final_pod_count, final_cpu_usage, final_mem_usage) numpy arrays."""

@@ -28,8 +28,12 @@ for n in (3, 100, 1000, 10000, 50000):
     iters = 200 if n <= 1000 else 20
     gpu = med_us(lambda: placer.fallback_decision(nodes, "x"), iters)
     cpu = med_us(lambda: py_oracle.fallback_decision(nodes, "x", "resource_balanced"), iters)
-    pack = med_us(lambda: NodeTable.from_node_metrics(nodes, exact=False), iters)
+    from k8s_llm_scheduler_b200._lib import FILTER_READY  # noqa: E402
+    pack = med_us(lambda: placer._node_columns(nodes, ready_only=True), iters)
+    st = placer._node_columns(nodes, ready_only=True)
+    bare = med_us(lambda: placer.session.decide(st, 0, FILTER_READY), iters)
     a, b = placer.fallback_decision(nodes, "x"), py_oracle.fallback_decision(nodes, "x", "resource_balanced")
     assert a.selected_node == b.selected_node
-    print(f"{n:6d} nodes: adapter {gpu:9.1f} us (of which list -> columns in Python {pack:9.1f} us)   CPython loop {cpu:9.1f} us")
+    print(f"{n:6d} nodes: adapter {gpu:9.1f} us (of which list -> columns {pack:9.1f} us, kp_session_decide {bare:7.1f} us)   "
+          f"CPython loop {cpu:9.1f} us")
 placer.close()

@@ -49,7 +49,9 @@ hp = (torch.as_tensor(p1.req_cpu_milli).pin_memory(), torch.as_tensor(p1.req_mem
 ho = (torch.empty(len(p1), dtype=torch.int64).pin_memory(), torch.empty(len(p1), dtype=torch.float64).pin_memory())
 with placement.Session(0, max_nodes=len(n1), max_pods=len(p1)) as sess:
     sess.snapshot(hn, hp, 1, 1, out=ho)
+    one = sess.decide(n1, 1, 1, int(p1.req_cpu_milli[0]), int(p1.req_mem_bytes[0]))     # one decision, host-memory kernel
 oi, _ = c_oracle.snapshot(n1.columns(), p1.req_cpu_milli, p1.req_mem_bytes, strategy=1, filter_mode=1, threads=4)
 assert np.array_equal(ho[0].numpy(), oi)
+assert one[0] == oi[0]
 torch.cuda.synchronize()
 print("sanitize case ok")
