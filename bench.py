@@ -904,7 +904,41 @@ def run_extras(args, torch, placement, lib, dev, peak_meas):
         extras["cache_keys"] = run_cachekey_extra(torch, lib, dev)
     except Exception as ex:  # noqa: BLE001
         extras["cache_keys"] = {"error": repr(ex)}
+    try:
+        extras["one_decision"] = run_one_decision_extra()
+    except Exception as ex:  # noqa: BLE001
+        extras["one_decision"] = {"error": repr(ex)}
     return extras
+
+
+def run_one_decision_extra(sizes=(3, 100, 1000), iters=300):
+    """The reference's own call shape: ONE _fallback_decision over a list of NodeMetrics records (scheduler.py:521-559),
+    through the drop-in adapter (record walk in C + kp_session_decide) and through the CPython port, wall clock."""
+    from k8s_llm_scheduler_b200.adapter import FallbackPlacer
+    from oracle import py_oracle
+
+    def med_us(fn):
+        for _ in range(10):
+            fn()
+        ts = []
+        for _ in range(iters):
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e6)
+        return statistics.median(ts)
+
+    out = {"api": "adapter.FallbackPlacer.fallback_decision -> kp_session_decide", "strategy": "resource_balanced", "filter": "ready"}
+    placer = FallbackPlacer({"fallback": {"strategy": "resource_balanced"}}, max_nodes=4096, max_pods=16)
+    try:
+        for n in sizes:
+            recs = [py_oracle.node_row(f"n{i}", "32", "128Gi", "110", (i * 37) % 111) for i in range(n)]
+            a, b = placer.fallback_decision(recs, "x"), py_oracle.fallback_decision(recs, "x", "resource_balanced")
+            out[f"{n}_nodes"] = {"adapter_us": med_us(lambda: placer.fallback_decision(recs, "x")),
+                                 "cpython_port_us": med_us(lambda: py_oracle.fallback_decision(recs, "x", "resource_balanced")),
+                                 "same_decision": a.selected_node == b.selected_node and a.reasoning == b.reasoning}
+    finally:
+        placer.close()
+    return out
 
 
 def run_cachekey_extra(torch, lib, dev, n_pods=100_000, n_nodes=1000, cpu_sample=3000):

@@ -1,6 +1,6 @@
 /* Plain C caller of the placement library: the C ABI needs no Python, no torch and no CUDA
  * headers on the caller's side.  It places a handful of pods on a small node table through the
- * host-pointer session (kp_session_snapshot, then kp_session_greedy) and prints the results, one
+ * host-pointer session (kp_session_snapshot, kp_session_decide per pod, then kp_session_greedy) and prints the results, one
  * line per pod; tests/test_c_abi_example_gpu.py compiles it with gcc, runs it on the GPU box and
  * compares the lines with the oracle.
  *
@@ -49,6 +49,14 @@ int main(void)
         if (st != KP_OK) return fail("kp_session_snapshot", st);
         for (int j = 0; j < N_PODS; ++j)
             printf("snapshot strategy=%d pod=%d node=%lld score=%a\n", strategy, j, (long long)idx[j], score[j]);
+        /* the reference's own call shape: one decision per pod over the node list (scheduler.py:598 -> :521-559) */
+        for (int j = 0; j < N_PODS; ++j) {
+            int64_t one_idx;
+            double one_score;
+            st = kp_session_decide(s, &nodes, strategy, KP_FILTER_CAPACITY, req_cpu[j], req_mem[j], &one_idx, &one_score);
+            if (st != KP_OK) return fail("kp_session_decide", st);
+            printf("decide strategy=%d pod=%d node=%lld score=%a\n", strategy, j, (long long)one_idx, one_score);
+        }
         st = kp_session_greedy(s, NULL, &pods, strategy, KP_FILTER_CAPACITY, idx, score, final_pc, final_cu, final_mu);
         if (st != KP_OK) return fail("kp_session_greedy", st);
         for (int j = 0; j < N_PODS; ++j)

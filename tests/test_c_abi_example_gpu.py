@@ -38,6 +38,7 @@ def test_plain_c_caller_matches_the_oracle(tmp_path):
     for sid in range(3):
         oi, os_ = oracle_snapshot(nodes, pods, sid, 1)
         want += [f"snapshot strategy={sid} pod={j} node={oi[j]} score={bits(os_[j])}" for j in range(len(pods))]
+        want += [f"decide strategy={sid} pod={j} node={oi[j]} score={bits(os_[j])}" for j in range(len(pods))]
         gi, gs, gpc, gcu, _ = oracle_greedy(nodes, pods, sid, 1)
         want += [f"greedy strategy={sid} pod={j} node={gi[j]} score={bits(gs[j])}" for j in range(len(pods))]
         want += [f"greedy strategy={sid} final node={i} pod_count={gpc[i]} cpu_usage={bits(gcu[i])}" for i in range(len(nodes))]
