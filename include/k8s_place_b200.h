@@ -137,6 +137,23 @@ int kp_snapshot_place_again(const kp_node_table *nodes, const kp_pod_table *pods
                             int64_t *out_node_idx, double *out_score, void *workspace, size_t workspace_bytes,
                             void *stream);
 
+/* kp_snapshot_place with a first-feasible probe in front of the table scan -- same decisions, bit for bit.
+ * A pod's node is the first entry of the best-first table (score descending, list order within equal scores:
+ * scheduler.py:547 keeps the earlier of equal scores) that it fits.  The probe tries the first `probe_depth`
+ * (at most 64) entries of the pod's strategy table directly and answers the pod on the spot when one fits; only the
+ * remaining pods are scanned against the whole table.  With clusters whose best-scoring nodes have room this turns
+ * pods x nodes pair tests into a few per pod.  It is an OPTION, not the benchmarked kernel: the pairs evaluated are no
+ * longer pods x nodes, so throughput in pairs/s is only "effective" here (kp_snapshot_scanned_pods tells how many
+ * pods still took the full scan).  KP_FILTER_READY ignores the probe.  The workspace must be sized with
+ * kp_snapshot_workspace_bytes(n_nodes, n_pods, 1) (the grouping pass needs the per-pod permutation) and also
+ * serves kp_snapshot_place_again afterwards. */
+int kp_snapshot_place_pruned(const kp_node_table *nodes, const kp_pod_table *pods, int strategy, int filter_mode,
+                             int probe_depth, int64_t *out_node_idx, double *out_score, void *workspace,
+                             size_t workspace_bytes, void *stream);
+/* Pods per strategy (3 counts) that the last kp_snapshot_place_pruned call -- or a call with per-pod strategy ids --
+ * on this workspace left for the full table scan.  Synchronises `stream`. */
+int kp_snapshot_scanned_pods(const void *workspace, void *stream, int64_t *out_scanned);
+
 /* ---- snapshot placement without a workspace, device pointers -------------------------
  * No counterpart in the reference: this entry point exists for hosts that cannot give
  * kp_snapshot_place a workspace because they cannot allocate device memory at the time
@@ -252,6 +269,8 @@ int kp_session_greedy(kp_session *s, const kp_node_table *nodes, const kp_pod_ta
                       int strategy, int filter_mode, int64_t *out_node_idx, double *out_score,
                       int64_t *out_pod_count, double *out_cpu_usage_pct,
                       double *out_mem_usage_pct);
+/* Probe depth of kp_snapshot_place_pruned for this session's kp_session_snapshot calls (0 = off, the default). */
+int kp_session_set_prune_depth(kp_session *s, int probe_depth);
 /* ONE decision for ONE pod -- the reference's own call shape: HuggingFaceClient._fallback_decision(node_metrics,
  * reason) is called once per pending pod (scheduler.py:598 -> :521-559) with the node list it was just handed.
  * `nodes` is host memory (required).  Under KP_FILTER_READY the request arguments and the two allocatable columns

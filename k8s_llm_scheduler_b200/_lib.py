@@ -87,6 +87,10 @@ SYMBOLS = {
                                     c_int, c_void_p, c_void_p]),
     "kp_session_greedy": (c_int, [c_void_p, POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "kp_snapshot_place_pruned": (c_int, [POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int, c_int, c_void_p, c_void_p,
+                                         c_void_p, c_size_t, c_void_p]),
+    "kp_snapshot_scanned_pods": (c_int, [c_void_p, c_void_p, POINTER(c_int64)]),
+    "kp_session_set_prune_depth": (c_int, [c_void_p, c_int]),
     "kp_session_decide": (c_int, [c_void_p, POINTER(KpNodeTable), c_int, c_int, c_int64, c_int64,
                                   POINTER(c_int64), POINTER(c_double)]),
     "kp_session_last_copy_bytes": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),

@@ -113,6 +113,7 @@ struct kp_session {
     // kp_session_decide: answer slot in pinned host memory (the kernel stores, the host polls) and its call counter
     DecideSlot *h_slot = nullptr;
     unsigned long long decide_seq = 0;
+    int prune_depth = 0;                // kp_session_set_prune_depth: first-feasible probe in kp_session_snapshot
 };
 
 namespace {
@@ -336,6 +337,31 @@ int kp_snapshot_place(const kp_node_table *nodes, const kp_pod_table *pods, int 
                                  workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+// kp_snapshot_place with the first-feasible probe in front of the table scan (kp_snapshot.cu, GroupPods): same results,
+// far fewer pairs evaluated when most pods fit one of the best-scoring nodes.
+int kp_snapshot_place_pruned(const kp_node_table *nodes, const kp_pod_table *pods, int strategy, int filter_mode, int probe_depth,
+                             int64_t *out_node_idx, double *out_score, void *workspace, size_t workspace_bytes, void *stream)
+{
+    int st = check_tables(nodes, pods);
+    if (st != KP_OK) return st;
+    if ((st = check_filter(filter_mode)) != KP_OK) return st;
+    if (pods->n_pods > 0 && (!out_node_idx || !out_score)) {
+        set_error("output pointer is NULL");
+        return KP_ERR_INVALID_ARG;
+    }
+    if (probe_depth < 0) { set_error("probe depth %d is negative", probe_depth); return KP_ERR_INVALID_ARG; }
+    PlaceTuning tuning;
+    tuning.prune_depth = probe_depth;
+    return snapshot_place_device(*nodes, *pods, strategy, filter_mode, out_node_idx, out_score, workspace, workspace_bytes,
+                                 (cudaStream_t)stream, tuning);
+}
+
+int kp_snapshot_scanned_pods(const void *workspace, void *stream, int64_t *out_scanned)
+{
+    if (!workspace || !out_scanned) { set_error("workspace / output is NULL"); return KP_ERR_INVALID_ARG; }
+    return snapshot_scanned_pods(workspace, (cudaStream_t)stream, out_scanned);
+}
+
 int kp_snapshot_place_again(const kp_node_table *nodes, const kp_pod_table *pods, int strategy, int filter_mode,
                             int64_t *out_node_idx, double *out_score, void *workspace, size_t workspace_bytes, void *stream)
 {
@@ -553,8 +579,10 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     // (requests: only when every row is read once -- a large table is cut into node segments and
     // each segment would fetch the rows again; results: whenever pods keep their order, every row is
     // written exactly once, by the CTA that finishes the pod chunk)
+    const int prune = filter_mode == KP_FILTER_CAPACITY ? s->prune_depth : 0;
     if (s->direct && b8 && pods->strategy_ids == nullptr) {
-        const bool once = snapshot_single_pass(s->resident_nodes, false);
+        // (with the probe the grouping pass reads every request twice: the columns are copied, not read in place)
+        const bool once = snapshot_single_pass(s->resident_nodes, false) && prune == 0;
         const void *rc = once ? device_alias(pods->req_cpu_milli) : nullptr;
         const void *rm = once ? device_alias(pods->req_mem_bytes) : nullptr;
         if ((s->direct & 1) && rc && rm && pods->n_pods <= s->max_pods) {
@@ -606,6 +634,7 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
             KP_CUDA(cudaStreamWaitEvent(s->stream, s->chunk_ready[c], 0));
             kp_pod_table part{hi - lo, g_rc + lo, g_rm + lo, nullptr};
             PlaceTuning tuning;
+            tuning.prune_depth = prune;
             tuning.plan_sig = &sig;
             tuning.reuse_plan = c > 0 || resident_plan;
             st = snapshot_place_device(dn, part, strategy, filter_mode, d_idx + lo, d_score + lo, s->d_ws, s->ws_bytes, s->stream, tuning);
@@ -614,6 +643,7 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     } else {
         if (!in_place && (st = upload_pods(s, pods, &dp)) != KP_OK) return fail_drained(s, st);
         PlaceTuning tuning;
+        tuning.prune_depth = prune;
         if (in_place) {
             tuning.flow = s->d_flow;
             tuning.flow_window = kFlowWindowCtas;
@@ -633,6 +663,13 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
         s->d2h += 2 * (int64_t)b8;
     }
     KP_CUDA(cudaStreamSynchronize(s->stream));
+    return KP_OK;
+}
+
+int kp_session_set_prune_depth(kp_session *s, int probe_depth)
+{
+    if (!s || probe_depth < 0) { set_error("session is NULL or probe depth negative"); return KP_ERR_INVALID_ARG; }
+    s->prune_depth = probe_depth;
     return KP_OK;
 }
 

@@ -213,6 +213,8 @@ struct PlaceTuning {
     unsigned long long *plan_sig = nullptr;
     bool reuse_plan_forced = false;   // reuse even with per-pod strategies: the plan was built by a plan_only call just before
     bool plan_only = false;           // build the node plan in the workspace and return (no pods are scored)
+    int prune_depth = 0;              // > 0: first-feasible probe of this many best-first nodes before the table scan (kp_snapshot.cu);
+                                      //      the workspace must be sized for per-pod strategies
     // Node-sharded form (kp_exchange.cu): besides index and score the epilogue stores, per pod, the chosen node's
     // GLOBAL rank position gpos_by_pos[strategy * gpos_stride + local rank position] (0xffffffff = no node).
     uint32_t *out_gpos = nullptr;
@@ -229,6 +231,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
                           size_t ws_bytes, cudaStream_t stream, const PlaceTuning &tuning = PlaceTuning());
 size_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod);
 bool snapshot_single_pass(int64_t n_nodes, bool per_pod);
+int snapshot_scanned_pods(const void *workspace, cudaStream_t stream, int64_t *out_scanned);
 int snapshot_place_noalloc(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,
                            int filter_mode, int64_t *out_idx, double *out_score, cudaStream_t stream);
 int greedy_place_device(const kp_node_table &nodes, const kp_pod_table &pods, int strategy,

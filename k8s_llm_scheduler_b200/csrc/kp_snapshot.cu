@@ -44,6 +44,7 @@ constexpr int kArgmaxMaxBlocks = 256;
 constexpr int kSmallPad = 1536;
 constexpr int64_t kSmallMaxPods = 1 << 19;
 constexpr int kMaxChunkPods = 2048;
+constexpr int kProbeMax = 64;                 // first-feasible probe: at most this many best-first nodes per strategy
 
 struct SnapLayout {
     int64_t n, p;
@@ -53,7 +54,7 @@ struct SnapLayout {
     size_t off_header, off_chunk_done, chunk_done_bytes;      // both zeroed by the large-table plan; the per-pod arrays
                                                               // (chunk_done, perm, best) sit BEHIND the plan, whose offsets
                                                               // therefore depend on the node count alone
-    size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_perm;
+    size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_probe, off_perm;
     size_t off_pos, off_kout, off_vout, off_iota, off_sorted, off_flag, off_incl, off_sort_tmp, off_best;   // large tables
     size_t sort_tmp_bytes, total;
 };
@@ -79,6 +80,7 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
     L.off_packed = o;  o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_partial = o; o = align_up(o + (sizeof(uint64_t) + sizeof(uint32_t) * 2) * kMaxStrategies * kArgmaxMaxBlocks);
+    L.off_probe = o;   o = align_up(o + sizeof(double2) * kMaxStrategies * kProbeMax);
     const int64_t nb = big ? n : 0, npb = big ? L.npad : 0;
     L.sort_tmp_bytes = big ? align_up(sort_temp_bytes(n)) : 0;            // per sorted array (they run concurrently)
     L.off_pos = o;      o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
@@ -129,6 +131,16 @@ PlanView snapshot_plan_view(int64_t n_nodes, int64_t n_pods, bool per_pod, void 
                     (int)L.npad};
 }
 
+// pods per strategy that the last grouped call (per-pod strategies, or the first-feasible probe) left for the table scan
+int snapshot_scanned_pods(const void *workspace, cudaStream_t stream, int64_t *out_scanned)
+{
+    SnapHeader h;
+    KP_CUDA(cudaMemcpyAsync(&h, workspace, sizeof(SnapHeader), cudaMemcpyDeviceToHost, stream));
+    KP_CUDA(cudaStreamSynchronize(stream));
+    for (int s = 0; s < kMaxStrategies; ++s) out_scanned[s] = (int64_t)h.group_count[s];
+    return KP_OK;
+}
+
 static NodePtrs node_ptrs(const kp_node_table &t)
 {
     return NodePtrs{(const long long *)t.alloc_cpu_milli, (const long long *)t.alloc_mem_bytes,
@@ -150,16 +162,33 @@ constexpr int kGroupItems = 256 * kGroupPerThread;
 // group, so the placement kernel does not scan the table for them.  Exact: the test is the kernel's own
 // request > threshold compare against the last entry of the sorted threshold arrays (which hold every node's
 // thresholds, NaN parked at +inf -- a table with such a node simply rejects nobody early).
+//
+// First-feasible probe (PlaceTuning::prune_depth > 0).  The best-first table is sorted by (score desc, node index asc),
+// so the node a pod gets is the FIRST table entry it fits (scheduler.py:547: strict '>' keeps the earlier of equal
+// scores).  The grouping pass therefore tries the first prune_depth entries of the pod's strategy table directly --
+// fp64 thresholds of those few nodes, computed by probe_table_kernel -- and a pod that fits one of them is answered on
+// the spot; only the rest enter a strategy group and are scanned against the whole table by the placement kernel.
+// The result is the same bit for bit; the number of pairs EVALUATED drops from pods x nodes to roughly pods x (depth
+// of the first fit), which is why this is an option and not the measured roofline kernel (SURVEY.md section 7,
+// "algorithmic honesty": evaluated and effective pairs are reported separately wherever it is used).
 struct GroupPods {
-    const long long *sid, *req_cpu, *req_mem;
+    const long long *sid, *req_cpu, *req_mem;      // sid == NULL: every pod uses `uniform`
+    int uniform;
     long long n_pods;
     const double *uniq;            // [2][npad] sorted thresholds
     int npad, small_n;             // small_n > 0: arrays keep duplicates and hold small_n entries; else hdr->distinct
     long long *out_idx;
     double *out_score;
     uint32_t *out_gpos;            // node-sharded form (may be NULL)
+    const double2 *probe;          // [3][kProbeMax] (free cpu, free mem) of the best-first nodes; NULL = no probe
+    int probe_depth;
+    const uint32_t *order;         // [3][npad] node index by best-first position
+    const double *score_pos;       // [3][npad]
+    const uint32_t *gpos_by_pos;   // node-sharded form: global position by local position
+    size_t gpos_stride;
 };
 constexpr int kGroupDead = kMaxStrategies;
+constexpr int kGroupDone = kMaxStrategies + 1;       // answered by the probe: `found` holds the table position
 
 __device__ __forceinline__ void group_limits(const GroupPods &g, const SnapHeader *hdr, double &ta_max, double &tb_max)
 {
@@ -168,10 +197,34 @@ __device__ __forceinline__ void group_limits(const GroupPods &g, const SnapHeade
     ta_max = da > 0 ? g.uniq[da - 1] : ninf;
     tb_max = db > 0 ? g.uniq[(size_t)g.npad + db - 1] : ninf;
 }
-__device__ __forceinline__ int group_of(const GroupPods &g, long long j, double ta_max, double tb_max)
+__device__ __forceinline__ int group_of(const GroupPods &g, long long j, double ta_max, double tb_max, int &found)
 {
-    if (req_cores(g.req_cpu[j]) > ta_max || req_gib(g.req_mem[j]) > tb_max) return kGroupDead;
-    return canon_strategy(g.sid[j]);
+    const double rc = req_cores(g.req_cpu[j]), rm = req_gib(g.req_mem[j]);
+    if (rc > ta_max || rm > tb_max) return kGroupDead;
+    const int s = g.sid ? canon_strategy(g.sid[j]) : g.uniform;
+    if (g.probe) {
+        const double2 *pt = g.probe + s * kProbeMax;
+        for (int k = 0; k < g.probe_depth; ++k) {                  // entries past the table hold -inf: nothing fits them
+            const double2 th = __ldg(pt + k);
+            if (rc <= th.x && rm <= th.y) { found = k; return kGroupDone; }
+        }
+    }
+    return s;
+}
+
+// (free cpu, free mem) of the first kProbeMax best-first nodes of every planned strategy, after the node plan.
+__global__ void __launch_bounds__(kMaxStrategies * kProbeMax)
+probe_table_kernel(NodePtrs t, int strat_mask, const SnapHeader *hdr, const uint32_t *__restrict__ order, int npad, double2 *__restrict__ probe)
+{
+    const int s = threadIdx.x / kProbeMax, k = threadIdx.x % kProbeMax;
+    const double ninf = __longlong_as_double((long long)0xfff0000000000000ull);
+    double2 v = make_double2(ninf, ninf);
+    if ((strat_mask & (1 << s)) && k < (int)hdr->nvalid[s]) {
+        const uint32_t n = order[(size_t)s * npad + k];
+        v.x = free_cpu_cores(t.alloc_cpu[n], t.cu[n]);
+        v.y = free_mem_gib(t.alloc_mem[n], t.mu[n]);
+    }
+    probe[threadIdx.x] = v;
 }
 
 __global__ void __launch_bounds__(256)
@@ -189,7 +242,8 @@ group_count_kernel(GroupPods gp, SnapHeader *hdr)
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
         if (j < n_pods) {
-            const int g = group_of(gp, j, ta_max, tb_max);
+            int found;
+            const int g = group_of(gp, j, ta_max, tb_max, found);
 #pragma unroll
             for (int s = 0; s < kMaxStrategies; ++s) c[s] += g == s;
         }
@@ -219,11 +273,18 @@ group_assign_kernel(GroupPods gp, int chunk_pods, SnapHeader *hdr, uint32_t *__r
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
-        g[i] = j < n_pods ? group_of(gp, j, ta_max, tb_max) : -1;
+        int found = 0;
+        g[i] = j < n_pods ? group_of(gp, j, ta_max, tb_max, found) : -1;
         if (g[i] == kGroupDead) {                                 // fits nothing: answered here, never scanned
             gp.out_idx[j] = -1;
             gp.out_score[j] = -1.0;
             if (gp.out_gpos) gp.out_gpos[j] = 0xffffffffu;
+        } else if (g[i] == kGroupDone) {                          // fits one of the first best-first nodes: that node is the answer
+            const int s = gp.sid ? canon_strategy(gp.sid[j]) : gp.uniform;
+            const size_t at = (size_t)s * gp.npad + found;
+            gp.out_idx[j] = (long long)gp.order[at];
+            gp.out_score[j] = gp.score_pos[at];
+            if (gp.out_gpos) gp.out_gpos[j] = gp.gpos_by_pos[(size_t)s * gp.gpos_stride + found];
         }
 #pragma unroll
         for (int s = 0; s < kMaxStrategies; ++s) c[s] += g[i] == s;
@@ -595,7 +656,10 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     unsigned flow_window = tuning.flow_window;
     if (const char *v = getenv("KP_PLACE_RESIDENT")) resident_cap = atoi(v);        // experiments only
     if (const char *v = getenv("KP_FLOW_WINDOW")) flow_window = (unsigned)atoi(v);  // experiments only
-    const bool per_pod = pods.strategy_ids != nullptr;
+    const bool by_sid = pods.strategy_ids != nullptr;
+    // first-feasible probe: pods go through the grouping pass (and its permutation) even with one strategy
+    const int prune_depth = filter_mode == KP_FILTER_CAPACITY ? std::max(0, std::min(tuning.prune_depth, kProbeMax)) : 0;
+    const bool per_pod = by_sid || prune_depth > 0;                // "grouped": the placement kernel reads pods through perm
     const SnapLayout L = make_layout(n, P, per_pod);
     if (!ws || ws_bytes < L.total || (reinterpret_cast<uintptr_t>(ws) & (kAlign - 1))) {
         set_error("snapshot workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", L.total,
@@ -605,7 +669,7 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     unsigned char *w = static_cast<unsigned char *>(ws);
     SnapHeader *hdr = reinterpret_cast<SnapHeader *>(w + L.off_header);
     const int uniform = per_pod ? -1 : canon_strategy(strategy);
-    const int strat_mask = per_pod ? 7 : (1 << uniform);
+    const int strat_mask = by_sid ? 7 : (1 << canon_strategy(strategy));
     const bool capacity = filter_mode == KP_FILTER_CAPACITY;
     const NodePtrs t = node_ptrs(nodes);
 
@@ -689,11 +753,13 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
 
     ProfileEvents &pe = profile_events();
     if (pe.enabled) KP_CUDA(cudaEventRecord(pe.e0, stream));
-    const unsigned long long sig = snapshot_plan_signature(n, P, per_pod, strategy, filter_mode);
+    const unsigned long long sig = snapshot_plan_signature(n, P, by_sid, strategy, filter_mode);
     if (tuning.plan_sig) *tuning.plan_sig = sig;
     if (tuning.reuse_plan && (sig != 0ull || tuning.reuse_plan_forced)) {
         // the workspace holds this table's plan: only the per-call merge counters of the segmented form are reset
         if (L.chunk_done_bytes) KP_CUDA(cudaMemsetAsync(w + L.off_chunk_done, 0, L.chunk_done_bytes, stream));
+        // (and the group counters of the probe's grouping pass, which a fresh plan leaves zeroed)
+        if (per_pod) KP_CUDA(cudaMemsetAsync(hdr->group_count, 0, sizeof(hdr->group_count) + sizeof(hdr->group_cursor), stream));
     } else if (!big) {
         // no sort, no memset, one launch: every node counts its own sorted positions
         const int groups = (int)((n + kCountNodes - 1) / kCountNodes);
@@ -763,8 +829,15 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     // ---- pods ----
     if (per_pod) {
         const int gb = (int)((P + kGroupItems - 1) / kGroupItems);
-        GroupPods gp{(const long long *)pods.strategy_ids, (const long long *)pods.req_cpu_milli, (const long long *)pods.req_mem_bytes, P,
-                     po.uniq, (int)L.npad, big ? 0 : (int)n, (long long *)out_idx, out_score, tuning.out_gpos};
+        double2 *probe = nullptr;
+        if (prune_depth > 0) {
+            probe = reinterpret_cast<double2 *>(w + L.off_probe);
+            probe_table_kernel<<<1, kMaxStrategies * kProbeMax, 0, stream>>>(t, strat_mask, hdr, po.order, (int)L.npad, probe);
+            KP_LAUNCH_CHECK("probe_table_kernel");
+        }
+        GroupPods gp{(const long long *)pods.strategy_ids, (const long long *)pods.req_cpu_milli, (const long long *)pods.req_mem_bytes,
+                     canon_strategy(strategy), P, po.uniq, (int)L.npad, big ? 0 : (int)n, (long long *)out_idx, out_score, tuning.out_gpos,
+                     probe, prune_depth, po.order, po.score_pos, tuning.gpos_by_pos, tuning.gpos_stride};
         group_count_kernel<<<gb, 256, 0, stream>>>(gp, hdr);
         KP_LAUNCH_CHECK("group_count_kernel");
         group_assign_kernel<<<gb, 256, 0, stream>>>(gp, chunk_pods, hdr, perm);

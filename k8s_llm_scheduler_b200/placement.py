@@ -148,6 +148,30 @@ def snapshot_place_again(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Te
     return out[0], out[1]
 
 
+def snapshot_place_pruned(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor, req_mem_bytes: torch.Tensor,
+                          strategy: Union[int, torch.Tensor] = 0, filter_mode: int = FILTER_CAPACITY, probe_depth: int = 32,
+                          workspace: Optional[torch.Tensor] = None, out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+                          scanned: bool = False):
+    """``snapshot_place`` with the first-feasible probe (kp_snapshot_place_pruned): the same (node_idx, score), but a
+    pod that fits one of the first ``probe_depth`` best-first nodes of its strategy is answered without a table scan.
+    ``scanned=True`` also returns how many pods per strategy still took the full scan (synchronises)."""
+    lib = _lib.load()
+    nst, device, n = _node_struct(nodes)
+    pst, p, strat, per_pod = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
+    ws = _workspace(snapshot_workspace_bytes(n, p, True), device, workspace)
+    if out is None:
+        out = (torch.empty(p, dtype=torch.int64, device=device), torch.empty(p, dtype=torch.float64, device=device))
+    with torch.cuda.device(device):
+        stream = c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        check(lib.kp_snapshot_place_pruned(byref(nst), byref(pst), strat, int(filter_mode), int(probe_depth), out[0].data_ptr(),
+                                           out[1].data_ptr(), ws.data_ptr(), ws.numel(), stream), "kp_snapshot_place_pruned")
+        if scanned:
+            cnt = (c_int64 * 3)()
+            check(lib.kp_snapshot_scanned_pods(ws.data_ptr(), stream, cnt), "kp_snapshot_scanned_pods")
+            return out[0], out[1], [int(c) for c in cnt]
+    return out[0], out[1]
+
+
 def greedy_place(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.Tensor,
                  req_mem_bytes: torch.Tensor, strategy: Union[int, torch.Tensor] = 0,
                  filter_mode: int = FILTER_CAPACITY, workspace: Optional[torch.Tensor] = None):
@@ -245,6 +269,10 @@ class Session:
             keep.append(r3)
             st.strategy_ids = p3
         return st, keep
+
+    def set_prune_depth(self, probe_depth: int) -> None:
+        """First-feasible probe for this session's snapshot() calls (kp_session_set_prune_depth; 0 = off)."""
+        check(self._lib.kp_session_set_prune_depth(self._h, int(probe_depth)), "kp_session_set_prune_depth")
 
     def set_nodes(self, nodes) -> None:
         st, keep = self._node_struct(nodes)
