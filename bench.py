@@ -518,6 +518,12 @@ def run_ours(args):
     e2e_value = pairs_per_step / float(e2e_s.item())
     e2e_idx = ho[0].numpy().copy() if snapshot else res["e2e"][0]
     sess.close()
+    first_fit = None
+    if world == 1 and snapshot and meta["filter"] == 1 and args.extra:
+        try:
+            first_fit = first_feasible_report(torch, placement, local, dev, nodes, pods, meta, dn, rc, rm, strat, hn, hp, ho, out[0], n_el)
+        except Exception as ex:  # noqa: BLE001
+            first_fit = {"error": repr(ex)}
 
     if rank != 0:
         if world > 1:
@@ -573,6 +579,8 @@ def run_ours(args):
     }
     if not snapshot:
         out_line["greedy"] = greedy_report(torch, placement, dn, rc, rm, strat, meta, res["out"], ws)
+    if first_fit is not None:
+        out_line["first_feasible_option"] = first_fit
     if world == 1 and args.extra:
         out_line["extra"] = run_extras(args, torch, placement, lib, dev, peak_meas)
     print(json.dumps(out_line))
@@ -632,6 +640,47 @@ def greedy_report(torch, placement, dn, rc, rm, strat, meta, out, ws):
         rep.update({"ms_to_depletion": ms, "pods_decided_to_depletion": k,
                     "placed_per_sec": placed / (ms * 1e-3), "ns_per_placed_pod": ms * 1e6 / placed})
     return rep
+
+
+def first_feasible_report(torch, placement, local, dev, nodes, pods, meta, dn, rc, rm, strat, hn, hp, ho, full_scan_idx, n_el, depth=32, steps=5):
+    """The same workload through the OPTIONAL first-feasible probe (kp_snapshot_place_pruned / kp_session_set_prune_depth):
+    identical answers, but most pairs are never evaluated, so its pairs/s are 'effective' only and it is neither the
+    headline nor a roofline figure ("algorithmic honesty")."""
+    n, p = len(nodes), len(pods)
+    ws = torch.empty(placement.snapshot_workspace_bytes(n, p, True), dtype=torch.uint8, device=dev)
+    out = (torch.empty(p, dtype=torch.int64, device=dev), torch.empty(p, dtype=torch.float64, device=dev))
+    for _ in range(3):
+        placement.snapshot_place_pruned(dn, rc, rm, strat, 1, depth, workspace=ws, out=out)
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        placement.snapshot_place_pruned(dn, rc, rm, strat, 1, depth, workspace=ws, out=out)
+        b.record()
+        torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    left = placement.snapshot_place_pruned(dn, rc, rm, strat, 1, depth, workspace=ws, out=out, scanned=True)[2]
+    same = bool(torch.equal(out[0], full_scan_idx))
+    ok_dev, k = c_oracle_check(nodes, pods, meta, out[0][:4096].cpu().numpy())
+    t = statistics.median(ms) * 1e-3
+    with placement.Session(local, max_nodes=n, max_pods=p) as sess:
+        sess.set_prune_depth(depth)
+        for _ in range(2):
+            sess.snapshot(hn, hp, meta["strategy"], 1, out=ho)
+        e2e = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            sess.snapshot(hn, hp, meta["strategy"], 1, out=ho)
+            e2e.append(time.perf_counter() - t0)
+        ok_e2e, _ = c_oracle_check(nodes, pods, meta, ho[0].numpy())
+    te = statistics.median(e2e)
+    return {"api": "kp_snapshot_place_pruned / kp_session_set_prune_depth (off by default)", "probe_depth": depth,
+            "ms_per_step": t * 1e3, "pods_per_sec": p / t, "pods_left_for_the_table_scan": int(sum(left)),
+            "pairs_per_sec_effective": p * n_el / t, "pairs_per_sec_evaluated_upper_bound": (p * depth + sum(left) * n_el) / t,
+            "same_answers_as_full_scan": same, "parity_vs_cpu_sample": bool(ok_dev and ok_e2e), "c_oracle_pods_checked": k,
+            "e2e_ms_per_step": te * 1e3, "e2e_pods_per_sec": p / te, "e2e_pairs_per_sec_effective": p * n_el / te,
+            "note": "pairs are skipped, not evaluated: not comparable with `value` or the roofline"}
 
 
 def session_probe(torch, placement, dev, nodes, pods, meta, steps=200):

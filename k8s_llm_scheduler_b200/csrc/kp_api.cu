@@ -109,7 +109,7 @@ struct kp_session {
     unsigned long long plan_sig = 0;
     // large uploads are pipelined: pod columns go up in chunks on copy_stream while earlier chunks are scored
     cudaStream_t copy_stream = nullptr;
-    cudaEvent_t chunk_ready[2] = {nullptr};
+    cudaEvent_t chunk_ready[8] = {nullptr};
     // kp_session_decide: answer slot in pinned host memory (the kernel stores, the host polls) and its call counter
     DecideSlot *h_slot = nullptr;
     unsigned long long decide_seq = 0;
@@ -118,7 +118,7 @@ struct kp_session {
 
 namespace {
 
-constexpr int kPipeMaxChunks = 2;
+constexpr int kPipeMaxChunks = 8;
 constexpr int64_t kPipeChunkMinPodsDefault = 1 << 19;   // below two pieces of this size one copy + one launch is as good
 constexpr unsigned kFlowWindowCtas = 64;      // request rows of this many CTAs in flight on the host link
 constexpr size_t kStageMaxBytes = 1u << 20;   // node tables up to ~18 k rows travel as one copy
@@ -608,9 +608,15 @@ int kp_session_snapshot(kp_session *s, const kp_node_table *nodes, const kp_pod_
     const int64_t P = pods->n_pods;
     const bool pipelined = !in_place && pods->strategy_ids == nullptr && filter_mode == KP_FILTER_CAPACITY && P <= s->max_pods &&
                            P >= 2 * kPipeChunkMinPods;
-    const int nchunks = pipelined ? 2 : 0;
-    int64_t cut[3] = {0, 0, P};
-    if (pipelined) {
+    int nchunks = pipelined ? 2 : 0;
+    int64_t cut[kPipeMaxChunks + 1] = {0, 0, P};
+    if (pipelined && prune > 0) {
+        // with the probe a pod costs about as much to place as to copy: equal pieces, several of them, so that piece
+        // c's answers travel to the host (written in place by the kernels) while piece c + 1 travels to the device
+        nchunks = (int)std::min<int64_t>(kPipeMaxChunks, P / kPipeChunkMinPods);
+        for (int c = 0; c <= nchunks; ++c) cut[c] = (P * c / nchunks) & ~(int64_t)255;
+        cut[nchunks] = P;
+    } else if (pipelined) {
         const double f = std::min(0.5, std::max(1.0 / 16, 3500.0 / (3500.0 + (double)dn.n_nodes)));
         cut[1] = std::max<int64_t>(kPipeChunkMinPods, (int64_t)(f * (double)P));
     }

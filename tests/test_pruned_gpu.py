@@ -142,3 +142,33 @@ def test_plan_left_by_a_pruned_call_serves_place_again_and_the_session_option():
             oi, os_ = oracle_snapshot(nodes, more, 0, FILTER_CAPACITY)
             assert_same_idx(hi, oi)
             assert_same_f64(hs, os_)
+
+
+@pytest.mark.parametrize("n,pinned", [(3000, True), (9000, False)])
+def test_session_probe_with_pods_uploaded_in_pieces(n, pinned):
+    """Two million pods through the session with the probe on: the columns go up in equal pieces, every piece is
+    grouped / probed / scanned against the first piece's plan, answers written as the pieces finish."""
+    import torch
+    from k8s_llm_scheduler_b200.placement import Session
+    from tests.helpers import device_snapshot
+    p = 2_100_003
+    nodes, pods = scattered_cluster(n, p, seed=90 + n, tight=0.9)
+    uniform = PodTable.from_columns(pods.req_cpu_milli, pods.req_mem_bytes)
+    want = device_snapshot(nodes, uniform, 0, FILTER_CAPACITY)               # the full scan (oracle-checked below on a sample)
+    head = PodTable.from_columns(pods.req_cpu_milli[:30_000], pods.req_mem_bytes[:30_000])
+    oi, _ = oracle_snapshot(nodes, head, 0, FILTER_CAPACITY)
+    assert_same_idx(want[0][:30_000], oi)
+    with Session(0, max_nodes=n, max_pods=p) as s:
+        s.set_prune_depth(8)
+        if pinned:
+            hp = (torch.as_tensor(pods.req_cpu_milli).pin_memory(), torch.as_tensor(pods.req_mem_bytes).pin_memory(), None)
+            out = (torch.empty(p, dtype=torch.int64).pin_memory(), torch.empty(p, dtype=torch.float64).pin_memory())
+            for _ in range(2):
+                out[0].fill_(-7)
+                s.snapshot(nodes, hp, 0, FILTER_CAPACITY, out=out)
+                assert_same_idx(out[0].numpy(), want[0])
+                assert_same_f64(out[1].numpy(), want[1])
+        else:
+            gi, gs = s.snapshot(nodes, uniform, 0, FILTER_CAPACITY)
+            assert_same_idx(gi, want[0])
+            assert_same_f64(gs, want[1])
