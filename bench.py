@@ -820,6 +820,34 @@ def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, 
     h2d = sum(v.numel() * v.element_size() for v in hn.values()) + sum(h.numel() * h.element_size() for h in hp)
     d2h = 16 * (phi - plo)
     e2e_idx = ho[0].numpy().copy()
+
+    # the OPTIONAL first-feasible probe in every rank's scan (kp_exchange_set_prune_depth): same answers, pairs skipped
+    first_fit = None
+    if args.extra:
+        full_idx = out[0].clone()
+        placer.set_prune_depth(32)
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        barrier()
+        evs = []
+        for _ in range(args.steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); step(); b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        barrier()
+        placer.check()
+        tp = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+        same = torch.tensor([int(torch.equal(out[0], full_idx))], device=dev)
+        if world > 1:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        placer.set_prune_depth(0)
+        t_ff = float(tp.item()) / args.steps * 1e-3
+        first_fit = {"api": "kp_exchange_set_prune_depth(32) (off by default)", "ms_per_step": t_ff * 1e3, "pods_per_sec": p / t_ff,
+                     "pairs_per_sec_effective": float(p) * n_el / t_ff, "same_answers_as_full_scan_all_ranks": bool(same.item()),
+                     "note": "pairs are skipped, not evaluated: not comparable with `value` or the roofline"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -861,6 +889,8 @@ def run_node_sharded(args, torch, dist, placement, lib, dev, nodes, pods, meta, 
         "parity_detail": {"c_oracle_pods_checked": k_chk, "device_pass": ok_dev, "host_api_pass": ok_e2e,
                           "checked": "first pods of rank 0's result shard against the oracle on the WHOLE node list"},
     }
+    if first_fit is not None:
+        out_line["first_feasible_option"] = first_fit
     if world == 1 and not args.no_cpu:
         cb = cpu_port_run(nodes, pods, meta, args.cpu_seconds)
         out_line["cpu_baseline"] = {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port",

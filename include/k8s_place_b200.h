@@ -205,6 +205,9 @@ int kp_exchange_connect(kp_exchange *ex, const unsigned char *handles /* world x
 int kp_exchange_connect_local(kp_exchange *ex, kp_exchange *const *all /* world exchanges, rank order */);
 void kp_exchange_destroy(kp_exchange *ex);
 int kp_exchange_error(kp_exchange *ex, int *out_error);
+/* First-feasible probe (see kp_snapshot_place_pruned) for this rank's scan of its node slice in kp_ns_place; 0 = off,
+ * the default.  The workspace must then be sized with per_pod_strategy = 1.  Ranks may differ; the reduce is unchanged. */
+int kp_exchange_set_prune_depth(kp_exchange *ex, int probe_depth);
 int kp_ns_keys(kp_exchange *ex, const kp_node_table *local_nodes, int64_t node_offset, const kp_pod_table *pods,
                int strategy, int filter_mode, void *workspace, size_t workspace_bytes, void *stream);
 int kp_ns_place(kp_exchange *ex, const kp_node_table *local_nodes, const kp_pod_table *pods, int strategy,

@@ -69,6 +69,7 @@ SYMBOLS = {
     "kp_exchange_connect_local": (c_int, [c_void_p, POINTER(c_void_p)]),
     "kp_exchange_destroy": (None, [c_void_p]),
     "kp_exchange_error": (c_int, [c_void_p, POINTER(c_int)]),
+    "kp_exchange_set_prune_depth": (c_int, [c_void_p, c_int]),
     "kp_ns_keys": (c_int, [c_void_p, POINTER(KpNodeTable), c_int64, POINTER(KpPodTable), c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "kp_ns_place": (c_int, [c_void_p, POINTER(KpNodeTable), POINTER(KpPodTable), c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "kp_ns_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -82,6 +82,7 @@ struct kp_exchange {
     bool connected = false;
     uint32_t epoch = 0;
     int64_t n_pods = 0;                 // of the call in flight
+    int prune_depth = 0;                // kp_exchange_set_prune_depth: first-feasible probe in kp_ns_place
     ExLayout L{};
 };
 
@@ -392,6 +393,13 @@ void kp_exchange_destroy(kp_exchange *ex)
     delete ex;
 }
 
+int kp_exchange_set_prune_depth(kp_exchange *ex, int probe_depth)
+{
+    if (!ex || probe_depth < 0) { set_error("kp_exchange_set_prune_depth: NULL exchange or negative depth"); return KP_ERR_INVALID_ARG; }
+    ex->prune_depth = probe_depth;
+    return KP_OK;
+}
+
 int kp_exchange_error(kp_exchange *ex, int *out_error)
 {
     if (!ex || !out_error) { set_error("kp_exchange_error: NULL argument"); return KP_ERR_INVALID_ARG; }
@@ -474,6 +482,7 @@ int kp_ns_place(kp_exchange *ex, const kp_node_table *nodes, const kp_pod_table 
     tuning.gpos_by_pos = reinterpret_cast<const uint32_t *>(ex->base + ex->L.off_gpos);
     tuning.gpos_stride = ex->max_local;
     tuning.reuse_plan = tuning.reuse_plan_forced = true;      // kp_ns_keys built it in this workspace a moment ago
+    tuning.prune_depth = ex->prune_depth;                     // (optional) local first fit by probe; the reduce is unchanged
     if (pods->n_pods > 0 && n == 0)                      // an empty slice offers no candidate
         KP_CUDA(cudaMemsetAsync(tuning.out_gpos, 0xff, sizeof(uint32_t) * (size_t)pods->n_pods, sq));
     if (pods->n_pods > 0 && n > 0) {

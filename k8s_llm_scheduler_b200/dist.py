@@ -151,6 +151,7 @@ class NodeShardedPlacer:
                                                  ctypes.byref(self._h)), "kp_exchange_create")
         self._ws: Optional[torch.Tensor] = None
         self._n_pods = 0
+        self._prune = 0
         if connect and self.world > 1:
             buf = (ctypes.c_ubyte * 64)()
             self._check(self._lib.kp_exchange_handle(self._h, buf), "kp_exchange_handle")
@@ -185,10 +186,15 @@ class NodeShardedPlacer:
         from . import placement
         nst, device, n = placement._node_struct(local_nodes)
         pst, p, strat, per_pod = placement._pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)
-        need = placement.snapshot_workspace_bytes(n, p, per_pod)
+        need = placement.snapshot_workspace_bytes(n, p, per_pod or self._prune > 0)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=device)
         return nst, pst, n, p, strat, per_pod
+
+    def set_prune_depth(self, probe_depth: int) -> None:
+        """Optional first-feasible probe for this rank's scan (kp_exchange_set_prune_depth; 0 = off, the default)."""
+        self._check(self._lib.kp_exchange_set_prune_depth(self._h, int(probe_depth)), "kp_exchange_set_prune_depth")
+        self._prune = int(probe_depth)
 
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)

@@ -13,13 +13,15 @@ from tests.helpers import assert_same_f64, assert_same_idx, oracle_snapshot
 pytestmark = pytest.mark.gpu
 
 
-def run_emulated(nodes: NodeTable, pods: PodTable, world: int, strategy, per_pod: bool, rounds: int = 1, cuts=None):
+def run_emulated(nodes: NodeTable, pods: PodTable, world: int, strategy, per_pod: bool, rounds: int = 1, cuts=None, prune=0):
     import torch
     from k8s_llm_scheduler_b200 import dist as kd, placement
     dev = torch.device("cuda:0")
     n, p = len(nodes), len(pods)
     cuts = cuts or [kd.shard_bounds(n, r, world) for r in range(world)]
     group = kd.NodeShardedPlacer.local_group([dev] * world, max_pods=p, max_local_nodes=max(1, max(b - a for a, b in cuts)))
+    for g in group:
+        g.set_prune_depth(prune if g.rank % 2 == 0 else 0)     # the probe is a per-rank choice: mix ranks with and without
     full = placement.nodes_to_device(nodes, dev)
     slices = [kd.slice_nodes(full, a, b) for a, b in cuts]
     rc, rm = torch.as_tensor(pods.req_cpu_milli).to(dev), torch.as_tensor(pods.req_mem_bytes).to(dev)
@@ -54,6 +56,23 @@ def test_emulated_ranks_match_the_oracle(n, p, world):
     oi, os_ = oracle_snapshot(nodes, pods, 0, 1, per_pod=True)
     assert_same_idx(gi, oi, f"n={n} world={world} per-pod strategies")
     assert_same_f64(gs, os_)
+
+
+@pytest.mark.parametrize("n,p,world", [(2500, 20_001, 2), (20_000, 30_000, 8), (9000, 40_000, 3)])
+def test_emulated_ranks_with_the_first_feasible_probe(n, p, world):
+    """kp_exchange_set_prune_depth: ranks that find their local winner by the probe and ranks that scan, same answer.
+    Score and capacity independent, so the local first fit lies anywhere in a slice."""
+    rng = np.random.default_rng(n + world)
+    nodes = NodeTable.from_columns(
+        alloc_cpu_milli=rng.integers(500, 64_000, n), alloc_mem_bytes=rng.integers(1 << 28, 256 << 30, n),
+        pod_count=rng.integers(0, 110, n), max_pods=rng.choice([0, 30, 110, 250], n), ready=(rng.random(n) > 0.03).astype(np.uint8),
+        cpu_usage_pct=np.round(rng.random(n) * 100, 2), mem_usage_pct=np.round(rng.random(n) * 100, 2))
+    pods = PodTable.from_columns(rng.integers(1, 60_000, p), rng.integers(1, 240 << 30, p), rng.integers(0, 4, p))
+    for sid, per_pod in ((0, False), (2, False), (0, True)):
+        gi, gs = run_emulated(nodes, pods, world, sid, per_pod, rounds=2, prune=8)
+        oi, os_ = oracle_snapshot(nodes, pods, sid, 1, per_pod=per_pod)
+        assert_same_idx(gi, oi, f"n={n} world={world} strategy={sid} per_pod={per_pod}")
+        assert_same_f64(gs, os_)
 
 
 def test_ties_across_ranks_go_to_the_first_node_in_list_order():

@@ -17,6 +17,11 @@ dev = torch.device("cuda:0")
 lib = _lib.load()
 cuts = [kd.shard_bounds(n, r, world) for r in range(world)]
 group = kd.NodeShardedPlacer.local_group([dev] * world, max_pods=p, max_local_nodes=max(b - a for a, b in cuts))
+import os  # noqa: E402
+if os.environ.get("NS_PRUNE"):                      # optional first-feasible probe in every rank's scan
+    for g in group:
+        g.set_prune_depth(int(os.environ["NS_PRUNE"]))
+    print(f"(first-feasible probe, depth {os.environ['NS_PRUNE']})")
 full = placement.nodes_to_device(nodes, dev)
 slices = [kd.slice_nodes(full, a, b) for a, b in cuts]
 rc, rm = torch.as_tensor(pods.req_cpu_milli).to(dev), torch.as_tensor(pods.req_mem_bytes).to(dev)
