@@ -45,6 +45,7 @@ constexpr int kSmallPad = 1536;
 constexpr int64_t kSmallMaxPods = 1 << 19;
 constexpr int kMaxChunkPods = 2048;
 constexpr int kProbeMax = 64;                 // first-feasible probe: at most this many best-first nodes per strategy
+constexpr size_t kProbeIntBytes = sizeof(long long) * (2 + 2 * 3 * kProbeMax);     // struct ProbeInt (defined with the grouping pass)
 
 struct SnapLayout {
     int64_t n, p;
@@ -54,7 +55,7 @@ struct SnapLayout {
     size_t off_header, off_chunk_done, chunk_done_bytes;      // both zeroed by the large-table plan; the per-pod arrays
                                                               // (chunk_done, perm, best) sit BEHIND the plan, whose offsets
                                                               // therefore depend on the node count alone
-    size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_probe, off_perm;
+    size_t off_keys, off_score, off_score_pos, off_uniq, off_order, off_ab, off_packed, off_partial, off_probe, off_probe_int, off_perm;
     size_t off_pos, off_kout, off_vout, off_iota, off_sorted, off_flag, off_incl, off_sort_tmp, off_best;   // large tables
     size_t sort_tmp_bytes, total;
 };
@@ -80,7 +81,8 @@ static SnapLayout make_layout(int64_t n, int64_t p, bool per_pod)
     L.off_ab = o;      o = align_up(o + sizeof(uint2) * kMaxStrategies * L.npad);
     L.off_packed = o;  o = align_up(o + sizeof(uint32_t) * kMaxStrategies * L.npad);
     L.off_partial = o; o = align_up(o + (sizeof(uint64_t) + sizeof(uint32_t) * 2) * kMaxStrategies * kArgmaxMaxBlocks);
-    L.off_probe = o;   o = align_up(o + sizeof(double2) * kMaxStrategies * kProbeMax);
+    L.off_probe = o;   o = align_up(o + sizeof(double2) * (kMaxStrategies * kProbeMax + 1));      // + the largest thresholds
+    L.off_probe_int = o; o = align_up(o + kProbeIntBytes);
     const int64_t nb = big ? n : 0, npb = big ? L.npad : 0;
     L.sort_tmp_bytes = big ? align_up(sort_temp_bytes(n)) : 0;            // per sorted array (they run concurrently)
     L.off_pos = o;      o = align_up(o + sizeof(uint32_t) * kKeyArrays * nb);
@@ -171,6 +173,43 @@ constexpr int kGroupItems = 256 * kGroupPerThread;
 // The result is the same bit for bit; the number of pairs EVALUATED drops from pods x nodes to roughly pods x (depth
 // of the first fit), which is why this is an option and not the measured roofline kernel (SURVEY.md section 7,
 // "algorithmic honesty": evaluated and effective pairs are reported separately wherever it is used).
+// Integer images of the fp64 thresholds the grouping pass compares against.  A request is an int64 (milli-cores,
+// bytes) and the reference compares fl(milli / 1000.0) resp. bytes * 2^-30 with a node's free capacity T; both maps are
+// monotone, so "request fits" is "request <= M" for M = the LARGEST integer whose image is <= T.  M is found once per
+// threshold (limit_cpu / limit_mem below, exact: the candidates around floor(T * 1000) are tested with the very
+// division the pod side would do), and the per-pod work of the pass is integer compares: no fp64 division, no
+// conversions.  The images cover requests with |x| < 2^53 (where (double)x is exact -- the ABI's stated range); a
+// request outside takes the fp64 compares.
+constexpr long long kExactMax = (1ll << 53) - 1;
+struct ProbeInt {
+    long long dead_cpu, dead_mem;                       // a request above either fits no node of the table
+    long long cpu[kMaxStrategies][kProbeMax], mem[kMaxStrategies][kProbeMax];
+};
+
+static_assert(sizeof(ProbeInt) == kProbeIntBytes, "workspace layout reserves exactly one ProbeInt");
+
+// largest m in [-kExactMax, kExactMax] with fl(m / 1000.0) <= T  (-kExactMax - 1: none).  No NaN reaches this.
+__device__ long long limit_cpu(double T)
+{
+    if (req_cores(kExactMax) <= T) return kExactMax;
+    if (!(req_cores(-kExactMax) <= T)) return -kExactMax - 1;
+    // m / 1000 <= T  <=>  m <= 1000 T in real arithmetic; the rounded division admits at most one more m, the rounded
+    // product moves the floor by at most one: the answer is within [g - 1, g + 2]
+    const double g = floor(__dmul_rn(T, 1000.0));
+    long long c = (long long)g + 2;
+    c = c > kExactMax ? kExactMax : c;
+    while (c > -kExactMax && req_cores(c) > T) --c;
+    return c;
+}
+// largest b in [-kExactMax, kExactMax] with b * 2^-30 <= T: the scaling is exact, so b <= floor(T * 2^30)
+__device__ long long limit_mem(double T)
+{
+    const double g = floor(__dmul_rn(T, 1073741824.0));            // exact unless it overflows to +-inf
+    if (g >= (double)kExactMax) return kExactMax;
+    if (g < -(double)kExactMax) return -kExactMax - 1;
+    return (long long)g;
+}
+
 struct GroupPods {
     const long long *sid, *req_cpu, *req_mem;      // sid == NULL: every pod uses `uniform`
     int uniform;
@@ -180,8 +219,9 @@ struct GroupPods {
     long long *out_idx;
     double *out_score;
     uint32_t *out_gpos;            // node-sharded form (may be NULL)
-    const double2 *probe;          // [3][kProbeMax] (free cpu, free mem) of the best-first nodes; NULL = no probe
-    int probe_depth;
+    const double2 *probe;          // [3][kProbeMax] (free cpu, free mem) of the best-first nodes
+    const ProbeInt *lim;           // integer images of the probe table and of the largest thresholds
+    int probe_depth;               // 0 = no probe
     const uint32_t *order;         // [3][npad] node index by best-first position
     const double *score_pos;       // [3][npad]
     const uint32_t *gpos_by_pos;   // node-sharded form: global position by local position
@@ -197,34 +237,72 @@ __device__ __forceinline__ void group_limits(const GroupPods &g, const SnapHeade
     ta_max = da > 0 ? g.uniq[da - 1] : ninf;
     tb_max = db > 0 ? g.uniq[(size_t)g.npad + db - 1] : ninf;
 }
-__device__ __forceinline__ int group_of(const GroupPods &g, long long j, double ta_max, double tb_max, int &found)
+// qc / qm: the pod's requests as they lie in the table; sid: its canonical strategy
+__device__ __forceinline__ int group_of(const GroupPods &g, long long qc, long long qm, int s, int &found)
 {
-    const double rc = req_cores(g.req_cpu[j]), rm = req_gib(g.req_mem[j]);
+    const ProbeInt *lim = g.lim;
+    const bool exact = (unsigned long long)qc + (unsigned long long)kExactMax <= 2ull * kExactMax &&
+                       (unsigned long long)qm + (unsigned long long)kExactMax <= 2ull * kExactMax;
+    if (exact) {
+        if (qc > __ldg(&lim->dead_cpu) || qm > __ldg(&lim->dead_mem)) return kGroupDead;
+        for (int k = 0; k < g.probe_depth; ++k)                    // entries past the table fit nothing
+            if (qc <= __ldg(&lim->cpu[s][k]) && qm <= __ldg(&lim->mem[s][k])) { found = k; return kGroupDone; }
+        return s;
+    }
+    // a request beyond 2^53: (double)x rounds, the integer images do not apply -- the fp64 compares themselves
+    double ta_max, tb_max;
+    {
+        const double2 d = __ldg(g.probe + kMaxStrategies * kProbeMax);
+        ta_max = d.x;
+        tb_max = d.y;
+    }
+    const double rc = req_cores(qc), rm = req_gib(qm);
     if (rc > ta_max || rm > tb_max) return kGroupDead;
-    const int s = g.sid ? canon_strategy(g.sid[j]) : g.uniform;
-    if (g.probe) {
-        const double2 *pt = g.probe + s * kProbeMax;
-        for (int k = 0; k < g.probe_depth; ++k) {                  // entries past the table hold -inf: nothing fits them
-            const double2 th = __ldg(pt + k);
-            if (rc <= th.x && rm <= th.y) { found = k; return kGroupDone; }
-        }
+    const double2 *pt = g.probe + s * kProbeMax;
+    for (int k = 0; k < g.probe_depth; ++k) {
+        const double2 th = __ldg(pt + k);
+        if (rc <= th.x && rm <= th.y) { found = k; return kGroupDone; }
     }
     return s;
 }
 
-// (free cpu, free mem) of the first kProbeMax best-first nodes of every planned strategy, after the node plan.
+// After the node plan, one CTA: (free cpu, free mem) of the first kProbeMax best-first nodes of every planned strategy,
+// the largest thresholds of the table (entry [3][0] of the fp64 table), and the integer images of all of them.
 __global__ void __launch_bounds__(kMaxStrategies * kProbeMax)
-probe_table_kernel(NodePtrs t, int strat_mask, const SnapHeader *hdr, const uint32_t *__restrict__ order, int npad, double2 *__restrict__ probe)
+probe_table_kernel(NodePtrs t, int strat_mask, const SnapHeader *hdr, GroupPods g, double2 *__restrict__ probe, ProbeInt *__restrict__ lim)
 {
     const int s = threadIdx.x / kProbeMax, k = threadIdx.x % kProbeMax;
     const double ninf = __longlong_as_double((long long)0xfff0000000000000ull);
     double2 v = make_double2(ninf, ninf);
-    if ((strat_mask & (1 << s)) && k < (int)hdr->nvalid[s]) {
-        const uint32_t n = order[(size_t)s * npad + k];
+    if ((strat_mask & (1 << s)) && k < g.probe_depth && k < (int)hdr->nvalid[s]) {
+        const uint32_t n = g.order[(size_t)s * g.npad + k];
         v.x = free_cpu_cores(t.alloc_cpu[n], t.cu[n]);
         v.y = free_mem_gib(t.alloc_mem[n], t.mu[n]);
     }
     probe[threadIdx.x] = v;
+    lim->cpu[s][k] = limit_cpu(v.x);
+    lim->mem[s][k] = limit_mem(v.y);
+    if (threadIdx.x == 0) {
+        double ta_max, tb_max;
+        group_limits(g, hdr, ta_max, tb_max);
+        probe[kMaxStrategies * kProbeMax] = make_double2(ta_max, tb_max);
+        lim->dead_cpu = limit_cpu(ta_max);
+        lim->dead_mem = limit_mem(tb_max);
+    }
+}
+
+// one block's pods, loaded before anything is computed (sixteen to twenty-four independent loads per thread in flight)
+struct GroupRows { long long qc[kGroupPerThread], qm[kGroupPerThread]; int s[kGroupPerThread]; };
+__device__ __forceinline__ void group_load(const GroupPods &gp, long long base, GroupRows &r)
+{
+#pragma unroll
+    for (int i = 0; i < kGroupPerThread; ++i) {
+        const long long j = base + i * 256 + threadIdx.x;
+        const bool in = j < gp.n_pods;
+        r.qc[i] = in ? gp.req_cpu[j] : 0;
+        r.qm[i] = in ? gp.req_mem[j] : 0;
+        r.s[i] = in ? (gp.sid ? canon_strategy(gp.sid[j]) : gp.uniform) : -1;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -233,17 +311,14 @@ group_count_kernel(GroupPods gp, SnapHeader *hdr)
     __shared__ unsigned s_cnt[kMaxStrategies];
     if (threadIdx.x < kMaxStrategies) s_cnt[threadIdx.x] = 0u;
     __syncthreads();
-    const long long n_pods = gp.n_pods;
-    double ta_max, tb_max;
-    group_limits(gp, hdr, ta_max, tb_max);
-    const long long base = (long long)blockIdx.x * kGroupItems;
+    GroupRows r;
+    group_load(gp, (long long)blockIdx.x * kGroupItems, r);
     unsigned c[kMaxStrategies] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
-        const long long j = base + i * 256 + threadIdx.x;
-        if (j < n_pods) {
+        if (r.s[i] >= 0) {
             int found;
-            const int g = group_of(gp, j, ta_max, tb_max, found);
+            const int g = group_of(gp, r.qc[i], r.qm[i], r.s[i], found);
 #pragma unroll
             for (int s = 0; s < kMaxStrategies; ++s) c[s] += g == s;
         }
@@ -259,28 +334,27 @@ group_count_kernel(GroupPods gp, SnapHeader *hdr)
 __global__ void __launch_bounds__(256)
 group_assign_kernel(GroupPods gp, int chunk_pods, SnapHeader *hdr, uint32_t *__restrict__ perm)
 {
-    const long long n_pods = gp.n_pods;
-    double ta_max, tb_max;
-    group_limits(gp, hdr, ta_max, tb_max);
     __shared__ unsigned s_cnt[kMaxStrategies], s_cur[kMaxStrategies];
     __shared__ long long s_base[kMaxStrategies];
     if (threadIdx.x < kMaxStrategies) { s_cnt[threadIdx.x] = 0u; s_cur[threadIdx.x] = 0u; }
     __syncthreads();
     const long long base = (long long)blockIdx.x * kGroupItems;
     const int lane = threadIdx.x & 31;
+    GroupRows r;
+    group_load(gp, base, r);
     int g[kGroupPerThread];
     unsigned c[kMaxStrategies] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
         int found = 0;
-        g[i] = j < n_pods ? group_of(gp, j, ta_max, tb_max, found) : -1;
+        g[i] = r.s[i] >= 0 ? group_of(gp, r.qc[i], r.qm[i], r.s[i], found) : -1;
         if (g[i] == kGroupDead) {                                 // fits nothing: answered here, never scanned
             gp.out_idx[j] = -1;
             gp.out_score[j] = -1.0;
             if (gp.out_gpos) gp.out_gpos[j] = 0xffffffffu;
         } else if (g[i] == kGroupDone) {                          // fits one of the first best-first nodes: that node is the answer
-            const int s = gp.sid ? canon_strategy(gp.sid[j]) : gp.uniform;
+            const int s = r.s[i];
             const size_t at = (size_t)s * gp.npad + found;
             gp.out_idx[j] = (long long)gp.order[at];
             gp.out_score[j] = gp.score_pos[at];
@@ -829,15 +903,14 @@ int snapshot_place_device(const kp_node_table &nodes, const kp_pod_table &pods, 
     // ---- pods ----
     if (per_pod) {
         const int gb = (int)((P + kGroupItems - 1) / kGroupItems);
-        double2 *probe = nullptr;
-        if (prune_depth > 0) {
-            probe = reinterpret_cast<double2 *>(w + L.off_probe);
-            probe_table_kernel<<<1, kMaxStrategies * kProbeMax, 0, stream>>>(t, strat_mask, hdr, po.order, (int)L.npad, probe);
-            KP_LAUNCH_CHECK("probe_table_kernel");
-        }
+        // thresholds the pass compares against (largest of the table; the probed best-first nodes) and their integer images
+        double2 *probe = reinterpret_cast<double2 *>(w + L.off_probe);
+        ProbeInt *lim = reinterpret_cast<ProbeInt *>(w + L.off_probe_int);
         GroupPods gp{(const long long *)pods.strategy_ids, (const long long *)pods.req_cpu_milli, (const long long *)pods.req_mem_bytes,
                      canon_strategy(strategy), P, po.uniq, (int)L.npad, big ? 0 : (int)n, (long long *)out_idx, out_score, tuning.out_gpos,
-                     probe, prune_depth, po.order, po.score_pos, tuning.gpos_by_pos, tuning.gpos_stride};
+                     probe, lim, prune_depth, po.order, po.score_pos, tuning.gpos_by_pos, (size_t)tuning.gpos_stride};
+        probe_table_kernel<<<1, kMaxStrategies * kProbeMax, 0, stream>>>(t, strat_mask, hdr, gp, probe, lim);
+        KP_LAUNCH_CHECK("probe_table_kernel");
         group_count_kernel<<<gb, 256, 0, stream>>>(gp, hdr);
         KP_LAUNCH_CHECK("group_count_kernel");
         group_assign_kernel<<<gb, 256, 0, stream>>>(gp, chunk_pods, hdr, perm);
