@@ -5,6 +5,7 @@
 //                                      mem_usage_pct, req_cpu_milli, req_mem_bytes, strategy_ids?, strategy, filter_mode)
 //       -> (node_idx int64[P], score float64[P])
 //   torch.ops.k8s_place.snapshot_place_out(... same ..., out_idx, out_score, workspace) -> ()      caller-owned buffers
+//   torch.ops.k8s_place.snapshot_place_pruned(... same inputs ..., probe_depth) -> (node_idx, score)   first-feasible probe (option)
 //   torch.ops.k8s_place.greedy_place(... same inputs ...) -> (node_idx, score, pod_count, cpu_usage_pct, mem_usage_pct)
 //   torch.ops.k8s_place.node_scores(7 node columns, strategy, filter_mode) -> (score, free_cpu, free_mem, eligible uint8)
 //   torch.ops.k8s_place.snapshot_workspace_bytes(n_nodes, n_pods, per_pod) / greedy_workspace_bytes(n_nodes, n_pods)
@@ -165,6 +166,26 @@ int64_t snapshot_workspace_bytes(int64_t n_nodes, int64_t n_pods, bool per_pod)
 
 int64_t greedy_workspace_bytes(int64_t n_nodes, int64_t n_pods) { return (int64_t)kp_greedy_workspace_bytes(n_nodes, n_pods); }
 
+// the same decisions with the first-feasible probe in front of the table scan (kp_snapshot_place_pruned; an option)
+std::tuple<Tensor, Tensor> snapshot_place_pruned(const Tensor &ac, const Tensor &am, const Tensor &pc, const Tensor &mp, const Tensor &ready,
+                                                 const Tensor &cu, const Tensor &mu, const Tensor &rc, const Tensor &rm,
+                                                 const c10::optional<Tensor> &sid, int64_t strategy, int64_t filter_mode, int64_t probe_depth)
+{
+    const Tables t = tables(ac, am, pc, mp, ready, cu, mu, rc, rm, sid);
+    const int64_t p = rc.numel();
+    Tensor out_idx = at::empty({p}, rc.options().dtype(at::kLong));
+    Tensor out_score = at::empty({p}, rc.options().dtype(at::kDouble));
+    const int64_t ws = (int64_t)kp_snapshot_workspace_bytes(pc.numel(), p, 1);      // the grouping pass needs the pod permutation
+    Tensor workspace = at::empty({ws < 256 ? 256 : ws}, rc.options().dtype(at::kByte));
+    if (probe_depth < 0 || probe_depth > 1 << 20) fail("probe_depth %lld out of range", (long long)probe_depth);
+    const c10::cuda::CUDAGuard guard(t.dev);
+    check(kp_snapshot_place_pruned(&t.nodes, &t.pods, (int)strategy, (int)filter_mode, (int)probe_depth, out_idx.data_ptr<int64_t>(),
+                                   out_score.data_ptr<double>(), workspace.data_ptr(), (size_t)workspace.numel(),
+                                   c10::cuda::getCurrentCUDAStream(t.dev.index()).stream()),
+          "kp_snapshot_place_pruned");
+    return {out_idx, out_score};
+}
+
 }  // namespace
 
 TORCH_LIBRARY(k8s_place, m)
@@ -175,6 +196,9 @@ TORCH_LIBRARY(k8s_place, m)
     m.def("snapshot_place_out(Tensor alloc_cpu_milli, Tensor alloc_mem_bytes, Tensor pod_count, Tensor max_pods, Tensor ready, "
           "Tensor cpu_usage_pct, Tensor mem_usage_pct, Tensor req_cpu_milli, Tensor req_mem_bytes, Tensor? strategy_ids, "
           "int strategy, int filter_mode, Tensor(a!) out_idx, Tensor(b!) out_score, Tensor(c!) workspace) -> ()");
+    m.def("snapshot_place_pruned(Tensor alloc_cpu_milli, Tensor alloc_mem_bytes, Tensor pod_count, Tensor max_pods, Tensor ready, "
+          "Tensor cpu_usage_pct, Tensor mem_usage_pct, Tensor req_cpu_milli, Tensor req_mem_bytes, Tensor? strategy_ids, "
+          "int strategy, int filter_mode, int probe_depth) -> (Tensor, Tensor)");
     m.def("greedy_place(Tensor alloc_cpu_milli, Tensor alloc_mem_bytes, Tensor pod_count, Tensor max_pods, Tensor ready, "
           "Tensor cpu_usage_pct, Tensor mem_usage_pct, Tensor req_cpu_milli, Tensor req_mem_bytes, Tensor? strategy_ids, "
           "int strategy, int filter_mode, Tensor? workspace) -> (Tensor, Tensor, Tensor, Tensor, Tensor)");
@@ -188,6 +212,7 @@ TORCH_LIBRARY_IMPL(k8s_place, CUDA, m)
 {
     m.impl("snapshot_place", &snapshot_place);
     m.impl("snapshot_place_out", &snapshot_place_out);
+    m.impl("snapshot_place_pruned", &snapshot_place_pruned);
     m.impl("greedy_place", &greedy_place);
     m.impl("node_scores", &node_scores);
 }

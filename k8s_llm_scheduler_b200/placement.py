@@ -155,6 +155,9 @@ def snapshot_place_pruned(nodes: Dict[str, torch.Tensor], req_cpu_milli: torch.T
     """``snapshot_place`` with the first-feasible probe (kp_snapshot_place_pruned): the same (node_idx, score), but a
     pod that fits one of the first ``probe_depth`` best-first nodes of its strategy is answered without a table scan.
     ``scanned=True`` also returns how many pods per strategy still took the full scan (synchronises)."""
+    if workspace is None and out is None and not scanned:        # the registered operator (torch.ops.k8s_place.snapshot_place_pruned)
+        sid, strat = _strategy_args(strategy)
+        return ops().snapshot_place_pruned(*_cols(nodes), req_cpu_milli, req_mem_bytes, sid, strat, int(filter_mode), int(probe_depth))
     lib = _lib.load()
     nst, device, n = _node_struct(nodes)
     pst, p, strat, per_pod = _pod_struct(req_cpu_milli, req_mem_bytes, strategy, device)

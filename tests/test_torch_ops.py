@@ -18,7 +18,7 @@ def ops():
 
 
 def test_extension_registers_its_operators(ops):
-    for name in ("snapshot_place", "snapshot_place_out", "greedy_place", "node_scores"):
+    for name in ("snapshot_place", "snapshot_place_out", "snapshot_place_pruned", "greedy_place", "node_scores"):
         schema = getattr(ops, name).default._schema
         assert schema.name == f"k8s_place::{name}"
     args = [a.name for a in ops.snapshot_place.default._schema.arguments]
@@ -50,6 +50,9 @@ def test_ops_match_the_oracle(ops):
     oi, os_ = oracle_snapshot(nodes, pods, 1, 1)
     assert_same_idx(out_idx.cpu().numpy(), oi)
     assert_same_f64(out_score.cpu().numpy(), os_)
+    pi, ps = ops.snapshot_place_pruned(*cols, rc, rm, None, 1, 1, 16)           # same answers with the probe in front
+    assert_same_idx(pi.cpu().numpy(), oi)
+    assert_same_f64(ps.cpu().numpy(), os_)
     g = ops.greedy_place(*cols, rc, rm, None, 0, 1, None)
     o = oracle_greedy(nodes, pods, 0, 1)
     assert_same_idx(g[0].cpu().numpy(), o[0])
