@@ -531,6 +531,9 @@ fast_greedy_kernel(FastIn in, FastRun r)
     __shared__ uint32_t c_res[2][8];                                   // best key of every CTA of the cluster
     __shared__ __align__(8) uint64_t xbar[2];                          // mbarriers of the per-pod exchange
     __shared__ uint32_t s_tbase[kFastMaxShapes + 1];
+    __shared__ uint32_t s_bound[2][32];
+    __shared__ uint16_t s_j[kFastPodBatch];                            // position in the batch of every pod that is scanned
+    __shared__ uint32_t s_wcnt[32];
 
     if (!r.hdr->ok) return;                                          // the fp64 kernel does the work instead
     constexpr int KS = MULTI ? kMaxStrategies : 1;
@@ -548,7 +551,11 @@ fast_greedy_kernel(FastIn in, FastRun r)
     const uint32_t idx_mask = (1u << r.idx_bits) - 1u;
     const int cta_base = crank * r.nodes_per_cta;
     const long long n_done = (long long)batch_n_done(r.hdr, r.batch);   // pods the sorted prefix has already decided
-    const uint32_t wmax_lo = r.hdr->wmax_lo, wmax_hi = r.hdr->wmax_hi;
+    // dead-pod bound: field-wise largest threshold of any node that can still be chosen.  It starts from every state
+    // that exists (prep kernels) and is refreshed from the LIVE node states at every pod batch: thresholds only shrink
+    // along a trajectory and a full node drops out, so the bound tightens as the cluster fills -- once no node is
+    // choosable it is 0 and every remaining pod is answered without a scan, a reduction or an exchange.
+    uint32_t wmax_lo = r.hdr->wmax_lo, wmax_hi = r.hdr->wmax_hi;
 
     if (tid <= kFastMaxShapes) s_tbase[tid] = r.hdr->traj_base[tid];
     for (int i = tid; i < kFastMaxTraj; i += kFastThreads) {
@@ -593,26 +600,112 @@ fast_greedy_kernel(FastIn in, FastRun r)
     uint32_t round = 0;
     __syncthreads();
     if (CLUSTER) cluster_barrier();                                    // every CTA's mbarriers exist before any peer signals them
+    // The live refresh of the dead-pod bound needs thresholds that never grow along a trajectory (usage rises with the
+    // pod count, so they do not -- unless an allocatable is negative).  Checked here once; otherwise the bound stays
+    // the static one.  (Every CTA of a cluster reads the same table and reaches the same verdict.)
+    bool mono = true;
+    {
+        const int n_shapes = (int)r.hdr->n_shapes;
+        for (int sh = warp; sh < n_shapes; sh += NW)
+            for (uint32_t i = s_tbase[sh] + lane; i + 1 < s_tbase[sh + 1]; i += 32)
+                mono = mono && (traj_w[i + 1] & 0x7fffu) <= (traj_w[i] & 0x7fffu) && ((traj_w[i + 1] >> 16) & 0x7fffu) <= ((traj_w[i] >> 16) & 0x7fffu);
+        mono = __syncthreads_and(mono) != 0;
+    }
+
+    // Maximum of one word over the CTAs of the cluster, through DSMEM without a cluster barrier: every CTA sends
+    // its word to every peer with st.async, which writes it into the peer's slot AND signals the peer's
+    // mbarrier (complete_tx); each CTA then waits on its OWN mbarrier only.  A cluster barrier
+    // here (even release / acquire at cluster scope) cost ~0.5 us per pod in ERRBAR + barrier
+    // latency -- 40 % of the kernel; tagging plain stores and spinning was slower still.
+    // Slots and mbarriers alternate by round parity: a CTA can be at most one round ahead of a
+    // peer, because round r + 1 needs the peer's word of round r + 1.
+    auto cluster_max = [&](uint32_t mine) -> uint32_t {
+        const int xp = (int)(round & 1u);
+        if (tid == 0) mbar_expect_tx(&xbar[xp], 4u * (CSIZE - 1));
+        if (tid < CSIZE && tid != crank)
+            dsmem_send_u32(smem_u32(&c_res[xp][crank]), smem_u32(&xbar[xp]), (uint32_t)tid, mine);
+        mbar_wait(&xbar[xp], (round >> 1) & 1u);
+        uint32_t g = mine;
+#pragma unroll
+        for (int c = 0; c < CSIZE; ++c) if (c != crank) g = max(g, c_res[xp][c]);
+        ++round;
+        return g;
+    };
 
     for (long long base = n_done; base < in.n_pods; base += kFastPodBatch) {
         const int cnt = (int)min((long long)kFastPodBatch, in.n_pods - base);
-        __syncthreads();
-        for (int i = tid; i < cnt; i += kFastThreads) {
-            s_x[i] = r.xs[base + i];
-            s_sid[i] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + i]) : us);
+        __syncthreads();                                               // the batch before is no longer read (s_x, s_sid, s_bound)
+        // the dead-pod bound from the live states (every CTA of a cluster ends up with the same two values): per
+        // choosable node the largest thresholds it can still have -- its current state's, and for a node that has not
+        // been committed to yet also those of the first trajectory state it would move to (an initial row need not
+        // lie on its shape's trajectory: the caller's usage figures are replaced at the first commit)
+        if (mono) {
+            uint32_t mlo = 0u, mhi = 0u;
+#pragma unroll
+            for (int k = 0; k < NPT; ++k) {
+                bool choosable = false;
+#pragma unroll
+                for (int q = 0; q < KS; ++q) choosable |= key[q][k] != 0u;
+                if (choosable) {
+                    mlo = max(mlo, w[k] & 0x7fffu);
+                    mhi = max(mhi, (w[k] >> 16) & 0x7fffu);
+                    const uint32_t ct = c_t[k * kFastThreads + tid];
+                    if (!(ct >> 31)) {
+                        const uint32_t nw = traj_w[(ct & 0x7fffffffu) + 1u];
+                        mlo = max(mlo, nw & 0x7fffu);
+                        mhi = max(mhi, (nw >> 16) & 0x7fffu);
+                    }
+                }
+            }
+            mlo = __reduce_max_sync(0xffffffffu, mlo);
+            mhi = __reduce_max_sync(0xffffffffu, mhi);
+            if (lane == 0) { s_bound[0][warp] = mlo; s_bound[1][warp] = mhi; }
+            __syncthreads();
+            mlo = __reduce_max_sync(0xffffffffu, lane < NW ? s_bound[0][lane] : 0u);
+            mhi = __reduce_max_sync(0xffffffffu, lane < NW ? s_bound[1][lane] : 0u);
+            if (CLUSTER) {
+                mlo = cluster_max(mlo);
+                mhi = cluster_max(mhi);
+            }
+            wmax_lo = min(wmax_lo, mlo);
+            wmax_hi = min(wmax_hi, mhi);
         }
-        __syncthreads();
+        // Load the batch.  Pods beyond the bound fit nothing: they are answered here, in parallel, and the rest is
+        // compacted (in order) so that the sequential loop below only walks pods that need a decision.  Every CTA of
+        // a cluster sees the same requests and the same bound, hence the same list.
+        int live = 0;
+        for (int i0 = 0; i0 < cnt; i0 += kFastThreads) {
+            const int i = i0 + tid;
+            uint32_t xi = 0u;
+            bool keep = false;
+            if (i < cnt) {
+                xi = r.xs[base + i];
+                keep = !((xi & 0xffffu) > wmax_lo || (xi >> 16) > wmax_hi);
+                if (!keep && crank == 0) { r.out_idx[base + i] = -1; r.out_entry[base + i] = kNoEntry; }
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) s_wcnt[warp] = (uint32_t)__popc(bal);
+            __syncthreads();
+            uint32_t before = 0u, all = 0u;
+#pragma unroll
+            for (int q = 0; q < NW; ++q) {
+                const uint32_t c = s_wcnt[q];
+                before += q < warp ? c : 0u;
+                all += c;
+            }
+            if (keep) {
+                const int at = live + (int)before + __popc(bal & ((1u << lane) - 1u));
+                s_x[at] = xi;
+                s_sid[at] = (uint8_t)(in.sid ? canon_strategy(in.sid[base + i]) : us);
+                s_j[at] = (uint16_t)i;
+            }
+            live += (int)all;
+            __syncthreads();                                           // s_wcnt is rewritten by the next chunk
+        }
         uint32_t x = s_x[0];
         int s = s_sid[0];
-        for (int j = 0; j < cnt; ++j) {
-            if ((x & 0xffffu) > wmax_lo || (x >> 16) > wmax_hi) {
-                // larger than every state that exists: no scan, no reduction, no exchange (every CTA of a cluster
-                // takes this branch for the same pods)
-                if (crank == 0 && tid == 0) { r.out_idx[base + j] = -1; r.out_entry[base + j] = kNoEntry; }
-                x = s_x[j + 1];
-                s = s_sid[j + 1];
-                continue;
-            }
+        for (int jj = 0; jj < live; ++jj) {
+            const int j = (int)s_j[jj];
             uint32_t best;
             if (!MULTI) {
                 const bool all_fit = ((~(wmin - x)) & kFastGuards) == 0u;
@@ -621,32 +714,14 @@ fast_greedy_kernel(FastIn in, FastRun r)
             } else if (s == 0) best = fast_scan<NPT, KS, 0>(w, key, x);         // block-uniform branch per pod
             else if (s == 1) best = fast_scan<NPT, KS, (KS > 1 ? 1 : 0)>(w, key, x);
             else best = fast_scan<NPT, KS, (KS > 2 ? 2 : 0)>(w, key, x);
-            const uint32_t x_next = s_x[j + 1];                        // next pod's request, off the critical path
-            const int s_next = s_sid[j + 1];                           // (one spare element past the batch)
-            const int par = j & 1;
+            const uint32_t x_next = s_x[jj + 1];                       // next pod's request, off the critical path
+            const int s_next = s_sid[jj + 1];                          // (one spare element past the batch)
+            const int par = jj & 1;
             best = __reduce_max_sync(0xffffffffu, best);
             if (lane == 0) w_res[par][warp] = best;
             __syncthreads();
             best = __reduce_max_sync(0xffffffffu, lane < NW ? w_res[par][lane] : 0u);
-            if (CLUSTER) {
-                // Exchange through DSMEM without a cluster barrier: every CTA sends its best key to every
-                // peer with st.async, which writes the word into the peer's slot AND signals the peer's
-                // mbarrier (complete_tx); each CTA then waits on its OWN mbarrier only.  A cluster barrier
-                // here (even release / acquire at cluster scope) cost ~0.5 us per pod in ERRBAR + barrier
-                // latency -- 40 % of the kernel; tagging plain stores and spinning was slower still.
-                // Slots and mbarriers alternate by round parity: a CTA can be at most one round ahead of a
-                // peer, because round r + 1 needs the peer's word of round r + 1.
-                const int xp = (int)(round & 1u);
-                if (tid == 0) mbar_expect_tx(&xbar[xp], 4u * (CSIZE - 1));
-                if (tid < CSIZE && tid != crank)
-                    dsmem_send_u32(smem_u32(&c_res[xp][crank]), smem_u32(&xbar[xp]), (uint32_t)tid, best);
-                mbar_wait(&xbar[xp], (round >> 1) & 1u);
-                uint32_t g = best;
-#pragma unroll
-                for (int c = 0; c < CSIZE; ++c) if (c != crank) g = max(g, c_res[xp][c]);
-                best = g;
-                ++round;
-            }
+            if (CLUSTER) best = cluster_max(best);
             x = x_next;
             s = s_next;
             if (best == 0u) {

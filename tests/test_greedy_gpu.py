@@ -157,6 +157,36 @@ def test_fast_path_large_tables_and_depletion():
     assert (g[0] < 0).any() and (g[2] <= 110).all()
 
 
+@pytest.mark.parametrize("cluster", ["1", "2"])
+def test_dead_pod_bound_follows_the_live_states(cluster, monkeypatch):
+    """The loop refreshes its "fits nothing" bound from the live node states at every pod batch.  It must stay exact
+    (a) when the cluster fills up and the rest of the pods is answered without a scan, per-pod strategies included;
+    (b) when a node's FIRST commit makes it roomier -- the caller's usage figures (99 %) are replaced by the
+        reference's pod_count / max_pods formula (scheduler.py:150-151), so pods that fit no node now fit later;
+    (c) when thresholds grow along a trajectory (negative allocatable): the refresh must not be used at all."""
+    monkeypatch.setenv("KP_GREEDY_CLUSTER", cluster)
+    rng = np.random.default_rng(8)
+    nodes, pods = synth.config5(300, 40_000, seed=41)                                      # (a) ~15 k free slots, 40 k pods
+    for sid in (0, 2):
+        _check_greedy(nodes, pods, sid, 1, what=f"fills up, strategy {sid}")
+    _check_greedy(nodes, pods, 0, 1, per_pod=True, what="fills up, per-pod strategies")
+    n = 64                                                                                 # (b)
+    busy = NodeTable.from_columns(alloc_cpu_milli=[32_000] * n, alloc_mem_bytes=[128 << 30] * n, pod_count=[1] * n, max_pods=[110] * n,
+                                  ready=[1] * n, cpu_usage_pct=[99.0] * n, mem_usage_pct=[99.0] * n)
+    small = rng.random(6000) < 0.5
+    small[:3] = False                                              # the first pods are large: no node has been reset yet
+    mixed = PodTable.from_columns(np.where(small, 100, 8000), np.where(small, 64 << 20, 16 << 30))
+    for sid in (0, 1, 2):
+        _check_greedy(busy, mixed, sid, 1, what=f"first commit frees capacity, strategy {sid}")
+    g = device_greedy(busy, mixed, 0, 1)
+    assert (g[0][~small] >= 0).any() and (g[0][~small] < 0).any()      # large pods: rejected at first, placed once a node was reset
+    odd = NodeTable.from_columns(alloc_cpu_milli=[-4000] * 8 + [16_000] * 40, alloc_mem_bytes=[64 << 30] * 48, pod_count=[2] * 48,    # (c)
+                                 max_pods=[60] * 48, ready=[1] * 48, cpu_usage_pct=[10.0] * 48, mem_usage_pct=[10.0] * 48)
+    neg = PodTable.from_columns(rng.integers(-4500, 3000, 5000), rng.integers(1, 1 << 30, 5000))
+    for sid in (0, 1):
+        _check_greedy(odd, neg, sid, 1, what=f"negative allocatable, strategy {sid}")
+
+
 def test_fast_path_matches_fp64_kernel(monkeypatch):
     nodes, pods = synth.config5(2500, 5000, seed=33)
     fast = device_greedy(nodes, pods, 0, 1, per_pod=True)
