@@ -357,21 +357,28 @@ class Session:
                                           self._d_idx_ref, self._d_score_ref), "kp_session_decide")
         return self._d_idx.value, self._d_score.value
 
-    def greedy(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY):
-        """Returns (idx, score, final_pod_count, final_cpu_usage, final_mem_usage) numpy arrays."""
+    def greedy(self, nodes, pods, strategy: int = 0, filter_mode: int = FILTER_CAPACITY, out=None):
+        """Returns (idx, score, final_pod_count, final_cpu_usage, final_mem_usage) numpy arrays, or fills ``out`` =
+        the same five host buffers (numpy, or pinned torch tensors: device-to-host copies into pageable memory are
+        staged and several times slower)."""
         nst, keep = self._node_struct(nodes) if nodes is not None else (None, [])
         pst, keep2 = self._pod_struct(pods)
         p = pst.n_pods
         n = nst.n_nodes if nst is not None else self._resident
-        idx, score = np.empty(p, np.int64), np.empty(p, np.float64)
-        pc, cu, mu = np.empty(n, np.int64), np.empty(n, np.float64), np.empty(n, np.float64)
+        if out is None:
+            out = (np.empty(p, np.int64), np.empty(p, np.float64), np.empty(n, np.int64), np.empty(n, np.float64), np.empty(n, np.float64))
+        want = ((p, np.int64), (p, np.float64), (n, np.int64), (n, np.float64), (n, np.float64))
+        ptrs = []
+        for buf, (count, dt) in zip(out, want):
+            ptr, ref = _host_ptr(buf, dt)
+            if ref is not buf or len(ref) != count:
+                raise TypeError("out buffers must be contiguous host arrays: int64[p], float64[p], int64[n], float64[n], float64[n]")
+            ptrs.append(ptr)
         check(self._lib.kp_session_greedy(self._h, byref(nst) if nst is not None else None, byref(pst),
-                                          int(strategy), int(filter_mode), idx.ctypes.data,
-                                          score.ctypes.data, pc.ctypes.data, cu.ctypes.data,
-                                          mu.ctypes.data), "kp_session_greedy")
+                                          int(strategy), int(filter_mode), *ptrs), "kp_session_greedy")
         if nst is not None:
             self._resident = nst.n_nodes
-        return idx, score, pc, cu, mu
+        return out
 
     def last_copy_bytes(self) -> Tuple[int, int]:
         a, b = c_int64(), c_int64()

@@ -118,6 +118,17 @@ def test_session_greedy_matches_device_api():
         assert_same_idx(h[0], d[0])
         assert_same_f64(h[1], d[1])
         assert np.array_equal(h[2], d[2])
+        # caller-owned (pinned) result buffers
+        import torch
+        out = tuple(torch.empty(k, dtype=t).pin_memory() for k, t in ((4000, torch.int64), (4000, torch.float64), (1500, torch.int64),
+                                                                      (1500, torch.float64), (1500, torch.float64)))
+        assert s.greedy(nodes, pods, 0, 1, out=out) is out
+        assert_same_idx(out[0].numpy(), d[0])
+        assert_same_f64(out[1].numpy(), d[1])
+        assert np.array_equal(out[2].numpy(), d[2])
+        assert_same_f64(out[3].numpy(), d[3])
+        with pytest.raises(TypeError):
+            s.greedy(nodes, pods, 0, 1, out=out[:4] + (np.empty(7),))
 
 
 # ---- fast path (kp_greedy_fast.cu): integer state machine, clusters, fallbacks --------------
