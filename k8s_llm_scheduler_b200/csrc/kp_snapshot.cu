@@ -237,15 +237,37 @@ __device__ __forceinline__ void group_limits(const GroupPods &g, const SnapHeade
     ta_max = da > 0 ? g.uniq[da - 1] : ninf;
     tb_max = db > 0 ? g.uniq[(size_t)g.npad + db - 1] : ninf;
 }
-// qc / qm: the pod's requests as they lie in the table; sid: its canonical strategy
-__device__ __forceinline__ int group_of(const GroupPods &g, long long qc, long long qm, int s, int &found)
+// what every pod of a thread is compared with first, loaded once per thread: the table's largest thresholds and the
+// first probed node of every strategy (most pods are settled by these; deeper probe entries are read on demand)
+struct GroupHot {
+    long long dead_cpu, dead_mem;
+    long long cpu0[kMaxStrategies], mem0[kMaxStrategies];
+};
+__device__ __forceinline__ GroupHot group_hot(const GroupPods &g)
+{
+    GroupHot h;
+    h.dead_cpu = __ldg(&g.lim->dead_cpu);
+    h.dead_mem = __ldg(&g.lim->dead_mem);
+#pragma unroll
+    for (int s = 0; s < kMaxStrategies; ++s) {
+        // no probe: an entry nothing fits
+        h.cpu0[s] = g.probe_depth > 0 ? __ldg(&g.lim->cpu[s][0]) : -kExactMax - 1;
+        h.mem0[s] = g.probe_depth > 0 ? __ldg(&g.lim->mem[s][0]) : -kExactMax - 1;
+    }
+    return h;
+}
+// qc / qm: the pod's requests as they lie in the table; s: its canonical strategy
+__device__ __forceinline__ int group_of(const GroupPods &g, const GroupHot &h, long long qc, long long qm, int s, int &found)
 {
     const ProbeInt *lim = g.lim;
     const bool exact = (unsigned long long)qc + (unsigned long long)kExactMax <= 2ull * kExactMax &&
                        (unsigned long long)qm + (unsigned long long)kExactMax <= 2ull * kExactMax;
     if (exact) {
-        if (qc > __ldg(&lim->dead_cpu) || qm > __ldg(&lim->dead_mem)) return kGroupDead;
-        for (int k = 0; k < g.probe_depth; ++k)                    // entries past the table fit nothing
+        if (qc > h.dead_cpu || qm > h.dead_mem) return kGroupDead;
+        const long long c0 = s == 0 ? h.cpu0[0] : (s == 1 ? h.cpu0[1] : h.cpu0[2]);
+        const long long m0 = s == 0 ? h.mem0[0] : (s == 1 ? h.mem0[1] : h.mem0[2]);
+        if (qc <= c0 && qm <= m0) { found = 0; return kGroupDone; }
+        for (int k = 1; k < g.probe_depth; ++k)                    // entries past the table fit nothing
             if (qc <= __ldg(&lim->cpu[s][k]) && qm <= __ldg(&lim->mem[s][k])) { found = k; return kGroupDone; }
         return s;
     }
@@ -313,12 +335,13 @@ group_count_kernel(GroupPods gp, SnapHeader *hdr)
     __syncthreads();
     GroupRows r;
     group_load(gp, (long long)blockIdx.x * kGroupItems, r);
+    const GroupHot hot = group_hot(gp);
     unsigned c[kMaxStrategies] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         if (r.s[i] >= 0) {
             int found;
-            const int g = group_of(gp, r.qc[i], r.qm[i], r.s[i], found);
+            const int g = group_of(gp, hot, r.qc[i], r.qm[i], r.s[i], found);
 #pragma unroll
             for (int s = 0; s < kMaxStrategies; ++s) c[s] += g == s;
         }
@@ -342,13 +365,14 @@ group_assign_kernel(GroupPods gp, int chunk_pods, SnapHeader *hdr, uint32_t *__r
     const int lane = threadIdx.x & 31;
     GroupRows r;
     group_load(gp, base, r);
+    const GroupHot hot = group_hot(gp);
     int g[kGroupPerThread];
     unsigned c[kMaxStrategies] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < kGroupPerThread; ++i) {
         const long long j = base + i * 256 + threadIdx.x;
         int found = 0;
-        g[i] = r.s[i] >= 0 ? group_of(gp, r.qc[i], r.qm[i], r.s[i], found) : -1;
+        g[i] = r.s[i] >= 0 ? group_of(gp, hot, r.qc[i], r.qm[i], r.s[i], found) : -1;
         if (g[i] == kGroupDead) {                                 // fits nothing: answered here, never scanned
             gp.out_idx[j] = -1;
             gp.out_score[j] = -1.0;
