@@ -148,3 +148,30 @@ def _raises(fn):
     except ValueError:
         return "ValueError"
     return "ok"
+
+
+def test_record_walker_fills_column_buffers_kept_across_calls():
+    """mode + 4 of the C walker (the adapter's one-decision path): buffers larger than the list, rows [0, n) written,
+    the rest untouched; without the flag the sizes must match exactly; shorter buffers are refused either way."""
+    import k8s_llm_scheduler_b200.tables as T
+    from k8s_llm_scheduler_b200.build import build_pyobj
+    from tests.helpers import COND
+    build_pyobj()
+    from k8s_llm_scheduler_b200 import _kp_pyobj as walker
+    nodes = [T.NodeMetrics(f"n{i}", 10.0 + i, 20.0 + i, 8.0, 16.0, i, 110, conditions=COND["ready" if i % 2 else "false"])
+             for i in range(5)]
+    dt = {"alloc_cpu_milli": np.int64, "alloc_mem_bytes": np.int64, "pod_count": np.int64, "max_pods": np.int64, "ready": np.uint8,
+          "cpu_usage_pct": np.float64, "mem_usage_pct": np.float64}
+    cap = [np.full(16, 77, dt[k]) for k in T.NODE_COLUMNS]
+    walker.node_metrics_to_columns(nodes, *cap, 1 | 4)
+    want = T.NodeTable.from_node_metrics(nodes)
+    for k, buf in zip(T.NODE_COLUMNS, cap):
+        assert np.array_equal(buf[:5], getattr(want, k)), k
+        assert (buf[5:] == 77).all(), k
+    walker.node_metrics_to_columns(nodes, *cap, 2 | 4)                      # ready-only: allocatable columns zeroed, not read
+    assert not cap[0][:5].any() and not cap[1][:5].any() and cap[2][:5].tolist() == [0, 1, 2, 3, 4]
+    with pytest.raises(ValueError):
+        walker.node_metrics_to_columns(nodes, *cap, 1)                      # exact-size mode refuses larger buffers
+    short = [np.zeros(3, dt[k]) for k in T.NODE_COLUMNS]
+    with pytest.raises(ValueError):
+        walker.node_metrics_to_columns(nodes, *short, 1 | 4)
