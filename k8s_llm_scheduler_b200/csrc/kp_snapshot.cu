@@ -168,11 +168,12 @@ constexpr int kGroupItems = 256 * kGroupPerThread;
 // First-feasible probe (PlaceTuning::prune_depth > 0).  The best-first table is sorted by (score desc, node index asc),
 // so the node a pod gets is the FIRST table entry it fits (scheduler.py:547: strict '>' keeps the earlier of equal
 // scores).  The grouping pass therefore tries the first prune_depth entries of the pod's strategy table directly --
-// fp64 thresholds of those few nodes, computed by probe_table_kernel -- and a pod that fits one of them is answered on
+// the thresholds of those few nodes, prepared by probe_table_kernel -- and a pod that fits one of them is answered on
 // the spot; only the rest enter a strategy group and are scanned against the whole table by the placement kernel.
 // The result is the same bit for bit; the number of pairs EVALUATED drops from pods x nodes to roughly pods x (depth
 // of the first fit), which is why this is an option and not the measured roofline kernel (SURVEY.md section 7,
 // "algorithmic honesty": evaluated and effective pairs are reported separately wherever it is used).
+//
 // Integer images of the fp64 thresholds the grouping pass compares against.  A request is an int64 (milli-cores,
 // bytes) and the reference compares fl(milli / 1000.0) resp. bytes * 2^-30 with a node's free capacity T; both maps are
 // monotone, so "request fits" is "request <= M" for M = the LARGEST integer whose image is <= T.  M is found once per
