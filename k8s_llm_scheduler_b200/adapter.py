@@ -10,6 +10,9 @@ it over the method without touching the reference file.
 The decision itself is computed on the GPU through the C ABI (kp_session_snapshot with
 one pod, KP_FILTER_READY -- the reference's own filter).  There is no CPU path here: if the
 CUDA library cannot be loaded the constructor raises.
+
+A ``FallbackPlacer`` owns one session and one set of column buffers that every call reuses: like the
+reference's scheduler object it serves one scheduling loop -- calls from several threads need a placer each.
 """
 from __future__ import annotations
 
