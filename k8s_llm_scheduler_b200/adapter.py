@@ -21,7 +21,7 @@ from typing import Any, Callable, List, Mapping, Optional, Sequence
 
 import numpy as np
 
-from ._lib import FILTER_CAPACITY, FILTER_READY, KpNodeTable, PlacementError
+from ._lib import FILTER_CAPACITY, FILTER_READY, KpNodeTable
 from .placement import Session
 from .tables import NODE_COLUMNS, NodeTable, PodTable, SchedulingDecision, _record_walker, strategy_id
 
